@@ -1,0 +1,255 @@
+/*
+ * rt_b200.h -- C ABI of librt_b200.so: the B200 (sm_100a) render path for rust_tracer.
+ *
+ * This header is the drop-in boundary.  Every entry point replaces one call the
+ * reference's host code (src/main.rs, src/gui.rs) makes into its render path; the
+ * reference file:line each one stands in for is cited beside it.  Signatures use plain
+ * pointers, sizes and POD structs only (no C++ / torch types) so that a Rust `-sys`
+ * crate, cgo, JNI or ctypes can bind them directly (INTEGRATION.md shows the Rust
+ * binding).
+ *
+ * Conventions
+ *   - every function returns RT_OK (0) or a negative rt_status; rt_last_error() gives
+ *     the message of the last failure on the calling thread.  Nothing unwinds across
+ *     the ABI (the reference panics instead: src/cli.rs:123, src/math/matrix.rs:106).
+ *   - there is NO CPU fallback: without a usable CUDA device every compute entry point
+ *     fails with RT_ERR_CUDA.
+ *   - calls are synchronous unless the name ends in _device; one handle is used from one
+ *     thread at a time (the reference is single-threaded, `Rc<RefCell<..>>` everywhere).
+ *   - all matrices are row-major 4x4 f32, column-vector convention
+ *     (src/math/matrix.rs:5-9,229-252).
+ *   - images are row-major: pixel (u, v) = column u, row v, 3 channels, at
+ *     ((v_local * width) + u) * 3 where v_local counts only the rows this call renders
+ *     (all rows when world == 1).  The reference's RenderBuffer is column-major
+ *     buf[u][v] (src/render.rs:5-19); the host shim transposes.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_B200_ABI_VERSION 1
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID = -1,      /* bad argument / malformed scene description        */
+    RT_ERR_UNSUPPORTED = -2,  /* e.g. a texture function that is not in rt_colorfn */
+    RT_ERR_CUDA = -3,         /* CUDA runtime failure or no device                 */
+    RT_ERR_NOMEM = -4,        /* host or device allocation failed                  */
+    RT_ERR_INTERNAL = -5
+} rt_status;
+
+/* ---- scene description (mirrors src/scene/{mod,sphere,plane,triangle,cube,material}.rs; copied at rt_scene_create) ---------- */
+
+typedef enum rt_shape_kind {
+    RT_SHAPE_SPHERE = 0,   /* src/scene/sphere.rs   : unit sphere under `transform`            */
+    RT_SHAPE_PLANE = 1,    /* src/scene/plane.rs    : one-sided infinite plane                 */
+    RT_SHAPE_TRIANGLE = 2, /* src/scene/triangle.rs : world-space triangle (transform ignored) */
+    RT_SHAPE_CUBE = 3      /* src/scene/cube.rs     : unit cube = 12 fixed triangles           */
+} rt_shape_kind;
+
+/*
+ * One entry of Scene::shapes (src/scene/mod.rs:22-27,40-44).  The index of a shape in
+ * rt_scene_desc.shapes is its id (add_shape assigns id = index) and is the tie-break
+ * order of Scene::intersect (src/scene/mod.rs:98-116).
+ *
+ * `transform` / `inv_transform` are what Sphere/Plane/Cube::set_transform store
+ * (src/scene/sphere.rs:100-103, plane.rs:54-57, cube.rs:104-107); the caller computes
+ * the inverse (the reference's Gauss-Jordan, src/math/matrix.rs:88-142) so that the
+ * device sees bit-identical matrices.  Triangles ignore both (src/scene/triangle.rs:51).
+ *
+ * p[12]:
+ *   plane    : origin(3), normal(3), u axis(3), v axis(3)      (src/scene/plane.rs:8-19,22-42)
+ *   triangle : v0(3), v1(3), v2(3), normal(3)                  (src/scene/triangle.rs:7-14,17-39)
+ *   sphere / cube : unused
+ */
+typedef struct rt_shape {
+    int32_t kind;      /* rt_shape_kind */
+    int32_t material;  /* index into rt_scene_desc.materials */
+    float transform[16];
+    float inv_transform[16];
+    float p[12];
+} rt_shape;
+
+/*
+ * ColorFun = fn((f32,f32)) -> Color (src/scene/material.rs:3) cannot cross an FFI, so
+ * the ABI carries a closed set of device texture functions.
+ */
+typedef enum rt_colorfn_kind {
+    RT_COLOR_CONST = 0,        /* rgb, whatever the texture coordinate                     */
+    RT_COLOR_CHECKERBOARD = 1  /* src/my_scene.rs:26-43 : rgb or 0.5*rgb by cell parity    */
+} rt_colorfn_kind;
+
+typedef struct rt_colorfn {
+    int32_t kind; /* rt_colorfn_kind */
+    float rgb[3];
+} rt_colorfn;
+
+typedef enum rt_material_kind {
+    RT_MATERIAL_PHONG = 0,         /* src/scene/material.rs:24-101  (set_diffuse mutates)   */
+    RT_MATERIAL_TEXTURE_PHONG = 1  /* src/scene/material.rs:103-191 (set_diffuse is a no-op) */
+} rt_material_kind;
+
+typedef struct rt_material {
+    int32_t kind; /* rt_material_kind */
+    rt_colorfn ambient;
+    rt_colorfn diffuse;
+    rt_colorfn specular;
+    float power;
+    float reflectivity;
+    float refraction_index;
+} rt_material;
+
+typedef enum rt_light_kind {
+    RT_LIGHT_POINT = 0,   /* src/scene/mod.rs:178-221 : casts a shadow ray                */
+    RT_LIGHT_AMBIENT = 1  /* src/scene/mod.rs:223-246 : direction (0,0,0), no shadow ray  */
+} rt_light_kind;
+
+typedef struct rt_light {
+    int32_t kind; /* rt_light_kind */
+    float pos[3];
+    float color[3];
+} rt_light;
+
+typedef struct rt_scene_desc {
+    const rt_shape *shapes;
+    int32_t n_shapes;
+    const rt_material *materials;
+    int32_t n_materials;
+    const rt_light *lights;
+    int32_t n_lights;
+    float ambient[3]; /* Scene::ambient (src/scene/mod.rs:50-56) */
+} rt_scene_desc;
+
+/* Camera (src/render.rs:155-186).  rt_camera_default fills Camera::new's constants. */
+typedef struct rt_camera {
+    float origin[3];
+    float x_min, x_max, y_min, y_max;
+    int32_t x_res, y_res;
+} rt_camera;
+
+typedef enum rt_render_flags {
+    RT_FLAG_NONE = 0,
+    /* test every (ray, shape) pair with the exact arithmetic instead of bound-filtering
+     * first; same image by construction, used to audit the filter.                      */
+    RT_FLAG_AUDIT_ALL_PAIRS = 1,
+    /* evaluate with render_tree.rs's weights instead of render.rs's        */
+    RT_FLAG_FOREST_SHADING = 2
+} rt_render_flags;
+
+typedef struct rt_render_params {
+    int32_t depth;     /* --depth (src/cli.rs:55-60); 0 renders black (src/render.rs:43-45) */
+    int32_t spp;       /* 1 = the reference's pixel-corner ray; 4 = 2x2 stratified jitter   */
+    uint64_t seed;     /* jitter seed, only read when spp == 4                              */
+    int32_t rank;      /* interleaved row tiles: this call renders the rows v with          */
+    int32_t world;     /*   (v / tile_rows) % world == rank                                 */
+    int32_t tile_rows; /* >= 1                                                              */
+    int32_t flags;     /* rt_render_flags                                                   */
+} rt_render_params;
+
+/* Work counters of one render / forest build (the roofline numerator). */
+typedef struct rt_stats {
+    uint64_t pixels;        /* pixels rendered by this call (after row tiling)            */
+    uint64_t rays;          /* Scene::intersect queries: primary + reflect + refract + shadow */
+    uint64_t shadow_rays;   /* of which PointLight::get_energy queries                    */
+    uint64_t nodes;         /* ray-tree nodes (rays that hit something, shadows excluded) */
+    uint64_t sphere_tests;  /* ray x sphere pairs resolved                                */
+    uint64_t plane_tests;
+    uint64_t triangle_tests;
+    uint64_t cube_tests;    /* each = 12 triangle tests + one ray transform               */
+    uint64_t exact_tests;   /* pairs that went through the exact (reference-order) test   */
+    double   algorithmic_flops; /* per SURVEY 8d: 54/sphere, 30/triangle, 47|14/plane, 33+12*30/cube, 60+70L/node */
+    float    sweep_ms;      /* device time in the nearest-hit sweeps (CUDA events)        */
+    float    shade_ms;      /* device time in ray generation, spawn and shading           */
+    float    total_ms;      /* device time of the whole call                              */
+} rt_stats;
+
+typedef struct rt_scene rt_scene;   /* opaque: device-resident scene tables */
+typedef struct rt_forest rt_forest; /* opaque: device-resident ray forest   */
+
+/* ---- library ------------------------------------------------------------------------ */
+
+int rt_abi_version(void);
+const char *rt_last_error(void);
+/* Number of CUDA devices, or RT_ERR_CUDA. */
+int rt_device_count(void);
+/* Camera::new(x_res, y_res) (src/render.rs:166-176). */
+void rt_camera_default(int32_t x_res, int32_t y_res, rt_camera *out);
+/* Rows a (rank, world, tile_rows) call renders out of `height`; fills rows[] (capacity
+ * `cap`, may be NULL) in increasing order and returns the count.                         */
+int32_t rt_tile_rows_for_rank(int32_t height, int32_t rank, int32_t world, int32_t tile_rows,
+                              int32_t *rows, int32_t cap);
+
+/* ---- scene -------------------------------------------------------------------------- */
+
+/* Replaces building `Scene` + `create_scene` for the device (src/main.rs:33-34): copies
+ * the description into structure-of-arrays device tables on CUDA device `device`.       */
+int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out);
+/* Material::set_diffuse + friends after upload (src/gui.rs:221-235): replaces the whole
+ * material table, geometry untouched.  n must equal the scene's n_materials.            */
+int rt_scene_update_materials(rt_scene *scene, const rt_material *materials, int32_t n);
+void rt_scene_destroy(rt_scene *scene);
+
+/* ---- Basic renderer ------------------------------------------------------------------ */
+
+/* render::render(&camera, &scene, &mut buffer, depth) (src/render.rs:31-38; callers
+ * src/main.rs:251, src/render.rs:27).  Host output buffers, either may be NULL:
+ *   rgb_f32 : un-clamped Color per pixel (what RenderBuffer holds), 3 floats
+ *   rgb_u8  : Color::as_u8 (src/scene/color.rs:43-46), what bmp.rs writes
+ * Both cover only the rows of (rank, world, tile_rows).  stats may be NULL.             */
+int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *params,
+              float *rgb_f32, uint8_t *rgb_u8, rt_stats *stats);
+
+/* Same, but the outputs are DEVICE pointers on the scene's device (e.g. a torch tensor's
+ * data_ptr) and nothing is copied to the host; returns after the work is complete.  Used
+ * to time the path with inputs resident, and to hand tiles to an NCCL gather.           */
+int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_render_params *params,
+                     void *d_rgb_f32, void *d_rgb_u8, rt_stats *stats);
+
+/* ---- RayForest renderer -------------------------------------------------------------- */
+
+/* render_tree::generate_ray_forest (src/render_tree.rs:147-164; caller src/main.rs:269):
+ * all ray casting; the forest stays on the device.                                      */
+int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_params *params,
+                    rt_forest **out, rt_stats *stats);
+/* render_tree::render_forest (src/render_tree.rs:121-127; caller src/main.rs:286):
+ * shading only, with the scene's CURRENT material table.  `ambient` overrides the
+ * scene's ambient when not NULL (the reference passes it explicitly).                   */
+int rt_forest_eval(rt_forest *forest, const float *ambient, float *rgb_f32, uint8_t *rgb_u8,
+                   rt_stats *stats);
+/* render_tree::render_forest_filter (src/render_tree.rs:129-145; callers src/main.rs:187,
+ * src/gui.rs:168): re-shades only pixels whose tree holds one of mutated_ids; the other
+ * pixels of the in/out buffers are left untouched.  *n_evaluated (may be NULL) receives
+ * the number of trees re-shaded.                                                         */
+int rt_forest_eval_filtered(rt_forest *forest, const float *ambient, const int32_t *mutated_ids,
+                            int32_t n_ids, float *rgb_f32_inout, uint8_t *rgb_u8_inout,
+                            uint64_t *n_evaluated, rt_stats *stats);
+
+/* RayForest::stats (src/render_tree.rs:73-105). */
+typedef struct rt_forest_stats {
+    uint64_t num_trees;
+    uint64_t num_intersections;
+    uint64_t smallest_tree, largest_tree, median, p90, p95, p99;
+} rt_forest_stats;
+int rt_forest_get_stats(rt_forest *forest, rt_forest_stats *out);
+/* RayForest::size (src/render_tree.rs:62-64) and trees_with (:68-70). */
+int rt_forest_size(rt_forest *forest, uint64_t *out);
+int rt_forest_trees_with(rt_forest *forest, int32_t shape_id, uint64_t *out);
+void rt_forest_destroy(rt_forest *forest);
+
+/* ---- measurement --------------------------------------------------------------------- */
+
+/* FMA-saturation micro-kernel: measured FP32 throughput of `device` in TFLOP/s (2 flop
+ * per FFMA) and the SM count / clock used for the nominal figure.           */
+int rt_measure_fp32_peak(int32_t device, double *tflops_measured, int32_t *sm_count,
+                         int32_t *sm_clock_khz);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */
