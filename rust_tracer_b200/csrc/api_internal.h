@@ -1,0 +1,59 @@
+// api_internal.h -- host-side state behind the opaque handles of include/rt_b200.h.
+#pragma once
+#include <vector>
+
+#include "../../include/rt_b200.h"
+#include "kernels.h"
+
+namespace rt {
+
+int fail(int code, const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);
+int convert_materials(const rt_material *in, int n, std::vector<DevMaterial> &out);
+
+// Device pools of one wavefront (kernels.h: Pools) plus the per-call scratch.
+struct Workspace {
+    Pools pools{};
+    float4 *sample_rgb = nullptr; // one colour per sample of the current band
+    long long sample_cap = 0;
+    int *rows = nullptr;          // device copy of the rendered rows
+    int rows_cap = 0;
+    unsigned char *mask = nullptr; // per-sample "re-shade" flags (filtered forest eval)
+    long long mask_cap = 0;
+    unsigned int *h_counters = nullptr; // pinned mirror of pools.counters
+    unsigned long long *exact_counter = nullptr;
+    void *out_f32 = nullptr, *out_u8 = nullptr; // device staging for host-buffer calls
+    size_t out_f32_cap = 0, out_u8_cap = 0;
+
+    int ensure_pools(long long t_cap, long long s_cap);
+    int ensure_samples(long long n);
+    int ensure_rows(int n);
+    int ensure_mask(long long n);
+    int ensure_misc();
+    void release_pools();
+    void release();
+};
+
+} // namespace rt
+
+struct rt_scene {
+    int device = 0;
+    rt::DevScene dev{};
+    std::vector<void *> allocs;
+    rt::DevMaterial *d_materials = nullptr;
+    int n_materials = 0;
+    int counts[4] = {0, 0, 0, 0}; // shapes per rt_shape_kind
+    int planes_identity = 0;
+    cudaStream_t stream = nullptr;
+    rt::Workspace ws;
+};
+
+struct rt_forest {
+    rt_scene *scene = nullptr;
+    rt::Workspace ws;   // owns the pools of the kept ray trees
+    rt::FrameParams fp{};
+    std::vector<int> tb, te; // tree-ray range of each level
+    int total_tree_rays = 0;
+    int n_samples = 0;       // = trees = pixels (spp is 1 in forest mode)
+    int width = 0, n_rows = 0;
+};

@@ -1,0 +1,667 @@
+// api_render.cu -- C ABI: Basic render, RayForest build/eval, FP32 peak (include/rt_b200.h).
+// Host orchestration of the wavefront: per band of samples, per ray-tree level:
+//   sweep(children of level k  +  shadow rays of level k-1)  ->  spawn(level k)
+// then shade from the deepest level up and resolve to RGB.
+#include <algorithm>
+#include <climits>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "api_internal.h"
+
+namespace rt {
+
+// ---- workspace --------------------------------------------------------------------------
+
+template <typename T> static int dev_alloc(T **p, size_t n, const char *what) {
+    *p = nullptr;
+    if (n == 0) return RT_OK;
+    cudaError_t e = cudaMalloc((void **)p, n * sizeof(T));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(e == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA, "cudaMalloc(%s, %zu bytes): %s", what,
+                    n * sizeof(T), cudaGetErrorString(e));
+    }
+    return RT_OK;
+}
+
+void Workspace::release_pools() {
+    Pools &p = pools;
+    cudaFree(p.t_a); cudaFree(p.t_b); cudaFree(p.t_key); cudaFree(p.t_parent); cudaFree(p.t_sbase);
+    cudaFree(p.t_crefl); cudaFree(p.t_crefr); cudaFree(p.t_root); cudaFree(p.t_hitid);
+    cudaFree(p.s_a); cudaFree(p.s_b); cudaFree(p.s_key);
+    unsigned int *c = p.counters;
+    std::memset(&p, 0, sizeof(p));
+    p.counters = c;
+}
+
+void Workspace::release() {
+    release_pools();
+    cudaFree(pools.counters); pools.counters = nullptr;
+    cudaFree(sample_rgb); sample_rgb = nullptr; sample_cap = 0;
+    cudaFree(rows); rows = nullptr; rows_cap = 0;
+    cudaFree(mask); mask = nullptr; mask_cap = 0;
+    if (h_counters) cudaFreeHost(h_counters);
+    h_counters = nullptr;
+    cudaFree(exact_counter); exact_counter = nullptr;
+    cudaFree(out_f32); cudaFree(out_u8);
+    out_f32 = out_u8 = nullptr; out_f32_cap = out_u8_cap = 0;
+}
+
+int Workspace::ensure_pools(long long t_cap, long long s_cap) {
+    if (t_cap > INT_MAX / 2 || s_cap > INT_MAX) return fail(RT_ERR_NOMEM, "ray pool of %lld tree rays exceeds the index range; lower the band size", t_cap);
+    Pools &p = pools;
+    if (p.t_cap >= t_cap && p.s_cap >= s_cap && p.t_a) return RT_OK;
+    release_pools();
+    int rc;
+    size_t t = (size_t)t_cap, s = (size_t)std::max<long long>(s_cap, 1);
+    if ((rc = dev_alloc(&p.t_a, t, "t_a")) || (rc = dev_alloc(&p.t_b, t, "t_b")) || (rc = dev_alloc(&p.t_key, t, "t_key")) ||
+        (rc = dev_alloc(&p.t_parent, t, "t_parent")) || (rc = dev_alloc(&p.t_sbase, t, "t_sbase")) ||
+        (rc = dev_alloc(&p.t_crefl, t, "t_crefl")) || (rc = dev_alloc(&p.t_crefr, t, "t_crefr")) ||
+        (rc = dev_alloc(&p.t_root, t, "t_root")) || (rc = dev_alloc(&p.t_hitid, t, "t_hitid")) ||
+        (rc = dev_alloc(&p.s_a, s, "s_a")) || (rc = dev_alloc(&p.s_b, s, "s_b")) || (rc = dev_alloc(&p.s_key, s, "s_key"))) {
+        release_pools();
+        return rc;
+    }
+    p.t_cap = (int)t_cap;
+    p.s_cap = (int)s_cap;
+    return RT_OK;
+}
+
+int Workspace::ensure_samples(long long n) {
+    if (sample_cap >= n && sample_rgb) return RT_OK;
+    cudaFree(sample_rgb);
+    sample_cap = 0;
+    int rc = dev_alloc(&sample_rgb, (size_t)n, "sample_rgb");
+    if (rc == RT_OK) sample_cap = n;
+    return rc;
+}
+
+int Workspace::ensure_rows(int n) {
+    if (rows_cap >= n && rows) return RT_OK;
+    cudaFree(rows);
+    rows_cap = 0;
+    int rc = dev_alloc(&rows, (size_t)std::max(n, 1), "rows");
+    if (rc == RT_OK) rows_cap = std::max(n, 1);
+    return rc;
+}
+
+int Workspace::ensure_mask(long long n) {
+    if (mask_cap >= n && mask) return RT_OK;
+    cudaFree(mask);
+    mask_cap = 0;
+    int rc = dev_alloc(&mask, (size_t)std::max<long long>(n, 1), "mask");
+    if (rc == RT_OK) mask_cap = std::max<long long>(n, 1);
+    return rc;
+}
+
+int Workspace::ensure_misc() {
+    int rc;
+    if (!pools.counters && (rc = dev_alloc(&pools.counters, 4, "counters"))) return rc;
+    if (!exact_counter && (rc = dev_alloc(&exact_counter, 1, "exact_counter"))) return rc;
+    if (!h_counters) {
+        cudaError_t e = cudaMallocHost((void **)&h_counters, 4 * sizeof(unsigned int) + sizeof(unsigned long long));
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
+    }
+    return RT_OK;
+}
+
+// ---- the wavefront ------------------------------------------------------------------------
+
+struct EventPool {
+    std::vector<cudaEvent_t> ev;
+    size_t used = 0;
+    cudaEvent_t get() {
+        if (used == ev.size()) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            ev.push_back(e);
+        }
+        return ev[used++];
+    }
+    ~EventPool() {
+        for (cudaEvent_t e : ev) cudaEventDestroy(e);
+    }
+};
+
+struct BandLevels {
+    std::vector<int> tb, te; // tree-ray range of level k
+    std::vector<int> sb, se; // shadow-ray range of level k
+    unsigned long long nodes = 0;
+};
+
+struct Accum {
+    unsigned long long tree_rays = 0, shadow_rays = 0, nodes = 0, exact = 0;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> sweep_spans;
+};
+
+static int env_int(const char *name, int dflt, int lo, int hi) {
+    const char *e = std::getenv(name);
+    if (!e) return dflt;
+    long v = std::atol(e);
+    if (v < lo || v > hi) return dflt;
+    return (int)v;
+}
+
+#define CK(call, what)                                        \
+    do {                                                      \
+        cudaError_t e__ = (call);                             \
+        if (e__ != cudaSuccess) return cuda_fail(e__, what);  \
+    } while (0)
+
+// Cast every ray of samples [sample0, sample0 + n): fills the pools and `lv`.
+// Returns RT_OK, an error, or +1 when a pool overflowed (caller grows it and retries).
+static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long long sample0, int n, int flags,
+                     BandLevels &lv, Accum &acc, EventPool &events) {
+    const DevScene &sc = scene->dev;
+    cudaStream_t st = scene->stream;
+    Pools &p = ws.pools;
+    const int rpt = env_int("RT_B200_RAYS_PER_THREAD", 2, 1, 4);
+    const bool audit = (flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
+    lv = BandLevels();
+
+    unsigned int init[4] = {(unsigned int)n, 0u, 0u, 0u};
+    CK(cudaMemcpyAsync(p.counters, init, sizeof(init), cudaMemcpyHostToDevice, st), "counters init");
+    launch_raygen(fp, p, sample0, n, st);
+
+    auto sweep = [&](RaySeg a, RaySeg b) {
+        if (a.n + b.n == 0) return;
+        cudaEvent_t e0 = events.get(), e1 = events.get();
+        cudaEventRecord(e0, st);
+        if (audit) launch_sweep_all_pairs(sc, a, b, ws.exact_counter, st);
+        else launch_sweep(sc, a, b, rpt, ws.exact_counter, st);
+        cudaEventRecord(e1, st);
+        acc.sweep_spans.push_back({e0, e1});
+        if (audit) acc.exact += (unsigned long long)(a.n + b.n) * (unsigned long long)sc.n_bounded;
+    };
+    auto tree_seg = [&](int b, int e) { return RaySeg{p.t_a + b, p.t_b + b, p.t_key + b, e - b}; };
+    auto shadow_seg = [&](int b, int e) { return RaySeg{p.s_a + b, p.s_b + b, p.s_key + b, e - b}; };
+
+    int tb = 0, te = n, sb = 0, se = 0; // current tree level, previous level's shadows
+    for (int k = 0; k < fp.depth; ++k) {
+        sweep(tree_seg(tb, te), shadow_seg(sb, se));
+        launch_spawn(sc, fp, p, tb, te, (k + 1 < fp.depth) ? 1 : 0, st);
+        CK(cudaMemcpyAsync(ws.h_counters, p.counters, 4 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st), "counters readback");
+        CK(cudaStreamSynchronize(st), "wavefront level");
+        if (ws.h_counters[3]) return 1; // pool overflow
+        lv.tb.push_back(tb); lv.te.push_back(te);
+        int new_te = (int)ws.h_counters[0], new_se = (int)ws.h_counters[1];
+        lv.sb.push_back(se); lv.se.push_back(new_se);
+        sb = se; se = new_se;
+        tb = te; te = new_te;
+        if (tb == te && sb == se) break; // nothing left to cast
+    }
+    sweep(RaySeg{nullptr, nullptr, nullptr, 0}, shadow_seg(sb, se)); // shadows of the last level
+    lv.nodes = ws.h_counters[2];
+    CK(cudaGetLastError(), "wavefront launch");
+    return RT_OK;
+}
+
+// Shade levels deepest-first into ws.sample_rgb (band-local sample index).
+static int shade_band(rt_scene *scene, const DevScene &sc, Workspace &ws, const FrameParams &fp, const BandLevels &lv,
+                      const unsigned char *sample_mask) {
+    for (int k = (int)lv.tb.size() - 1; k >= 0; --k)
+        launch_shade(sc, fp, ws.pools, lv.tb[k], lv.te[k], k, ws.sample_rgb, sample_mask, scene->stream);
+    CK(cudaGetLastError(), "shade launch");
+    return RT_OK;
+}
+
+static long long worst_case_tree_rays(long long n, int depth) {
+    if (depth >= 31) return LLONG_MAX / 4;
+    long long f = (1ll << depth) - 1;
+    if (f <= 0) f = 1;
+    if (n > LLONG_MAX / 4 / f) return LLONG_MAX / 4;
+    return n * f;
+}
+
+
+struct Outputs {
+    float *d_f32 = nullptr;        // device, may be null
+    unsigned char *d_u8 = nullptr; // device, may be null
+};
+
+static void fill_stats(rt_scene *scene, const Accum &acc, unsigned long long pixels, rt_stats *st) {
+    std::memset(st, 0, sizeof(*st));
+    const int *c = scene->counts;
+    unsigned long long rays = acc.tree_rays + acc.shadow_rays;
+    st->pixels = pixels;
+    st->rays = rays;
+    st->shadow_rays = acc.shadow_rays;
+    st->nodes = acc.nodes;
+    st->sphere_tests = rays * (unsigned long long)c[RT_SHAPE_SPHERE];
+    st->plane_tests = rays * (unsigned long long)c[RT_SHAPE_PLANE];
+    st->triangle_tests = rays * (unsigned long long)c[RT_SHAPE_TRIANGLE];
+    st->cube_tests = rays * (unsigned long long)c[RT_SHAPE_CUBE];
+    st->exact_tests = acc.exact + st->plane_tests;
+    // sphere 54, triangle 30, plane 47 (14 when inv is the identity), cube 33 + 12*30,
+    // node 60 + 70 L
+    double per_ray = 54.0 * c[RT_SHAPE_SPHERE] + 30.0 * c[RT_SHAPE_TRIANGLE] + 393.0 * c[RT_SHAPE_CUBE] +
+                     47.0 * (c[RT_SHAPE_PLANE] - scene->planes_identity) + 14.0 * scene->planes_identity;
+    st->algorithmic_flops = (double)rays * per_ray + (double)acc.nodes * (60.0 + 70.0 * scene->dev.n_lights);
+}
+
+static int check_params(const rt_scene *scene, const rt_camera *cam, const rt_render_params *pr) {
+    if (!scene || !cam || !pr) return fail(RT_ERR_INVALID, "null argument");
+    if (cam->x_res <= 0 || cam->y_res <= 0) return fail(RT_ERR_INVALID, "resolution %dx%d", cam->x_res, cam->y_res);
+    if (pr->depth < 0 || pr->depth > 30) return fail(RT_ERR_INVALID, "depth %d not in 0..30", pr->depth);
+    if (pr->spp != 1 && pr->spp != 4) return fail(RT_ERR_UNSUPPORTED, "spp must be 1 or 4, got %d", pr->spp);
+    if (pr->world < 1 || pr->rank < 0 || pr->rank >= pr->world || pr->tile_rows < 1)
+        return fail(RT_ERR_INVALID, "bad row tiling rank %d world %d tile_rows %d", pr->rank, pr->world, pr->tile_rows);
+    return RT_OK;
+}
+
+static FrameParams frame_params(const rt_camera *cam, const rt_render_params *pr, const int *d_rows, int n_rows) {
+    FrameParams fp;
+    fp.cam_ox = cam->origin[0]; fp.cam_oy = cam->origin[1]; fp.cam_oz = cam->origin[2];
+    fp.x_min = cam->x_min; fp.x_max = cam->x_max; fp.y_min = cam->y_min; fp.y_max = cam->y_max;
+    fp.x_res = cam->x_res; fp.y_res = cam->y_res;
+    fp.depth = pr->depth; fp.spp = pr->spp; fp.seed = pr->seed;
+    fp.rows = d_rows; fp.n_rows = n_rows;
+    fp.forest_shading = (pr->flags & RT_FLAG_FOREST_SHADING) ? 1 : 0;
+    return fp;
+}
+
+static int upload_rows(rt_scene *scene, Workspace &ws, const rt_camera *cam, const rt_render_params *pr,
+                       std::vector<int> &rows) {
+    rows.clear();
+    for (int v = 0; v < cam->y_res; ++v)
+        if ((v / pr->tile_rows) % pr->world == pr->rank) rows.push_back(v);
+    int rc = ws.ensure_rows((int)rows.size());
+    if (rc != RT_OK) return rc;
+    if (!rows.empty())
+        CK(cudaMemcpyAsync(ws.rows, rows.data(), rows.size() * sizeof(int), cudaMemcpyHostToDevice, scene->stream), "rows upload");
+    return RT_OK;
+}
+
+// Grow-and-retry wrapper around cast_band.
+static int cast_band_sized(rt_scene *scene, Workspace &ws, const FrameParams &fp, long long sample0, int n, int flags,
+                           BandLevels &lv, Accum &acc, EventPool &events) {
+    const long long worst = worst_case_tree_rays(n, std::max(fp.depth, 1));
+    const int npl = std::max(scene->dev.n_point_lights, 0);
+    long long t_cap = std::max<long long>(ws.pools.t_cap, std::min<long long>(worst, std::max<long long>((long long)n * 3, 1 << 16)));
+    for (;;) {
+        int rc = ws.ensure_pools(t_cap, t_cap * npl);
+        if (rc != RT_OK) return rc;
+        rc = cast_band(scene, ws, fp, sample0, n, flags, lv, acc, events);
+        if (rc <= 0) return rc;
+        if (t_cap >= worst) return fail(RT_ERR_INTERNAL, "ray pool overflow at the worst-case size");
+        t_cap = std::min(worst, t_cap * 2);
+    }
+}
+
+static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_params *pr, Outputs out, rt_stats *stats) {
+    int rc = check_params(scene, cam, pr);
+    if (rc != RT_OK) return rc;
+    CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    Workspace &ws = scene->ws;
+    if ((rc = ws.ensure_misc()) != RT_OK) return rc;
+    cudaStream_t st = scene->stream;
+    std::vector<int> rows;
+    if ((rc = upload_rows(scene, ws, cam, pr, rows)) != RT_OK) return rc;
+    const long long n_pixels = (long long)rows.size() * cam->x_res;
+    const long long n_samples = n_pixels * pr->spp;
+    FrameParams fp = frame_params(cam, pr, ws.rows, (int)rows.size());
+
+    EventPool events;
+    cudaEvent_t ev0 = events.get(), ev1 = events.get();
+    CK(cudaMemsetAsync(ws.exact_counter, 0, sizeof(unsigned long long), st), "exact counter");
+    cudaEventRecord(ev0, st);
+
+    Accum acc;
+    long long band = env_int("RT_B200_BAND_SAMPLES", 1 << 22, 1 << 10, 1 << 28);
+    if (n_samples > 0) {
+        long long nb = (n_samples + band - 1) / band;
+        band = (n_samples + nb - 1) / nb;
+        band = (band + pr->spp - 1) / pr->spp * pr->spp; // whole pixels per band
+    }
+    if ((rc = ws.ensure_samples(std::min(band, std::max<long long>(n_samples, 1)))) != RT_OK) return rc;
+    for (long long s0 = 0; s0 < n_samples; s0 += band) {
+        int n = (int)std::min(band, n_samples - s0);
+        if (fp.depth == 0) {
+            CK(cudaMemsetAsync(ws.sample_rgb, 0, (size_t)n * sizeof(float4), st), "black frame"); // render.rs:43-45
+        } else {
+            BandLevels lv;
+            if ((rc = cast_band_sized(scene, ws, fp, s0, n, pr->flags, lv, acc, events)) != RT_OK) return rc;
+            acc.tree_rays += (unsigned long long)(lv.te.empty() ? 0 : lv.te.back());
+            acc.shadow_rays += (unsigned long long)(lv.se.empty() ? 0 : lv.se.back());
+            acc.nodes += lv.nodes;
+            if ((rc = shade_band(scene, scene->dev, ws, fp, lv, nullptr)) != RT_OK) return rc;
+        }
+        launch_resolve(ws.sample_rgb, s0 / pr->spp, n / pr->spp, pr->spp, out.d_f32, out.d_u8, nullptr, st);
+    }
+    cudaEventRecord(ev1, st);
+    CK(cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
+    CK(cudaStreamSynchronize(st), "render");
+    CK(cudaGetLastError(), "render");
+    if (!(pr->flags & RT_FLAG_AUDIT_ALL_PAIRS)) std::memcpy(&acc.exact, ws.h_counters + 4, sizeof(unsigned long long));
+    if (stats) {
+        fill_stats(scene, acc, (unsigned long long)n_pixels, stats);
+        float ms = 0.f, sweep = 0.f;
+        cudaEventElapsedTime(&ms, ev0, ev1);
+        for (auto &sp : acc.sweep_spans) {
+            float t = 0.f;
+            cudaEventElapsedTime(&t, sp.first, sp.second);
+            sweep += t;
+        }
+        stats->total_ms = ms;
+        stats->sweep_ms = sweep;
+        stats->shade_ms = ms - sweep;
+    }
+    return RT_OK;
+}
+
+} // namespace rt
+
+using namespace rt;
+
+extern "C" {
+
+int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_render_params *params, void *d_rgb_f32,
+                     void *d_rgb_u8, rt_stats *stats) {
+    Outputs out;
+    out.d_f32 = (float *)d_rgb_f32;
+    out.d_u8 = (unsigned char *)d_rgb_u8;
+    return render_impl(scene, camera, params, out, stats);
+}
+
+int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *params, float *rgb_f32,
+              uint8_t *rgb_u8, rt_stats *stats) {
+    int rc = check_params(scene, camera, params);
+    if (rc != RT_OK) return rc;
+    CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    Workspace &ws = scene->ws;
+    int32_t n_rows = rt_tile_rows_for_rank(camera->y_res, params->rank, params->world, params->tile_rows, nullptr, 0);
+    size_t n_ch = (size_t)n_rows * (size_t)camera->x_res * 3;
+    if (rgb_f32 && ws.out_f32_cap < n_ch * sizeof(float)) {
+        cudaFree(ws.out_f32);
+        ws.out_f32 = nullptr; ws.out_f32_cap = 0;
+        float *p;
+        if ((rc = dev_alloc(&p, n_ch, "out_f32")) != RT_OK) return rc;
+        ws.out_f32 = p; ws.out_f32_cap = n_ch * sizeof(float);
+    }
+    if (rgb_u8 && ws.out_u8_cap < n_ch) {
+        cudaFree(ws.out_u8);
+        ws.out_u8 = nullptr; ws.out_u8_cap = 0;
+        unsigned char *p;
+        if ((rc = dev_alloc(&p, n_ch, "out_u8")) != RT_OK) return rc;
+        ws.out_u8 = p; ws.out_u8_cap = n_ch;
+    }
+    Outputs out;
+    out.d_f32 = rgb_f32 ? (float *)ws.out_f32 : nullptr;
+    out.d_u8 = rgb_u8 ? (unsigned char *)ws.out_u8 : nullptr;
+    if ((rc = render_impl(scene, camera, params, out, stats)) != RT_OK) return rc;
+    if (rgb_f32 && n_ch) CK(cudaMemcpy(rgb_f32, ws.out_f32, n_ch * sizeof(float), cudaMemcpyDeviceToHost), "D2H rgb_f32");
+    if (rgb_u8 && n_ch) CK(cudaMemcpy(rgb_u8, ws.out_u8, n_ch, cudaMemcpyDeviceToHost), "D2H rgb_u8");
+    return RT_OK;
+}
+
+// ---- RayForest ------------------------------------------------------------------------------
+
+int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_params *params, rt_forest **out,
+                    rt_stats *stats) {
+    if (!out) return fail(RT_ERR_INVALID, "null argument");
+    *out = nullptr;
+    int rc = check_params(scene, camera, params);
+    if (rc != RT_OK) return rc;
+    if (params->spp != 1) return fail(RT_ERR_UNSUPPORTED, "the ray forest keeps one tree per pixel: spp must be 1");
+    if (params->depth < 1) return fail(RT_ERR_INVALID, "forest depth must be >= 1");
+    CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    rt_forest *f = new (std::nothrow) rt_forest();
+    if (!f) return fail(RT_ERR_NOMEM, "out of host memory");
+    f->scene = scene;
+    Workspace &ws = f->ws;
+    std::vector<int> rows;
+    if ((rc = ws.ensure_misc()) != RT_OK || (rc = upload_rows(scene, ws, camera, params, rows)) != RT_OK) {
+        rt_forest_destroy(f);
+        return rc;
+    }
+    long long n = (long long)rows.size() * camera->x_res;
+    if (n > (1 << 28)) {
+        rt_forest_destroy(f);
+        return fail(RT_ERR_NOMEM, "forest of %lld trees does not fit one device-resident pool", n);
+    }
+    rt_render_params pr = *params;
+    pr.flags |= RT_FLAG_FOREST_SHADING;
+    f->fp = frame_params(camera, &pr, ws.rows, (int)rows.size());
+    f->n_samples = (int)n;
+    f->width = camera->x_res;
+    f->n_rows = (int)rows.size();
+    EventPool events;
+    cudaEvent_t ev0 = events.get(), ev1 = events.get();
+    cudaStream_t st = scene->stream;
+    cudaMemsetAsync(ws.exact_counter, 0, sizeof(unsigned long long), st);
+    cudaEventRecord(ev0, st);
+    Accum acc;
+    BandLevels lv;
+    if (n > 0 && (rc = cast_band_sized(scene, ws, f->fp, 0, (int)n, pr.flags, lv, acc, events)) != RT_OK) {
+        rt_forest_destroy(f);
+        return rc;
+    }
+    cudaEventRecord(ev1, st);
+    cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+        rt_forest_destroy(f);
+        return cuda_fail(e, "forest build");
+    }
+    f->tb = lv.tb;
+    f->te = lv.te;
+    f->total_tree_rays = lv.te.empty() ? 0 : lv.te.back();
+    if (stats) {
+        acc.tree_rays = (unsigned long long)f->total_tree_rays;
+        acc.shadow_rays = lv.se.empty() ? 0 : (unsigned long long)lv.se.back();
+        acc.nodes = lv.nodes;
+        if (!(pr.flags & RT_FLAG_AUDIT_ALL_PAIRS)) std::memcpy(&acc.exact, ws.h_counters + 4, sizeof(unsigned long long));
+        fill_stats(scene, acc, (unsigned long long)n, stats);
+        float ms = 0.f, sweep = 0.f;
+        cudaEventElapsedTime(&ms, ev0, ev1);
+        for (auto &sp : acc.sweep_spans) {
+            float t = 0.f;
+            cudaEventElapsedTime(&t, sp.first, sp.second);
+            sweep += t;
+        }
+        stats->total_ms = ms; stats->sweep_ms = sweep; stats->shade_ms = ms - sweep;
+    }
+    *out = f;
+    return RT_OK;
+}
+
+void rt_forest_destroy(rt_forest *forest) {
+    if (!forest) return;
+    if (forest->scene) cudaSetDevice(forest->scene->device);
+    forest->ws.release();
+    delete forest;
+}
+
+// shared by rt_forest_eval / rt_forest_eval_filtered
+static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *ids, int32_t n_ids, float *rgb_f32,
+                            uint8_t *rgb_u8, uint64_t *n_evaluated, rt_stats *stats) {
+    if (!f) return fail(RT_ERR_INVALID, "null forest");
+    if (ids == nullptr && n_ids != 0) return fail(RT_ERR_INVALID, "null id list");
+    rt_scene *scene = f->scene;
+    CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    Workspace &ws = f->ws;
+    cudaStream_t st = scene->stream;
+    const int n = f->n_samples;
+    const bool filtered = ids != nullptr;
+    int rc;
+    if ((rc = ws.ensure_samples(std::max(n, 1))) != RT_OK) return rc;
+    DevScene sc = scene->dev; // current materials; ambient as passed by the caller
+    if (ambient) { sc.amb_r = ambient[0]; sc.amb_g = ambient[1]; sc.amb_b = ambient[2]; }
+    EventPool events;
+    cudaEvent_t ev0 = events.get(), ev1 = events.get();
+    cudaEventRecord(ev0, st);
+    const unsigned char *mask = nullptr;
+    uint64_t evaluated = (uint64_t)n;
+    int *d_ids = nullptr;
+    if (filtered) {
+        if ((rc = ws.ensure_mask(n)) != RT_OK) return rc;
+        CK(cudaMemsetAsync(ws.mask, 0, (size_t)std::max(n, 1), st), "mask clear");
+        if (n_ids > 0) {
+            CK(cudaMalloc((void **)&d_ids, sizeof(int) * n_ids), "cudaMalloc(ids)");
+            CK(cudaMemcpyAsync(d_ids, ids, sizeof(int) * n_ids, cudaMemcpyHostToDevice, st), "ids upload");
+            launch_forest_mark(ws.pools, f->total_tree_rays, d_ids, n_ids, ws.mask, st);
+        }
+        mask = ws.mask;
+    }
+    BandLevels lv;
+    lv.tb = f->tb;
+    lv.te = f->te;
+    if ((rc = shade_band(scene, sc, ws, f->fp, lv, mask)) != RT_OK) return rc;
+    size_t n_ch = (size_t)n * 3;
+    float *d_f32 = nullptr;
+    unsigned char *d_u8 = nullptr;
+    if (rgb_f32 && n_ch) {
+        CK(cudaMalloc((void **)&d_f32, n_ch * sizeof(float)), "cudaMalloc(out)");
+        if (filtered) CK(cudaMemcpyAsync(d_f32, rgb_f32, n_ch * sizeof(float), cudaMemcpyHostToDevice, st), "H2D inout");
+    }
+    if (rgb_u8 && n_ch) {
+        CK(cudaMalloc((void **)&d_u8, n_ch), "cudaMalloc(out)");
+        if (filtered) CK(cudaMemcpyAsync(d_u8, rgb_u8, n_ch, cudaMemcpyHostToDevice, st), "H2D inout");
+    }
+    launch_resolve(ws.sample_rgb, 0, n, 1, d_f32, d_u8, mask, st);
+    cudaEventRecord(ev1, st);
+    if (d_f32) CK(cudaMemcpyAsync(rgb_f32, d_f32, n_ch * sizeof(float), cudaMemcpyDeviceToHost, st), "D2H");
+    if (d_u8) CK(cudaMemcpyAsync(rgb_u8, d_u8, n_ch, cudaMemcpyDeviceToHost, st), "D2H");
+    std::vector<unsigned char> hmask;
+    if (filtered && n > 0) {
+        hmask.resize(n);
+        CK(cudaMemcpyAsync(hmask.data(), ws.mask, (size_t)n, cudaMemcpyDeviceToHost, st), "D2H mask");
+    }
+    CK(cudaStreamSynchronize(st), "forest eval");
+    cudaFree(d_f32); cudaFree(d_u8); cudaFree(d_ids);
+    CK(cudaGetLastError(), "forest eval");
+    if (filtered) {
+        evaluated = 0;
+        for (unsigned char m : hmask) evaluated += m ? 1 : 0;
+    }
+    if (n_evaluated) *n_evaluated = evaluated;
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        stats->pixels = evaluated;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ev0, ev1);
+        stats->total_ms = ms;
+        stats->shade_ms = ms;
+    }
+    return RT_OK;
+}
+
+int rt_forest_eval(rt_forest *forest, const float *ambient, float *rgb_f32, uint8_t *rgb_u8, rt_stats *stats) {
+    return forest_eval_impl(forest, ambient, nullptr, 0, rgb_f32, rgb_u8, nullptr, stats);
+}
+
+int rt_forest_eval_filtered(rt_forest *forest, const float *ambient, const int32_t *mutated_ids, int32_t n_ids,
+                            float *rgb_f32_inout, uint8_t *rgb_u8_inout, uint64_t *n_evaluated, rt_stats *stats) {
+    static const int32_t none = 0;
+    if (n_ids < 0) return fail(RT_ERR_INVALID, "negative id count");
+    return forest_eval_impl(forest, ambient, mutated_ids ? mutated_ids : &none, mutated_ids ? n_ids : 0, rgb_f32_inout,
+                            rgb_u8_inout, n_evaluated, stats);
+}
+
+int rt_forest_size(rt_forest *forest, uint64_t *out) { // RayForest::size (render_tree.rs:62-64)
+    if (!forest || !out) return fail(RT_ERR_INVALID, "null argument");
+    *out = (uint64_t)forest->n_samples;
+    return RT_OK;
+}
+
+static int forest_tree_sizes(rt_forest *f, std::vector<int> &sizes) {
+    rt_scene *scene = f->scene;
+    CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    const int n = f->n_samples;
+    sizes.assign(n, 0);
+    if (n == 0) return RT_OK;
+    int *d = nullptr;
+    CK(cudaMalloc((void **)&d, sizeof(int) * n), "cudaMalloc(sizes)");
+    cudaMemsetAsync(d, 0, sizeof(int) * n, scene->stream);
+    launch_forest_sizes(f->ws.pools, f->total_tree_rays, d, scene->stream);
+    cudaError_t e = cudaMemcpyAsync(sizes.data(), d, sizeof(int) * n, cudaMemcpyDeviceToHost, scene->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(scene->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return cuda_fail(e, "forest sizes");
+    return RT_OK;
+}
+
+int rt_forest_get_stats(rt_forest *forest, rt_forest_stats *out) { // RayForest::stats (render_tree.rs:73-93)
+    if (!forest || !out) return fail(RT_ERR_INVALID, "null argument");
+    std::vector<int> sizes;
+    int rc = forest_tree_sizes(forest, sizes);
+    if (rc != RT_OK) return rc;
+    if (sizes.empty()) return fail(RT_ERR_INVALID, "empty forest"); // the reference unwraps max() of an empty list
+    std::sort(sizes.begin(), sizes.end());
+    size_t n = sizes.size();
+    uint64_t total = 0;
+    for (int s : sizes) total += (uint64_t)s;
+    out->num_trees = n;
+    out->num_intersections = total;
+    out->smallest_tree = (uint64_t)sizes.front();
+    out->largest_tree = (uint64_t)sizes.back();
+    out->median = (uint64_t)sizes[n / 2];
+    out->p90 = (uint64_t)sizes[(size_t)(0.9f * (float)n)];
+    out->p95 = (uint64_t)sizes[(size_t)(0.95f * (float)n)];
+    out->p99 = (uint64_t)sizes[(size_t)(0.99f * (float)n)];
+    return RT_OK;
+}
+
+int rt_forest_trees_with(rt_forest *forest, int32_t shape_id, uint64_t *out) { // render_tree.rs:68-70
+    if (!forest || !out) return fail(RT_ERR_INVALID, "null argument");
+    rt_scene *scene = forest->scene;
+    CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    Workspace &ws = forest->ws;
+    const int n = forest->n_samples;
+    int rc = ws.ensure_mask(n);
+    if (rc != RT_OK) return rc;
+    int *d_id = nullptr;
+    CK(cudaMalloc((void **)&d_id, sizeof(int)), "cudaMalloc(id)");
+    cudaMemcpyAsync(d_id, &shape_id, sizeof(int), cudaMemcpyHostToDevice, scene->stream);
+    cudaMemsetAsync(ws.mask, 0, (size_t)std::max(n, 1), scene->stream);
+    launch_forest_mark(ws.pools, forest->total_tree_rays, d_id, 1, ws.mask, scene->stream);
+    std::vector<unsigned char> h(std::max(n, 1));
+    cudaError_t e = cudaMemcpyAsync(h.data(), ws.mask, (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, scene->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(scene->stream);
+    cudaFree(d_id);
+    if (e != cudaSuccess) return cuda_fail(e, "trees_with");
+    uint64_t c = 0;
+    for (int i = 0; i < n; ++i) c += h[i] ? 1 : 0;
+    *out = c;
+    return RT_OK;
+}
+
+int rt_measure_fp32_peak(int32_t device, double *tflops_measured, int32_t *sm_count, int32_t *sm_clock_khz) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    if (device < 0 || device >= ndev) return fail(RT_ERR_CUDA, "CUDA device %d not present", device);
+    CK(cudaSetDevice(device), "cudaSetDevice");
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+    int clock_khz = 0;
+    cudaDeviceGetAttribute(&clock_khz, cudaDevAttrClockRate, device);
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (sm_clock_khz) *sm_clock_khz = clock_khz;
+    const int blocks = prop.multiProcessorCount * 8;
+    float *sink = nullptr;
+    CK(cudaMalloc((void **)&sink, (size_t)blocks * 256 * sizeof(float)), "cudaMalloc(sink)");
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) { // first reps warm up clocks; keep the best
+        cudaEventRecord(e0, 0);
+        double flops = launch_fp32_peak(blocks, 4096, sink, 0);
+        cudaEventRecord(e1, 0);
+        if ((e = cudaEventSynchronize(e1)) != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (ms > 0.f) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(sink);
+    if (e != cudaSuccess) return cuda_fail(e, "fp32 peak kernel");
+    if (tflops_measured) *tflops_measured = best;
+    return RT_OK;
+}
+
+} // extern "C"

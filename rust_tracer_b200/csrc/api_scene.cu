@@ -1,0 +1,365 @@
+// api_scene.cu -- C ABI: library, scene upload, material update (include/rt_b200.h).
+// Turns the reference-shaped scene description (array of shapes in add order) into the
+// structure-of-arrays device tables of scene_dev.cuh, and builds the conservative
+// bounding spheres the sweep filters with.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "api_internal.h"
+
+namespace rt {
+
+static thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    return fail(RT_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+// ---- bounding spheres (host, double precision) ------------------------------------------
+
+static bool inv3(const double a[9], double out[9]) {
+    double c00 = a[4] * a[8] - a[5] * a[7], c01 = a[5] * a[6] - a[3] * a[8], c02 = a[3] * a[7] - a[4] * a[6];
+    double det = a[0] * c00 + a[1] * c01 + a[2] * c02;
+    if (!(std::fabs(det) > 0.0) || !std::isfinite(det)) return false;
+    double id = 1.0 / det;
+    out[0] = c00 * id; out[1] = (a[2] * a[7] - a[1] * a[8]) * id; out[2] = (a[1] * a[5] - a[2] * a[4]) * id;
+    out[3] = c01 * id; out[4] = (a[0] * a[8] - a[2] * a[6]) * id; out[5] = (a[2] * a[3] - a[0] * a[5]) * id;
+    out[6] = c02 * id; out[7] = (a[1] * a[6] - a[0] * a[7]) * id; out[8] = (a[0] * a[4] - a[1] * a[3]) * id;
+    return true;
+}
+
+// largest singular value of a 3x3 matrix = sqrt(largest eigenvalue of M^T M)
+static double sigma_max3(const double m[9]) {
+    double s[3][3];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) s[i][j] = m[0 * 3 + i] * m[0 * 3 + j] + m[1 * 3 + i] * m[1 * 3 + j] + m[2 * 3 + i] * m[2 * 3 + j];
+    double p1 = s[0][1] * s[0][1] + s[0][2] * s[0][2] + s[1][2] * s[1][2];
+    double q = (s[0][0] + s[1][1] + s[2][2]) / 3.0;
+    double lam;
+    if (p1 <= 1e-300) {
+        lam = std::max(s[0][0], std::max(s[1][1], s[2][2]));
+    } else {
+        double p2 = (s[0][0] - q) * (s[0][0] - q) + (s[1][1] - q) * (s[1][1] - q) + (s[2][2] - q) * (s[2][2] - q) + 2.0 * p1;
+        double p = std::sqrt(p2 / 6.0);
+        double b[3][3];
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) b[i][j] = (s[i][j] - (i == j ? q : 0.0)) / p;
+        double detb = b[0][0] * (b[1][1] * b[2][2] - b[1][2] * b[2][1]) - b[0][1] * (b[1][0] * b[2][2] - b[1][2] * b[2][0]) +
+                      b[0][2] * (b[1][0] * b[2][1] - b[1][1] * b[2][0]);
+        double r = std::min(1.0, std::max(-1.0, detb / 2.0));
+        lam = q + 2.0 * p * std::cos(std::acos(r) / 3.0);
+    }
+    return std::sqrt(std::max(lam, 0.0));
+}
+
+// Object->world map of a shape whose exact test moves the ray by inv (3x4): centre and
+// the largest stretch of a unit vector.
+static bool world_extent(const float *inv16, double centre[3], double &stretch) {
+    double a[9] = {inv16[0], inv16[1], inv16[2], inv16[4], inv16[5], inv16[6], inv16[8], inv16[9], inv16[10]};
+    double t[3] = {inv16[3], inv16[7], inv16[11]};
+    double f[9];
+    if (!inv3(a, f)) return false;
+    for (int i = 0; i < 3; ++i) centre[i] = -(f[i * 3 + 0] * t[0] + f[i * 3 + 1] * t[1] + f[i * 3 + 2] * t[2]);
+    stretch = sigma_max3(f);
+    return std::isfinite(stretch) && std::isfinite(centre[0]) && std::isfinite(centre[1]) && std::isfinite(centre[2]);
+}
+
+static float round_up_f32(double x) {
+    float f = (float)x;
+    if ((double)f < x) f = std::nextafter(f, INFINITY);
+    return f;
+}
+
+static float tri_bound_scale() {
+    const char *e = std::getenv("RT_B200_TRI_BOUND_SCALE");
+    if (e) {
+        double v = std::atof(e);
+        if (v >= 1.0 && v <= 64.0) return (float)v;
+    }
+    return 1.5f;
+}
+
+// (cx, cy, cz, R^2): R = r * scale + absolute slack for the reference's own rounding of
+// the object-space ray ("filter margins")
+static float4 make_bound(const double c[3], double r, double scale) {
+    double cn = std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
+    double rf = r * scale + 64.0 * 1.1920929e-07 * (cn + r);
+    float4 b;
+    b.x = (float)c[0]; b.y = (float)c[1]; b.z = (float)c[2];
+    // the centre is rounded to f32: cover the displacement
+    double dx = c[0] - b.x, dy = c[1] - b.y, dz = c[2] - b.z;
+    rf += std::sqrt(dx * dx + dy * dy + dz * dz);
+    b.w = round_up_f32(rf * rf * (1.0 + 1e-6));
+    return b;
+}
+
+template <typename T> static int upload(rt_scene *s, const std::vector<T> &host, const T **dev) {
+    *dev = nullptr;
+    if (host.empty()) return RT_OK;
+    void *d = nullptr;
+    cudaError_t e = cudaMalloc(&d, host.size() * sizeof(T));
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(scene table)");
+    s->allocs.push_back(d);
+    e = cudaMemcpy(d, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(scene table)");
+    *dev = (const T *)d;
+    return RT_OK;
+}
+
+static int convert_colorfn(const rt_colorfn &in, DevColorFn &out) {
+    if (in.kind != RT_COLOR_CONST && in.kind != RT_COLOR_CHECKERBOARD)
+        return fail(RT_ERR_UNSUPPORTED, "texture function kind %d is not a device texture (only CONST, CHECKERBOARD)", in.kind);
+    out.kind = in.kind;
+    out.r = in.rgb[0]; out.g = in.rgb[1]; out.b = in.rgb[2];
+    return RT_OK;
+}
+
+int convert_materials(const rt_material *in, int n, std::vector<DevMaterial> &out) {
+    out.resize(n);
+    for (int i = 0; i < n; ++i) {
+        int rc;
+        if ((rc = convert_colorfn(in[i].ambient, out[i].ambient)) != RT_OK) return rc;
+        if ((rc = convert_colorfn(in[i].diffuse, out[i].diffuse)) != RT_OK) return rc;
+        if ((rc = convert_colorfn(in[i].specular, out[i].specular)) != RT_OK) return rc;
+        if (in[i].kind != RT_MATERIAL_PHONG && in[i].kind != RT_MATERIAL_TEXTURE_PHONG)
+            return fail(RT_ERR_INVALID, "material %d: unknown kind %d", i, in[i].kind);
+        out[i].power = in[i].power;
+        out[i].reflectivity = in[i].reflectivity;
+        out[i].refraction_index = in[i].refraction_index;
+        out[i].kind = in[i].kind;
+    }
+    return RT_OK;
+}
+
+// Triangle::new's normal (reference src/scene/triangle.rs:25-29), host f32, no FMA: this
+// TU is built with -ffp-contract=off (Makefile).
+static void tri_normal(const float *a, const float *b, const float *c, float *n) {
+    float e0[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]};
+    float e1[3] = {c[0] - b[0], c[1] - b[1], c[2] - b[2]};
+    float x = e0[1] * e1[2] - e0[2] * e1[1];
+    float y = e0[2] * e1[0] - e0[0] * e1[2];
+    float z = e0[0] * e1[1] - e0[1] * e1[0];
+    float len = std::sqrt(x * x + y * y + z * z);
+    n[0] = x / len; n[1] = y / len; n[2] = z / len;
+}
+
+static void pack_tri(const float *v0, const float *v1, const float *v2, const float *n, float4 *out) {
+    out[0] = make_float4(v0[0], v0[1], v0[2], v1[0]);
+    out[1] = make_float4(v1[1], v1[2], v2[0], v2[1]);
+    out[2] = make_float4(v2[2], n[0], n[1], n[2]);
+}
+
+// Cube::new (reference src/scene/cube.rs:21-77): the 12 triangles in add order
+static void cube_tris(std::vector<float4> &out) {
+    const float V[8][3] = {{0.5f, 0.5f, -0.5f}, {0.5f, -0.5f, -0.5f}, {-0.5f, -0.5f, -0.5f}, {-0.5f, 0.5f, -0.5f},
+                           {0.5f, 0.5f, 0.5f},  {-0.5f, 0.5f, 0.5f},  {-0.5f, -0.5f, 0.5f},  {0.5f, -0.5f, 0.5f}};
+    const int T[12][3] = {{1, 2, 3}, {0, 1, 3}, {7, 5, 4}, {5, 7, 6}, {0, 4, 7}, {7, 1, 0},
+                          {5, 3, 6}, {6, 3, 2}, {5, 4, 0}, {0, 3, 5}, {1, 7, 6}, {6, 2, 1}};
+    out.resize(36);
+    for (int k = 0; k < 12; ++k) {
+        float n[3];
+        tri_normal(V[T[k][0]], V[T[k][1]], V[T[k][2]], n);
+        pack_tri(V[T[k][0]], V[T[k][1]], V[T[k][2]], n, &out[3 * k]);
+    }
+}
+
+} // namespace rt
+
+using namespace rt;
+
+extern "C" {
+
+int rt_abi_version(void) { return RT_B200_ABI_VERSION; }
+const char *rt_last_error(void) { return g_err; }
+
+int rt_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    return n;
+}
+
+void rt_camera_default(int32_t x_res, int32_t y_res, rt_camera *out) {
+    out->origin[0] = 0.f; out->origin[1] = 0.f; out->origin[2] = -8.f;
+    out->x_min = -3.f; out->x_max = 3.f; out->y_min = -3.f; out->y_max = 3.f;
+    out->x_res = x_res; out->y_res = y_res;
+}
+
+int32_t rt_tile_rows_for_rank(int32_t height, int32_t rank, int32_t world, int32_t tile_rows, int32_t *rows,
+                              int32_t cap) {
+    if (height < 0 || world < 1 || rank < 0 || rank >= world || tile_rows < 1) return fail(RT_ERR_INVALID, "bad tiling");
+    int32_t n = 0;
+    for (int32_t v = 0; v < height; ++v)
+        if ((v / tile_rows) % world == rank) {
+            if (rows && n < cap) rows[n] = v;
+            ++n;
+        }
+    return n;
+}
+
+int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
+    if (!desc || !out) return fail(RT_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (desc->n_shapes < 0 || desc->n_materials < 0 || desc->n_lights < 0 || (desc->n_shapes && !desc->shapes) ||
+        (desc->n_materials && !desc->materials) || (desc->n_lights && !desc->lights))
+        return fail(RT_ERR_INVALID, "malformed scene description");
+    if (desc->n_shapes >= (1 << 24)) return fail(RT_ERR_UNSUPPORTED, "more than 2^24 shapes");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount (no CPU fallback exists)");
+    if (device < 0 || device >= ndev) return fail(RT_ERR_CUDA, "CUDA device %d not present (%d devices)", device, ndev);
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+
+    const int n = desc->n_shapes;
+    std::vector<int4> meta(n);
+    std::vector<float4> geom(3 * (size_t)n);
+    std::vector<int> plane_shape;
+    std::vector<float4> plane_data;
+    struct B { float4 b; int shape; int kind; };
+    std::vector<B> bounds;
+    const float tri_scale = tri_bound_scale();
+    int counts[4] = {0, 0, 0, 0}, planes_identity = 0, first_nan = -1;
+
+    for (int i = 0; i < n; ++i) {
+        const rt_shape &s = desc->shapes[i];
+        if (s.material < 0 || s.material >= desc->n_materials)
+            return fail(RT_ERR_INVALID, "shape %d: material %d out of range", i, s.material);
+        if (s.kind < 0 || s.kind > 3) return fail(RT_ERR_INVALID, "shape %d: unknown kind %d", i, s.kind);
+        counts[s.kind]++;
+        meta[i] = make_int4(s.kind, s.material, -1, 0);
+        const float *iv = s.inv_transform;
+        float4 r0 = make_float4(iv[0], iv[1], iv[2], iv[3]), r1 = make_float4(iv[4], iv[5], iv[6], iv[7]),
+               r2 = make_float4(iv[8], iv[9], iv[10], iv[11]);
+        double c[3], stretch;
+        switch (s.kind) {
+        case RT_SHAPE_SPHERE:
+        case RT_SHAPE_CUBE:
+            geom[3 * i] = r0; geom[3 * i + 1] = r1; geom[3 * i + 2] = r2;
+            if (!world_extent(iv, c, stretch)) return fail(RT_ERR_INVALID, "shape %d: singular inverse transform", i);
+            if (s.kind == RT_SHAPE_SPHERE) bounds.push_back({make_bound(c, stretch, 1.0 + 1e-4), i, s.kind});
+            else bounds.push_back({make_bound(c, stretch * 0.8660254037844387, tri_scale), i, s.kind});
+            if (first_nan < 0) first_nan = i;
+            break;
+        case RT_SHAPE_TRIANGLE: {
+            const float *p = s.p;
+            pack_tri(p, p + 3, p + 6, p + 9, &geom[3 * i]);
+            for (int k = 0; k < 3; ++k) c[k] = ((double)p[k] + p[3 + k] + p[6 + k]) / 3.0;
+            double r = 0.0;
+            for (int v = 0; v < 3; ++v) {
+                double dx = p[3 * v] - c[0], dy = p[3 * v + 1] - c[1], dz = p[3 * v + 2] - c[2];
+                r = std::max(r, std::sqrt(dx * dx + dy * dy + dz * dz));
+            }
+            if (!std::isfinite(r)) return fail(RT_ERR_INVALID, "shape %d: non-finite triangle", i);
+            bounds.push_back({make_bound(c, r, tri_scale), i, s.kind});
+            if (first_nan < 0) first_nan = i;
+            break;
+        }
+        case RT_SHAPE_PLANE: {
+            geom[3 * i] = r0; geom[3 * i + 1] = r1; geom[3 * i + 2] = r2;
+            meta[i].z = (int)plane_shape.size();
+            plane_shape.push_back(i);
+            const float *p = s.p, *f = s.transform;
+            plane_data.push_back(make_float4(p[0], p[1], p[2], 0.f));
+            plane_data.push_back(make_float4(p[3], p[4], p[5], 0.f));
+            plane_data.push_back(make_float4(p[6], p[7], p[8], 0.f));
+            plane_data.push_back(make_float4(p[9], p[10], p[11], 0.f));
+            plane_data.push_back(make_float4(f[0], f[1], f[2], 0.f));
+            plane_data.push_back(make_float4(f[4], f[5], f[6], 0.f));
+            plane_data.push_back(make_float4(f[8], f[9], f[10], 0.f));
+            static const float I[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+            if (std::memcmp(iv, I, sizeof(I)) == 0) planes_identity++;
+            break;
+        }
+        }
+    }
+    std::stable_sort(bounds.begin(), bounds.end(), [](const B &a, const B &b) { return a.kind < b.kind; });
+    const int nb = (int)bounds.size();
+    const int nb_pad = (nb + BOUND_PAD - 1) / BOUND_PAD * BOUND_PAD;
+    std::vector<float4> bound(nb_pad, make_float4(0.f, 0.f, 0.f, -1e30f)); // pads pass no ray
+    std::vector<int> bound_shape(nb_pad, -1);
+    for (int j = 0; j < nb; ++j) { bound[j] = bounds[j].b; bound_shape[j] = bounds[j].shape; }
+
+    std::vector<DevMaterial> mats;
+    int rc = convert_materials(desc->materials, desc->n_materials, mats);
+    if (rc != RT_OK) return rc;
+    std::vector<DevLight> lights(desc->n_lights);
+    int n_point = 0;
+    for (int l = 0; l < desc->n_lights; ++l) {
+        const rt_light &L = desc->lights[l];
+        if (L.kind != RT_LIGHT_POINT && L.kind != RT_LIGHT_AMBIENT) return fail(RT_ERR_INVALID, "light %d: unknown kind", l);
+        lights[l].px = L.pos[0]; lights[l].py = L.pos[1]; lights[l].pz = L.pos[2];
+        lights[l].kind = L.kind;
+        lights[l].cr = L.color[0]; lights[l].cg = L.color[1]; lights[l].cb = L.color[2];
+        lights[l].point_index = (L.kind == RT_LIGHT_POINT) ? n_point++ : -1;
+    }
+    std::vector<float4> ctris;
+    cube_tris(ctris);
+
+    rt_scene *s = new (std::nothrow) rt_scene();
+    if (!s) return fail(RT_ERR_NOMEM, "out of host memory");
+    s->device = device;
+    s->n_materials = desc->n_materials;
+    s->counts[0] = counts[0]; s->counts[1] = counts[1]; s->counts[2] = counts[2]; s->counts[3] = counts[3];
+    s->planes_identity = planes_identity;
+    DevScene &d = s->dev;
+    std::memset(&d, 0, sizeof(d));
+    d.n_shapes = n; d.n_bounded = nb; d.n_planes = (int)plane_shape.size();
+    d.n_lights = desc->n_lights; d.n_point_lights = n_point; d.first_nan_shape = first_nan;
+    d.amb_r = desc->ambient[0]; d.amb_g = desc->ambient[1]; d.amb_b = desc->ambient[2];
+    const DevMaterial *dm = nullptr;
+    if ((rc = upload(s, bound, &d.bound)) != RT_OK || (rc = upload(s, bound_shape, &d.bound_shape)) != RT_OK ||
+        (rc = upload(s, meta, &d.shape_meta)) != RT_OK || (rc = upload(s, geom, &d.geom)) != RT_OK ||
+        (rc = upload(s, plane_shape, &d.plane_shape)) != RT_OK || (rc = upload(s, plane_data, &d.plane_data)) != RT_OK ||
+        (rc = upload(s, ctris, &d.cube_tris)) != RT_OK || (rc = upload(s, mats, &dm)) != RT_OK ||
+        (rc = upload(s, lights, &d.lights)) != RT_OK) {
+        rt_scene_destroy(s);
+        return rc;
+    }
+    d.materials = dm;
+    s->d_materials = const_cast<DevMaterial *>(dm);
+    if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        rt_scene_destroy(s);
+        return cuda_fail(e, "cudaStreamCreate");
+    }
+    *out = s;
+    return RT_OK;
+}
+
+int rt_scene_update_materials(rt_scene *scene, const rt_material *materials, int32_t n) {
+    if (!scene || (!materials && n)) return fail(RT_ERR_INVALID, "null argument");
+    if (n != scene->n_materials) return fail(RT_ERR_INVALID, "expected %d materials, got %d", scene->n_materials, n);
+    std::vector<DevMaterial> mats;
+    int rc = convert_materials(materials, n, mats);
+    if (rc != RT_OK) return rc;
+    cudaError_t e = cudaSetDevice(scene->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    if (n) {
+        e = cudaMemcpy(scene->d_materials, mats.data(), sizeof(DevMaterial) * n, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(materials)");
+    }
+    return RT_OK;
+}
+
+void rt_scene_destroy(rt_scene *scene) {
+    if (!scene) return;
+    cudaSetDevice(scene->device);
+    scene->ws.release();
+    for (void *p : scene->allocs) cudaFree(p);
+    if (scene->stream) cudaStreamDestroy(scene->stream);
+    delete scene;
+}
+
+} // extern "C"

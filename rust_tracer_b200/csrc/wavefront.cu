@@ -1,0 +1,286 @@
+// wavefront.cu -- everything of the render path that is not the nearest-hit sweep:
+//   raygen   Camera::get_ray                       (reference src/render.rs:178-185)
+//   spawn    get_light_energy's shadow rays, reflect_ray, refract_ray
+//                                                  (src/render.rs:105-125,142-153; scene/mod.rs:189-193)
+//   shade    trace_ray's colour sum / render_ray_tree, deepest level first
+//                                                  (src/render.rs:57-100; src/render_tree.rs:214-255)
+//   resolve  Color::as_u8 (+ the 4-spp average)    (src/scene/color.rs:43-46)
+//
+// trace_ray's recursion becomes a breadth-first ray tree held in flat pools: level k of every
+// pixel's tree is one contiguous range, swept in one launch.  Colours flow back up through
+// per-node child slots in the reference's own summation order (deterministic, no atomics
+// on colours), so the only arithmetic that differs from the reference is powf/atan2f/acosf.
+#include "kernels.h"
+#include "shade.cuh"
+
+namespace rt {
+
+constexpr int WF_BLOCK = 128;
+
+RT_DEV unsigned long long splitmix64(unsigned long long &state) {
+    unsigned long long z = (state += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+RT_DEV float u01(unsigned long long x) { return xmul((float)(x >> 40), 1.0f / 16777216.0f); }
+
+__global__ void __launch_bounds__(WF_BLOCK) raygen_kernel(FrameParams fp, Pools p, long long sample0, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    long long sidx = sample0 + i;
+    long long pix = sidx / fp.spp;
+    int s = (int)(sidx - pix * fp.spp);
+    int v = fp.rows[pix / fp.x_res];
+    int u = (int)(pix % fp.x_res);
+    float x_delta = xdiv(xsub(fp.x_max, fp.x_min), (float)fp.x_res);
+    float y_delta = xdiv(xsub(fp.y_max, fp.y_min), (float)fp.y_res);
+    float fu = (float)u, fv = (float)v;
+    if (fp.spp == 4) { // extension, no reference behaviour; mirrored by the oracle
+        unsigned long long key = ((unsigned long long)v * (unsigned long long)fp.x_res + (unsigned long long)u) * 4ull +
+                                 (unsigned long long)s;
+        unsigned long long st = fp.seed ^ (key * 0xD1B54A32D192ED03ull);
+        float xi1 = u01(splitmix64(st));
+        float xi2 = u01(splitmix64(st));
+        fu = xadd(fu, xmul(xadd((float)(s & 1), xi1), 0.5f));
+        fv = xadd(fv, xmul(xadd((float)(s >> 1), xi2), 0.5f));
+    }
+    float x = xadd(fp.x_min, xmul(fu, x_delta));
+    float y = xsub(fp.y_max, xmul(fv, y_delta));
+    V3 origin = v3(fp.cam_ox, fp.cam_oy, fp.cam_oz);
+    V3 dir = vnorm(vsub(v3(x, y, 0.f), origin));
+    p.t_a[i] = make_float4(origin.x, origin.y, origin.z, dir.x);
+    p.t_b[i] = make_float4(dir.y, dir.z, 0.f, 0.f);
+    p.t_parent[i] = i;
+    p.t_root[i] = i;
+}
+
+RT_DEV void load_tree_ray(const Pools &p, int i, V3 &o, V3 &d) {
+    float4 a = p.t_a[i], b = p.t_b[i];
+    o = v3(a.x, a.y, a.z);
+    d = v3(a.w, b.x, b.y);
+}
+
+__global__ void __launch_bounds__(WF_BLOCK)
+spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn_children) {
+    int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= end) return;
+    p.t_sbase[i] = -1;
+    p.t_crefl[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    p.t_crefr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    V3 o, d;
+    load_tree_ray(p, i, o, d);
+    Hit h;
+    if (!hit_record(sc, p.t_key[i], o, d, h)) {
+        if (p.t_hitid) p.t_hitid[i] = -1;
+        return;
+    }
+    if (p.t_hitid) p.t_hitid[i] = h.id;
+    atomicAdd(&p.counters[2], 1u);
+    const DevMaterial m = sc.materials[h.material];
+    float n1, n2;
+    refraction_indices(m, h.entering, n1, n2);
+
+    // shadow rays: p = point + 0.0002 * normal (render.rs:147); one per point light
+    if (sc.n_point_lights > 0) {
+        unsigned int sb = atomicAdd(&p.counters[1], (unsigned int)sc.n_point_lights);
+        if (sb + (unsigned int)sc.n_point_lights <= (unsigned int)p.s_cap) {
+            p.t_sbase[i] = (int)sb;
+            V3 sp = vadd(h.point, vscale(h.normal, 0.0002f));
+            for (int l = 0; l < sc.n_lights; ++l) {
+                DevLight L = sc.lights[l];
+                if (L.kind != 0) continue;
+                V3 ldir = vnorm(vsub(v3(L.px, L.py, L.pz), sp)); // scene/mod.rs:191
+                p.s_a[sb + L.point_index] = make_float4(sp.x, sp.y, sp.z, ldir.x);
+                p.s_b[sb + L.point_index] = make_float4(ldir.y, ldir.z, 0.f, 0.f);
+            }
+        } else {
+            p.counters[3] = 1u;
+        }
+    }
+    if (!spawn_children) return;
+    if (m.reflectivity > F32_EPS) { // render.rs:70
+        V3 ro, rd;
+        reflect_ray(d, h, ro, rd);
+        unsigned int c = atomicAdd(&p.counters[0], 1u);
+        if (c < (unsigned int)p.t_cap) {
+            p.t_a[c] = make_float4(ro.x, ro.y, ro.z, rd.x);
+            p.t_b[c] = make_float4(rd.y, rd.z, 0.f, 0.f);
+            p.t_parent[c] = (i << 1) | 0;
+            p.t_root[c] = p.t_root[i];
+        } else {
+            p.counters[3] = 1u;
+        }
+    }
+    if (m.refraction_index > F32_EPS) { // render.rs:86
+        V3 ro, rd;
+        if (refract_ray(d, h, n1, n2, ro, rd)) {
+            unsigned int c = atomicAdd(&p.counters[0], 1u);
+            if (c < (unsigned int)p.t_cap) {
+                p.t_a[c] = make_float4(ro.x, ro.y, ro.z, rd.x);
+                p.t_b[c] = make_float4(rd.y, rd.z, 0.f, 0.f);
+                p.t_parent[c] = (i << 1) | 1;
+                p.t_root[c] = p.t_root[i];
+            } else {
+                p.counters[3] = 1u;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(WF_BLOCK)
+shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level, float4 *sample_rgb,
+             const unsigned char *sample_mask) {
+    int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= end) return;
+    if (sample_mask && !sample_mask[p.t_root[i]]) return; // render_forest_filter: tree untouched
+    V3 o, d;
+    load_tree_ray(p, i, o, d);
+    Hit h;
+    V3 colour = v3(0.f, 0.f, 0.f);
+    bool is_node = hit_record(sc, p.t_key[i], o, d, h);
+    if (is_node) {
+        const DevMaterial m = sc.materials[h.material];
+        float n1, n2;
+        refraction_indices(m, h.entering, n1, n2);
+        V3 ambient = cmul(eval_colorfn(m.ambient, h.tu, h.tv), v3(sc.amb_r, sc.amb_g, sc.amb_b));
+
+        // lights (render.rs:59-68 / render_tree.rs:223-232): Sum starts from BLACK
+        V3 lights = v3(0.f, 0.f, 0.f);
+        int sb = p.t_sbase[i];
+        V3 sp = vadd(h.point, vscale(h.normal, 0.0002f));
+        for (int l = 0; l < sc.n_lights; ++l) {
+            DevLight L = sc.lights[l];
+            V3 ldir, energy = v3(L.cr, L.cg, L.cb);
+            if (L.kind == 0) { // PointLight::get_energy (scene/mod.rs:189-206)
+                V3 lpos = v3(L.px, L.py, L.pz);
+                ldir = vnorm(vsub(lpos, sp));
+                unsigned long long sk = p.s_key[sb + L.point_index];
+                if (sk != KEY_MISS) {
+                    V3 hp = ray_at(sp, ldir, key_t(sk));
+                    if (vlen2(vsub(hp, sp)) < vlen2(vsub(lpos, sp))) energy = v3(0.f, 0.f, 0.f);
+                }
+            } else { // AmbientLight::get_energy (scene/mod.rs:236-238)
+                ldir = v3(0.f, 0.f, 0.f);
+            }
+            float fresnel = fresnel_reflection(ldir, h.normal, n1, n2);
+            lights = vadd(lights, cscale(fresnel, reflected_energy(m, energy, ldir, h)));
+        }
+
+        float4 cr = p.t_crefl[i], ct = p.t_crefr[i];
+        V3 reflected = v3(0.f, 0.f, 0.f), refracted = v3(0.f, 0.f, 0.f);
+        if (!fp.forest_shading) {
+            if (m.reflectivity > F32_EPS) { // render.rs:70-84
+                V3 ro, rd;
+                reflect_ray(d, h, ro, rd);
+                float fresnel = fresnel_reflection(rd, h.normal, n1, n2);
+                reflected = cscale(fresnel, reflected_energy(m, v3(cr.x, cr.y, cr.z), rd, h));
+            }
+            if (m.refraction_index > F32_EPS) { // render.rs:86-98
+                V3 ro, rd, inner = v3(0.f, 0.f, 0.f);
+                if (refract_ray(d, h, n1, n2, ro, rd)) {
+                    float fresnel = xsub(1.f, fresnel_reflection(rd, vneg(h.normal), n1, n2));
+                    inner = cscale(fresnel, v3(ct.x, ct.y, ct.z));
+                }
+                refracted = cmul(eval_colorfn(m.diffuse, h.tu, h.tv), inner);
+            }
+        } else {
+            // render_tree.rs:234-249: a missing child evaluates to (BLACK, (0,0,0)); an
+            // existing one returns its -eye_dir = norm(its ray direction)
+            V3 dir = v3(0.f, 0.f, 0.f);
+            if (cr.w != 0.f) {
+                V3 ro, rd;
+                reflect_ray(d, h, ro, rd);
+                dir = vnorm(rd); // -(child eye_dir) = norm(child ray direction)
+            }
+            float fresnel = fresnel_reflection(dir, h.normal, n1, n2);
+            reflected = cscale(fresnel, reflected_energy(m, v3(cr.x, cr.y, cr.z), h.eye, h));
+            dir = v3(0.f, 0.f, 0.f);
+            if (ct.w != 0.f) {
+                V3 ro, rd;
+                refract_ray(d, h, n1, n2, ro, rd);
+                dir = vnorm(rd); // -(child eye_dir) = norm(child ray direction)
+            }
+            float ft = xsub(1.f, fresnel_reflection(dir, vneg(h.normal), n1, n2));
+            refracted = cscale(ft, v3(ct.x, ct.y, ct.z));
+        }
+        colour = vadd(vadd(vadd(ambient, lights), reflected), refracted); // render.rs:100
+    }
+    if (level == 0) {
+        sample_rgb[p.t_parent[i]] = make_float4(colour.x, colour.y, colour.z, is_node ? 1.f : 0.f);
+    } else if (is_node) {
+        int par = p.t_parent[i];
+        float4 out = make_float4(colour.x, colour.y, colour.z, 1.f);
+        if (par & 1) p.t_crefr[par >> 1] = out;
+        else p.t_crefl[par >> 1] = out;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+resolve_kernel(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp, float *rgb_f32,
+               unsigned char *rgb_u8, const unsigned char *pixel_mask) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pixels) return;
+    if (pixel_mask && !pixel_mask[i]) return;
+    V3 c;
+    if (spp == 1) {
+        float4 s = sample_rgb[i];
+        c = v3(s.x, s.y, s.z);
+    } else {
+        V3 sum = v3(0.f, 0.f, 0.f);
+        for (int s = 0; s < spp; ++s) {
+            float4 q = sample_rgb[(long long)i * spp + s];
+            sum = vadd(sum, v3(q.x, q.y, q.z));
+        }
+        c = cscale(0.25f, sum);
+    }
+    long long o = (pixel0 + i) * 3;
+    if (rgb_f32) { rgb_f32[o] = c.x; rgb_f32[o + 1] = c.y; rgb_f32[o + 2] = c.z; }
+    if (rgb_u8) { rgb_u8[o] = as_u8(c.x); rgb_u8[o + 1] = as_u8(c.y); rgb_u8[o + 2] = as_u8(c.z); }
+}
+
+__global__ void forest_sizes_kernel(Pools p, int n, int *sizes) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && p.t_hitid[i] >= 0) atomicAdd(&sizes[p.t_root[i]], 1);
+}
+
+__global__ void forest_mark_kernel(Pools p, int n, const int *ids, int n_ids, unsigned char *mask) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int id = p.t_hitid[i];
+    if (id < 0) return;
+    for (int k = 0; k < n_ids; ++k)
+        if (ids[k] == id) { mask[p.t_root[i]] = 1; return; }
+}
+
+static unsigned int nblk(long long n, int b) { return (unsigned int)((n + b - 1) / b); }
+
+void launch_raygen(const FrameParams &fp, const Pools &p, long long sample0, int n, cudaStream_t stream) {
+    if (n > 0) raygen_kernel<<<nblk(n, WF_BLOCK), WF_BLOCK, 0, stream>>>(fp, p, sample0, n);
+}
+void launch_spawn(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int spawn_children,
+                  cudaStream_t stream) {
+    if (end > begin)
+        spawn_kernel<<<nblk(end - begin, WF_BLOCK), WF_BLOCK, 0, stream>>>(sc, fp, p, begin, end, spawn_children);
+}
+void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level,
+                  float4 *sample_rgb, const unsigned char *sample_mask, cudaStream_t stream) {
+    if (end > begin)
+        shade_kernel<<<nblk(end - begin, WF_BLOCK), WF_BLOCK, 0, stream>>>(sc, fp, p, begin, end, level, sample_rgb,
+                                                                          sample_mask);
+}
+void launch_resolve(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp, float *rgb_f32,
+                    unsigned char *rgb_u8, const unsigned char *pixel_mask, cudaStream_t stream) {
+    if (n_pixels > 0)
+        resolve_kernel<<<nblk(n_pixels, 256), 256, 0, stream>>>(sample_rgb, pixel0, n_pixels, spp, rgb_f32, rgb_u8,
+                                                                pixel_mask);
+}
+
+void launch_forest_sizes(const Pools &p, int n, int *sizes, cudaStream_t stream) {
+    if (n > 0) forest_sizes_kernel<<<nblk(n, 256), 256, 0, stream>>>(p, n, sizes);
+}
+void launch_forest_mark(const Pools &p, int n, const int *ids, int n_ids, unsigned char *mask, cudaStream_t stream) {
+    if (n > 0) forest_mark_kernel<<<nblk(n, 256), 256, 0, stream>>>(p, n, ids, n_ids, mask);
+}
+
+} // namespace rt
