@@ -167,6 +167,7 @@ typedef struct rt_stats {
     float    sweep_ms;      /* device time in the nearest-hit sweeps (CUDA events)        */
     float    shade_ms;      /* device time in ray generation, spawn and shading           */
     float    total_ms;      /* device time of the whole call                              */
+    uint32_t kernel_launches; /* kernels of this library launched by the call             */
 } rt_stats;
 
 typedef struct rt_scene rt_scene;   /* opaque: device-resident scene tables */
@@ -193,6 +194,10 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out);
 /* Material::set_diffuse + friends after upload (src/gui.rs:221-235): replaces the whole
  * material table, geometry untouched.  n must equal the scene's n_materials.            */
 int rt_scene_update_materials(rt_scene *scene, const rt_material *materials, int32_t n);
+/* Launch this scene's kernels and copies on `stream` (a cudaStream_t created by the caller
+ * on the scene's device, e.g. a torch stream's handle) so that the caller's own events
+ * bracket the work; NULL restores the scene's private stream.  Calls stay synchronous.   */
+int rt_scene_set_stream(rt_scene *scene, void *stream);
 void rt_scene_destroy(rt_scene *scene);
 
 /* ---- Basic renderer ------------------------------------------------------------------ */

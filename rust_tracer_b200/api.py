@@ -107,6 +107,10 @@ class Scene:
         check(lib().rt_scene_create(C.byref(desc.desc), device, C.byref(self._h)))
         self.device = device
 
+    def set_stream(self, cuda_stream_handle):
+        """Run on a caller-created CUDA stream (int handle); 0/None restores the private one."""
+        check(lib().rt_scene_set_stream(self._h, C.c_void_p(cuda_stream_handle or None)))
+
     def update_materials(self, materials):
         check(lib().rt_scene_update_materials(self._h, materials, len(materials)))
 

@@ -44,7 +44,9 @@ struct rt_scene {
     int n_materials = 0;
     int counts[4] = {0, 0, 0, 0}; // shapes per rt_shape_kind
     int planes_identity = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;     // the stream work is launched on
+    cudaStream_t own_stream = nullptr; // created with the scene
+    unsigned int launches = 0;         // kernels launched by the current call
     rt::Workspace ws;
 };
 

@@ -164,6 +164,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     unsigned int init[4] = {(unsigned int)n, 0u, 0u, 0u};
     CK(cudaMemcpyAsync(p.counters, init, sizeof(init), cudaMemcpyHostToDevice, st), "counters init");
     launch_raygen(fp, p, sample0, n, st);
+    scene->launches += 1;
 
     auto sweep = [&](RaySeg a, RaySeg b) {
         if (a.n + b.n == 0) return;
@@ -173,6 +174,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         else launch_sweep(sc, a, b, rpt, ws.exact_counter, st);
         cudaEventRecord(e1, st);
         acc.sweep_spans.push_back({e0, e1});
+        scene->launches += 1;
         if (audit) acc.exact += (unsigned long long)(a.n + b.n) * (unsigned long long)sc.n_bounded;
     };
     auto tree_seg = [&](int b, int e) { return RaySeg{p.t_a + b, p.t_b + b, p.t_key + b, e - b}; };
@@ -182,6 +184,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     for (int k = 0; k < fp.depth; ++k) {
         sweep(tree_seg(tb, te), shadow_seg(sb, se));
         launch_spawn(sc, fp, p, tb, te, (k + 1 < fp.depth) ? 1 : 0, st);
+        if (te > tb) scene->launches += 1;
         CK(cudaMemcpyAsync(ws.h_counters, p.counters, 4 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st), "counters readback");
         CK(cudaStreamSynchronize(st), "wavefront level");
         if (ws.h_counters[3]) return 1; // pool overflow
@@ -201,8 +204,10 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
 // Shade levels deepest-first into ws.sample_rgb (band-local sample index).
 static int shade_band(rt_scene *scene, const DevScene &sc, Workspace &ws, const FrameParams &fp, const BandLevels &lv,
                       const unsigned char *sample_mask) {
-    for (int k = (int)lv.tb.size() - 1; k >= 0; --k)
+    for (int k = (int)lv.tb.size() - 1; k >= 0; --k) {
         launch_shade(sc, fp, ws.pools, lv.tb[k], lv.te[k], k, ws.sample_rgb, sample_mask, scene->stream);
+        if (lv.te[k] > lv.tb[k]) scene->launches += 1;
+    }
     CK(cudaGetLastError(), "shade launch");
     return RT_OK;
 }
@@ -285,6 +290,7 @@ static int cast_band_sized(rt_scene *scene, Workspace &ws, const FrameParams &fp
         if (rc != RT_OK) return rc;
         rc = cast_band(scene, ws, fp, sample0, n, flags, lv, acc, events);
         if (rc <= 0) return rc;
+        cudaMemsetAsync(ws.exact_counter, 0, sizeof(unsigned long long), scene->stream); // the band is recast
         if (t_cap >= worst) return fail(RT_ERR_INTERNAL, "ray pool overflow at the worst-case size");
         t_cap = std::min(worst, t_cap * 2);
     }
@@ -305,6 +311,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
 
     EventPool events;
     cudaEvent_t ev0 = events.get(), ev1 = events.get();
+    scene->launches = 0;
     CK(cudaMemsetAsync(ws.exact_counter, 0, sizeof(unsigned long long), st), "exact counter");
     cudaEventRecord(ev0, st);
 
@@ -329,6 +336,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
             if ((rc = shade_band(scene, scene->dev, ws, fp, lv, nullptr)) != RT_OK) return rc;
         }
         launch_resolve(ws.sample_rgb, s0 / pr->spp, n / pr->spp, pr->spp, out.d_f32, out.d_u8, nullptr, st);
+        if (n > 0) scene->launches += 1;
     }
     cudaEventRecord(ev1, st);
     CK(cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
@@ -347,6 +355,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
         stats->total_ms = ms;
         stats->sweep_ms = sweep;
         stats->shade_ms = ms - sweep;
+        stats->kernel_launches = scene->launches;
     }
     return RT_OK;
 }

@@ -334,7 +334,14 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         rt_scene_destroy(s);
         return cuda_fail(e, "cudaStreamCreate");
     }
+    s->own_stream = s->stream;
     *out = s;
+    return RT_OK;
+}
+
+int rt_scene_set_stream(rt_scene *scene, void *stream) {
+    if (!scene) return fail(RT_ERR_INVALID, "null scene");
+    scene->stream = stream ? (cudaStream_t)stream : scene->own_stream;
     return RT_OK;
 }
 
@@ -358,7 +365,7 @@ void rt_scene_destroy(rt_scene *scene) {
     cudaSetDevice(scene->device);
     scene->ws.release();
     for (void *p : scene->allocs) cudaFree(p);
-    if (scene->stream) cudaStreamDestroy(scene->stream);
+    if (scene->own_stream) cudaStreamDestroy(scene->own_stream);
     delete scene;
 }
 
