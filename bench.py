@@ -1,0 +1,329 @@
+#!/usr/bin/env python
+"""bench.py -- the headline measurement of the render path (driver contract).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c3|c2|c5s] [--impl ours|reference]
+
+A "step" is one full frame of the workload: primary rays -> nearest-hit sweeps -> shading ->
+RGB8, rendered by the CUDA path of librt_b200.so.  With N > 1 (one process per GPU, torchrun)
+the frame is split into interleaved row tiles and the finished tiles are gathered to rank 0
+over NCCL inside the step (strong scaling: the frame is fixed).
+
+Prints ONE JSON line (rank 0).  `value` = Mrays/s with the scene resident in HBM, timed with
+CUDA events on the launching stream; `e2e` = the same metric through the host-buffer call
+(scene upload + render + RGB8 read-back inside the timed region).  The oracle is executed
+only by the cpu_baseline leg and by --impl reference (it is never on the product path).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# BASELINE.json configs.  c4 is the north_star target ("4K, 10k-primitive, depth-5 ... on 1
+# GPU, >= 7x at 8 GPUs") and fits one GPU, so it is the default at every N.
+WORKLOADS = {
+    "c2": dict(scene="default", width=1920, height=1080, depth=3, spp=1, desc="my_scene.rs 1920x1080 depth 3"),
+    "c3": dict(scene="s1k", width=3840, height=2160, depth=5, spp=1, desc="1,000 spheres + plane, 4 lights, 3840x2160 depth 5"),
+    "c4": dict(scene="m10k", width=3840, height=2160, depth=5, spp=1, desc="10k mixed spheres/triangles, 4 lights, 3840x2160 depth 5"),
+    "c5s": dict(scene="m10k", width=3840, height=2160, depth=8, spp=4, desc="config 5 at 4K instead of 8K: 10k prims, 4 spp, depth 8"),
+}
+ROWS_PER_TILE = 8
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU every 100 ms while the timed region runs."""
+
+    REASONS = {  # nvmlClocksEventReason* bits
+        0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+        0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+        0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+    }
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        while not self.stop_flag and self.nv is not None:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                bits = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for b, name in self.REASONS.items():
+                    if bits & b and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def result(self):
+        self.stop_flag = True
+        if self.is_alive():
+            self.join(timeout=1.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def oracle_rate(desc, wl, seconds, threads):
+    """Times the CPU oracle (the port of the reference's own algorithm) on a bounded row sample
+    of the workload; returns (Mrays/s, description, rays, seconds)."""
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import orc
+    from rust_tracer_b200 import abi
+
+    cam = abi.default_camera(wl["width"], wl["height"])
+    h = wl["height"]
+    probe = np.array([h // 3, (2 * h) // 3], dtype=np.int32)
+    t0 = time.perf_counter()
+    _, _, c = orc.render(desc.desc, cam, wl["depth"], rows=probe, spp=wl["spp"], seed=1, threads=threads, want_f32=False)
+    dt = max(time.perf_counter() - t0, 1e-6)
+    n_rows = int(max(threads, min(h // 2, round(len(probe) * seconds / dt))))
+    rows = np.unique(np.linspace(7, h - 1, n_rows).astype(np.int32))
+    t0 = time.perf_counter()
+    _, _, c = orc.render(desc.desc, cam, wl["depth"], rows=rows, spp=wl["spp"], seed=1, threads=threads, want_f32=False)
+    dt = time.perf_counter() - t0
+    sample = "%d of %d rows of the %dx%d frame (%d rays, %.1f s)" % (len(rows), h, wl["width"], h, c.rays, dt)
+    return c.rays / dt / 1e6, sample, int(c.rays), dt
+
+
+def emit(obj):
+    print(json.dumps(obj), flush=True)
+
+
+def run_reference(args, wl):
+    """--impl reference: the reference's own CPU algorithm (the oracle port -- the Rust crate
+    cannot be built here) on all host threads; each step renders a bounded row
+    sample of the same workload.  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import rust_tracer_b200 as rt
+    desc = rt.SceneDesc.builtin(wl["scene"])
+    threads = os.cpu_count() or 1
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    rates, sample = [], ""
+    for i in range(args.warmup + args.steps):
+        _, sample, rays, dt = oracle_rate(desc, wl, per_step, threads)
+        if i >= args.warmup:
+            rates.append((rays, dt))
+    total_rays = sum(r for r, _ in rates)
+    total_s = sum(t for _, t in rates)
+    value = total_rays / total_s / 1e6
+    emit({
+        "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_s / max(1, args.steps),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "scene": wl["scene"], "width": wl["width"],
+                   "height": wl["height"], "depth": wl["depth"], "spp": wl["spp"]},
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    })
+
+
+def scene_bytes(desc):
+    """Bytes of the flat scene description rt_scene_create copies to the device."""
+    import ctypes as C
+    from rust_tracer_b200 import abi
+    d = desc.desc
+    return (d.n_shapes * C.sizeof(abi.rt_shape) + d.n_materials * C.sizeof(abi.rt_material)
+            + d.n_lights * C.sizeof(abi.rt_light) + 12)
+
+
+def run_ours(args, wl):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import rust_tracer_b200 as rt
+    from rust_tracer_b200.distributed import gather_rows
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the render path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    w, h, depth, spp = wl["width"], wl["height"], wl["depth"], wl["spp"]
+    desc = rt.SceneDesc.builtin(wl["scene"])
+    scene = rt.Scene(desc, device=local)
+    stream = torch.cuda.Stream(device=dev)
+    scene.set_stream(stream.cuda_stream)
+    n_rows = len(rt.tile_rows(h, rank, world, ROWS_PER_TILE))
+    tile = torch.empty((n_rows, w, 3), dtype=torch.uint8, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > the 126 MB L2
+    pinned = torch.empty((h, w, 3), dtype=torch.uint8).pin_memory() if rank == 0 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        """One frame with the scene resident: render this rank's row tiles, gather to rank 0."""
+        with torch.cuda.stream(stream):
+            st = scene.render_device(w, h, depth, d_rgb_u8=tile.data_ptr(), spp=spp, seed=1, rank=rank, world=world,
+                                     rows_per_tile=ROWS_PER_TILE)
+            full = gather_rows(tile, h, w, rank, world, ROWS_PER_TILE)
+        return st, full
+
+    for _ in range(args.warmup):
+        flush.zero_()
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    spans, stats_list = [], []
+    for _ in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        st, full = step()
+        e1.record(stream)
+        spans.append((e0, e1))
+        stats_list.append(st)
+    barrier()
+    clocks = sampler.result()
+    dev_ms = sum(a.elapsed_time(b) for a, b in spans)
+
+    # whole-job numbers: rays of all ranks / max-over-ranks device time
+    rays_step = float(sum(s["rays"] for s in stats_list)) / max(1, args.steps)
+    flops_step = float(sum(s["algorithmic_flops"] for s in stats_list)) / max(1, args.steps)
+    agg = torch.tensor([rays_step, flops_step, float(stats_list[-1]["kernel_launches"])], dtype=torch.float64, device=dev)
+    tmax = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    rays_step, flops_step, launches = (float(x) for x in agg.tolist())
+    dev_ms = float(tmax.item())
+    ms_per_step = dev_ms / max(1, args.steps)
+    value = rays_step / (ms_per_step * 1e-3) / 1e6
+
+    # ---- e2e: the host-buffer call a user of the reference would make -----------------------
+    # every step: rt_scene_create (scene description H2D) -> render -> RGB8 on the host.
+    scene.close()
+    del tile
+    torch.cuda.empty_cache()
+    h2d = scene_bytes(desc)
+    d2h = w * h * 3
+    e2e_steps = max(1, min(args.steps, 3))
+
+    def e2e_step():
+        sc = rt.Scene(desc, device=local)
+        if world == 1:
+            sc.render(w, h, depth, spp=spp, seed=1, want_f32=False, out_u8=pinned.numpy())
+        else:
+            t = torch.empty((n_rows, w, 3), dtype=torch.uint8, device=dev)
+            sc.render_device(w, h, depth, d_rgb_u8=t.data_ptr(), spp=spp, seed=1, rank=rank, world=world,
+                             rows_per_tile=ROWS_PER_TILE)
+            full = gather_rows(t, h, w, rank, world, ROWS_PER_TILE)
+            if rank == 0:
+                pinned.copy_(full)
+                torch.cuda.synchronize()
+        sc.close()
+
+    e2e_step()  # warm-up
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = rays_step * e2e_steps / float(e2e_s.item()) / 1e6
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (sweep_kernel): FP32, not HBM and not tensor --------
+    n_lights = desc.desc.n_lights
+    sweep_ms = sum(s["sweep_ms"] for s in stats_list) / max(1, args.steps)          # rank 0, CUDA events on its stream
+    total_ms = sum(s["total_ms"] for s in stats_list) / max(1, args.steps)
+    r0 = stats_list[-1]
+    sweep_flops = r0["algorithmic_flops"] - r0["nodes"] * (60.0 + 70.0 * n_lights)    # SURVEY 8d credit, rank 0's share
+    pairs = r0["sphere_tests"] + r0["triangle_tests"] + r0["cube_tests"] * 12 + r0["plane_tests"]
+    measured_peak, sms, khz = rt.measure_fp32_peak(local)
+    nominal_peak = sms * 128 * 2 * khz * 1e3 / 1e12
+    achieved = sweep_flops / (sweep_ms * 1e-3) / 1e12 if sweep_ms > 0 else 0.0
+    # what the kernel really executes per pair in its filter: 3 FADD + 2 FMUL + 7 FFMA = 19 flop
+    # (sweep.cu phase 1), plus the exact tests (<1% of pairs)
+    executed = (pairs * 19.0) / (sweep_ms * 1e-3) / 1e12 if sweep_ms > 0 else 0.0
+    roofline = {
+        "bound": "fp32", "kernel": "sweep_kernel", "achieved": achieved, "peak": measured_peak, "unit": "TFLOP/s",
+        "frac": achieved / measured_peak if measured_peak else None, "traffic": None,
+        "peak_source": "rt_measure_fp32_peak FFMA micro-kernel on this GPU (MEASURED_PEAKS.json has no FP32 figure); "
+                       "nominal %d SMs x 128 x 2 x %.0f MHz = %.1f TFLOP/s" % (sms, khz / 1e3, nominal_peak),
+        "achieved_is": "algorithmic flops credited per SURVEY 8d (54/sphere, 30/triangle pair) / sweep time",
+        "executed_tflops": executed, "executed_frac": executed / measured_peak if measured_peak else None,
+        "pairs_per_s": pairs / (sweep_ms * 1e-3) if sweep_ms > 0 else None,
+        "sweep_ms_per_step": sweep_ms, "sweep_share_of_step": sweep_ms / total_ms if total_ms else None,
+    }
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, sample, _, _ = oracle_rate(desc, wl, args.cpu_seconds, threads)
+        cpu = {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample}
+
+    emit({
+        "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "scene": wl["scene"], "width": w, "height": h,
+                   "depth": depth, "spp": spp, "rays_per_frame": rays_step, "rows_per_tile": ROWS_PER_TILE,
+                   "l2": "256 MiB buffer written between timed steps; ray pools (>1 GB) exceed L2 anyway",
+                   "partition": "interleaved row tiles, gather to rank 0 inside the step" if world > 1 else "single GPU"},
+        "roofline": roofline, "cpu_baseline": cpu,
+        "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_steps, "what": "rt_scene_create + rt_render into a pinned host RGB8 buffer + rt_scene_destroy"},
+        "gpu_launches": int(launches) * args.steps, "clocks": clocks,
+        "frame_ms": ms_per_step,
+    })
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

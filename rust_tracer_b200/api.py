@@ -115,13 +115,18 @@ class Scene:
         check(lib().rt_scene_update_materials(self._h, materials, len(materials)))
 
     def render(self, width, height, depth, spp=1, seed=0, rank=0, world=1, rows_per_tile=8, flags=0,
-               want_f32=True, want_u8=True):
-        """Returns (rgb_f32 | None, rgb_u8 | None, stats dict); arrays are [rows, width, 3]."""
+               want_f32=True, want_u8=True, out_u8=None):
+        """Returns (rgb_f32 | None, rgb_u8 | None, stats dict); arrays are [rows, width, 3].
+        out_u8: caller-owned uint8 array of that shape to fill (e.g. a view of pinned memory)."""
         cam = camera(width, height)
         p = _params(depth, spp, seed, rank, world, rows_per_tile, flags)
         n_rows = len(tile_rows(height, rank, world, rows_per_tile))
         f = np.zeros((n_rows, width, 3), dtype=np.float32) if want_f32 else None
         u = np.zeros((n_rows, width, 3), dtype=np.uint8) if want_u8 else None
+        if out_u8 is not None:
+            if out_u8.dtype != np.uint8 or out_u8.size != n_rows * width * 3 or not out_u8.flags.c_contiguous:
+                raise ValueError("out_u8 must be a contiguous uint8 array of %d x %d x 3" % (n_rows, width))
+            u, want_u8 = out_u8, True
         st = abi.rt_stats()
         check(lib().rt_render(self._h, C.byref(cam), C.byref(p),
                               f.ctypes.data if want_f32 else None, u.ctypes.data if want_u8 else None, C.byref(st)))
