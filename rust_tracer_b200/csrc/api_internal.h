@@ -22,6 +22,8 @@ struct Workspace {
     long long mask_cap = 0;
     unsigned int *h_counters = nullptr; // pinned mirror of pools.counters
     unsigned long long *exact_counter = nullptr;
+    unsigned int *batch_counters = nullptr; // one work counter per sweep launch of a band
+    int batch_next = 0;
     void *out_f32 = nullptr, *out_u8 = nullptr; // device staging for host-buffer calls
     size_t out_f32_cap = 0, out_u8_cap = 0;
 
@@ -44,6 +46,7 @@ struct rt_scene {
     int n_materials = 0;
     int counts[4] = {0, 0, 0, 0}; // shapes per rt_shape_kind
     int planes_identity = 0;
+    int sm_count = 0;
     cudaStream_t stream = nullptr;     // the stream work is launched on
     cudaStream_t own_stream = nullptr; // created with the scene
     unsigned int launches = 0;         // kernels launched by the current call

@@ -14,6 +14,8 @@ namespace rt {
 
 // ---- workspace --------------------------------------------------------------------------
 
+constexpr int BATCH_COUNTERS = 2048; // one per sweep launch of a band: (depth + 1 <= 31) x table chunks
+
 template <typename T> static int dev_alloc(T **p, size_t n, const char *what) {
     *p = nullptr;
     if (n == 0) return RT_OK;
@@ -45,6 +47,7 @@ void Workspace::release() {
     if (h_counters) cudaFreeHost(h_counters);
     h_counters = nullptr;
     cudaFree(exact_counter); exact_counter = nullptr;
+    cudaFree(batch_counters); batch_counters = nullptr;
     cudaFree(out_f32); cudaFree(out_u8);
     out_f32 = out_u8 = nullptr; out_f32_cap = out_u8_cap = 0;
 }
@@ -100,6 +103,7 @@ int Workspace::ensure_misc() {
     int rc;
     if (!pools.counters && (rc = dev_alloc(&pools.counters, 4, "counters"))) return rc;
     if (!exact_counter && (rc = dev_alloc(&exact_counter, 1, "exact_counter"))) return rc;
+    if (!batch_counters && (rc = dev_alloc(&batch_counters, BATCH_COUNTERS, "batch_counters"))) return rc;
     if (!h_counters) {
         cudaError_t e = cudaMallocHost((void **)&h_counters, 4 * sizeof(unsigned int) + sizeof(unsigned long long));
         if (e != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
@@ -157,12 +161,15 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     const DevScene &sc = scene->dev;
     cudaStream_t st = scene->stream;
     Pools &p = ws.pools;
-    const int rpt = env_int("RT_B200_RAYS_PER_THREAD", 2, 1, 4);
+    const int rpt = env_int("RT_B200_RAYS_PER_THREAD", 0, 0, 4);
     const bool audit = (flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
     lv = BandLevels();
 
     unsigned int init[4] = {(unsigned int)n, 0u, 0u, 0u};
     CK(cudaMemcpyAsync(p.counters, init, sizeof(init), cudaMemcpyHostToDevice, st), "counters init");
+    CK(cudaMemsetAsync(ws.batch_counters, 0, BATCH_COUNTERS * sizeof(unsigned int), st), "batch counters");
+    ws.batch_next = 0;
+    cudaError_t sweep_err = cudaSuccess;
     launch_raygen(fp, p, sample0, n, st);
     scene->launches += 1;
 
@@ -171,7 +178,14 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         cudaEvent_t e0 = events.get(), e1 = events.get();
         cudaEventRecord(e0, st);
         if (audit) launch_sweep_all_pairs(sc, a, b, ws.exact_counter, st);
-        else launch_sweep(sc, a, b, rpt, ws.exact_counter, st);
+        else {
+            int used = 0;
+            cudaError_t e = launch_sweep(sc, a, b, rpt, scene->sm_count, ws.batch_counters + ws.batch_next,
+                                         BATCH_COUNTERS - ws.batch_next, &used, ws.exact_counter, st);
+            ws.batch_next += used;
+            scene->launches += used > 0 ? used - 1 : 0;
+            if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
+        }
         cudaEventRecord(e1, st);
         acc.sweep_spans.push_back({e0, e1});
         scene->launches += 1;
@@ -197,6 +211,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     }
     sweep(RaySeg{nullptr, nullptr, nullptr, 0}, shadow_seg(sb, se)); // shadows of the last level
     lv.nodes = ws.h_counters[2];
+    CK(sweep_err, "sweep launch");
     CK(cudaGetLastError(), "wavefront launch");
     return RT_OK;
 }

@@ -67,14 +67,18 @@ static double sigma_max3(const double m[9]) {
 
 // Object->world map of a shape whose exact test moves the ray by inv (3x4): centre and
 // the largest stretch of a unit vector.
-static bool world_extent(const float *inv16, double centre[3], double &stretch) {
+// `aniso` = largest / smallest stretch (1 for a similarity transform).
+static bool world_extent(const float *inv16, double centre[3], double &stretch, double &aniso) {
     double a[9] = {inv16[0], inv16[1], inv16[2], inv16[4], inv16[5], inv16[6], inv16[8], inv16[9], inv16[10]};
     double t[3] = {inv16[3], inv16[7], inv16[11]};
     double f[9];
     if (!inv3(a, f)) return false;
     for (int i = 0; i < 3; ++i) centre[i] = -(f[i * 3 + 0] * t[0] + f[i * 3 + 1] * t[1] + f[i * 3 + 2] * t[2]);
     stretch = sigma_max3(f);
-    return std::isfinite(stretch) && std::isfinite(centre[0]) && std::isfinite(centre[1]) && std::isfinite(centre[2]);
+    double inv_min = sigma_max3(a); // 1 / smallest stretch of the forward map
+    aniso = stretch * inv_min;
+    return std::isfinite(stretch) && std::isfinite(aniso) && std::isfinite(centre[0]) && std::isfinite(centre[1]) &&
+           std::isfinite(centre[2]);
 }
 
 static float round_up_f32(double x) {
@@ -92,19 +96,42 @@ static float tri_bound_scale() {
     return 1.5f;
 }
 
-// (cx, cy, cz, R^2): R = r * scale + absolute slack for the reference's own rounding of
-// the object-space ray ("filter margins")
-static float4 make_bound(const double c[3], double r, double scale) {
+static float round_down_f32(double x) {
+    float f = (float)x;
+    if ((double)f > x) f = std::nextafter(f, -INFINITY);
+    return f;
+}
+
+// One bound slot: f32 centre, W = |C|^2 - R^2 rounded down, and |C| + R (for cmax).
+// R = r * scale + absolute slack for the reference's own rounding of the object-space ray
+// + the displacement of the centre when it is rounded to f32 ("filter margins").
+// A bound too large or too far for f32 squares gets W = -FLT_MAX: every ray passes it.
+struct Bound {
+    float cx, cy, cz, w;
+    double reach;
+};
+static Bound make_bound(const double c[3], double r, double scale) {
     double cn = std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
     double rf = r * scale + 64.0 * 1.1920929e-07 * (cn + r);
-    float4 b;
-    b.x = (float)c[0]; b.y = (float)c[1]; b.z = (float)c[2];
-    // the centre is rounded to f32: cover the displacement
-    double dx = c[0] - b.x, dy = c[1] - b.y, dz = c[2] - b.z;
+    Bound b;
+    b.cx = (float)c[0]; b.cy = (float)c[1]; b.cz = (float)c[2];
+    double dx = c[0] - b.cx, dy = c[1] - b.cy, dz = c[2] - b.cz;
     rf += std::sqrt(dx * dx + dy * dy + dz * dz);
-    b.w = round_up_f32(rf * rf * (1.0 + 1e-6));
+    double c2 = (double)b.cx * b.cx + (double)b.cy * b.cy + (double)b.cz * b.cz;
+    b.reach = std::sqrt(c2) + rf;
+    if (!(b.reach < 1e15)) {
+        b.cx = b.cy = b.cz = 0.f;
+        b.w = -3.402823466e+38f;
+        b.reach = 0.0;
+    } else {
+        b.w = round_down_f32(c2 - rf * rf * (1.0 + 1e-6));
+    }
     return b;
 }
+
+// Margin factor of a segment ("filter margins"): 1.5 x (32 for the filter's own
+// rounding + 25 for the reference's object-space ray + 15 aniso^2 for its discriminant).
+static float seg_margin(double aniso) { return round_up_f32(1.5 * (57.0 + 15.0 * aniso * aniso)); }
 
 template <typename T> static int upload(rt_scene *s, const std::vector<T> &host, const T **dev) {
     *dev = nullptr;
@@ -228,7 +255,8 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     std::vector<float4> geom(3 * (size_t)n);
     std::vector<int> plane_shape;
     std::vector<float4> plane_data;
-    struct B { float4 b; int shape; int kind; };
+    // error class of a bound: 0 similarity-transformed spheres, 1 triangles, 2 the rest
+    struct B { Bound b; int shape; int cls; double aniso; };
     std::vector<B> bounds;
     const float tri_scale = tri_bound_scale();
     int counts[4] = {0, 0, 0, 0}, planes_identity = 0, first_nan = -1;
@@ -243,14 +271,15 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         const float *iv = s.inv_transform;
         float4 r0 = make_float4(iv[0], iv[1], iv[2], iv[3]), r1 = make_float4(iv[4], iv[5], iv[6], iv[7]),
                r2 = make_float4(iv[8], iv[9], iv[10], iv[11]);
-        double c[3], stretch;
+        double c[3], stretch, aniso;
         switch (s.kind) {
         case RT_SHAPE_SPHERE:
         case RT_SHAPE_CUBE:
             geom[3 * i] = r0; geom[3 * i + 1] = r1; geom[3 * i + 2] = r2;
-            if (!world_extent(iv, c, stretch)) return fail(RT_ERR_INVALID, "shape %d: singular inverse transform", i);
-            if (s.kind == RT_SHAPE_SPHERE) bounds.push_back({make_bound(c, stretch, 1.0 + 1e-4), i, s.kind});
-            else bounds.push_back({make_bound(c, stretch * 0.8660254037844387, tri_scale), i, s.kind});
+            if (!world_extent(iv, c, stretch, aniso)) return fail(RT_ERR_INVALID, "shape %d: singular inverse transform", i);
+            if (s.kind == RT_SHAPE_SPHERE)
+                bounds.push_back({make_bound(c, stretch, 1.0 + 1e-4), i, aniso <= 1.001 ? 0 : 2, aniso});
+            else bounds.push_back({make_bound(c, stretch * 0.8660254037844387, tri_scale), i, 2, aniso});
             if (first_nan < 0) first_nan = i;
             break;
         case RT_SHAPE_TRIANGLE: {
@@ -263,7 +292,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
                 r = std::max(r, std::sqrt(dx * dx + dy * dy + dz * dz));
             }
             if (!std::isfinite(r)) return fail(RT_ERR_INVALID, "shape %d: non-finite triangle", i);
-            bounds.push_back({make_bound(c, r, tri_scale), i, s.kind});
+            bounds.push_back({make_bound(c, r, tri_scale), i, 1, 1.0});
             if (first_nan < 0) first_nan = i;
             break;
         }
@@ -285,12 +314,37 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         }
         }
     }
-    std::stable_sort(bounds.begin(), bounds.end(), [](const B &a, const B &b) { return a.kind < b.kind; });
+    // segments by error class, each padded to SEG_PAD slots; slot pairs interleaved for FFMA2
+    std::stable_sort(bounds.begin(), bounds.end(), [](const B &a, const B &b) { return a.cls < b.cls; });
     const int nb = (int)bounds.size();
-    const int nb_pad = (nb + BOUND_PAD - 1) / BOUND_PAD * BOUND_PAD;
-    std::vector<float4> bound(nb_pad, make_float4(0.f, 0.f, 0.f, -1e30f)); // pads pass no ray
-    std::vector<int> bound_shape(nb_pad, -1);
-    for (int j = 0; j < nb; ++j) { bound[j] = bounds[j].b; bound_shape[j] = bounds[j].shape; }
+    SweepSegs segs;
+    std::memset(&segs, 0, sizeof(segs));
+    std::vector<Bound> slots;
+    std::vector<int> bound_shape;
+    double cmax = 0.0;
+    const Bound pad = {0.f, 0.f, 0.f, 3.402823466e+38f, 0.0}; // passes no ray
+    for (int j = 0; j < nb;) {
+        int cls = bounds[j].cls;
+        double aniso = 1.0;
+        int g = segs.n++;
+        segs.begin[g] = (int)slots.size();
+        for (; j < nb && bounds[j].cls == cls; ++j) {
+            slots.push_back(bounds[j].b);
+            bound_shape.push_back(bounds[j].shape);
+            aniso = std::max(aniso, bounds[j].aniso);
+            cmax = std::max(cmax, bounds[j].b.reach);
+        }
+        while (slots.size() % SEG_PAD) { slots.push_back(pad); bound_shape.push_back(-1); }
+        segs.end[g] = (int)slots.size();
+        segs.k[g] = seg_margin(aniso);
+    }
+    const int n_slots = (int)slots.size();
+    std::vector<float4> bound(n_slots);
+    for (int j = 0; j < n_slots; j += 2) {
+        const Bound &a = slots[j], &b = slots[j + 1];
+        bound[j] = make_float4(a.cx, b.cx, a.cy, b.cy);
+        bound[j + 1] = make_float4(a.cz, b.cz, a.w, b.w);
+    }
 
     std::vector<DevMaterial> mats;
     int rc = convert_materials(desc->materials, desc->n_materials, mats);
@@ -317,6 +371,8 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     DevScene &d = s->dev;
     std::memset(&d, 0, sizeof(d));
     d.n_shapes = n; d.n_bounded = nb; d.n_planes = (int)plane_shape.size();
+    d.n_slots = n_slots; d.segs = segs; d.cmax = round_up_f32(cmax * (1.0 + 1e-6));
+    cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
     d.n_lights = desc->n_lights; d.n_point_lights = n_point; d.first_nan_shape = first_nan;
     d.amb_r = desc->ambient[0]; d.amb_g = desc->ambient[1]; d.amb_b = desc->ambient[2];
     const DevMaterial *dm = nullptr;

@@ -16,12 +16,14 @@ struct RaySeg {
     int n;
 };
 
-constexpr int BOUND_PAD = 128; // the bound table is padded to a multiple of this
-
 // Nearest-hit query for every ray of s0 then s1 (Scene::intersect, scene/mod.rs:98-116).
+// rays_per_thread: 1, 2 or 4, or 0 to choose by the number of rays.  batch_counters (device,
+// n_counters zeroed words) hand ray batches to the persistent warps, one word per launch;
+// *used receives the number consumed (one per shared-memory chunk of the bound table).
 // exact_counter (device, may be null) accumulates the number of exact pair tests.
-void launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, int rays_per_thread, unsigned long long *exact_counter,
-                  cudaStream_t stream);
+cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, int rays_per_thread, int sm_count,
+                         unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
+                         cudaStream_t stream);
 // Same result, every (ray, shape) pair through the exact test in shape order (audit).
 void launch_sweep_all_pairs(const DevScene &sc, RaySeg s0, RaySeg s1, unsigned long long *exact_counter,
                             cudaStream_t stream);

@@ -2,12 +2,15 @@
 //
 // Layout in HBM (all immutable during a render except `materials`, which
 // rt_scene_update_materials may replace between calls):
-//   bound[j]       float4 (cx, cy, cz, R^2)   conservative bounding sphere of the j-th
-//                                             bounded shape (sphere / triangle / cube),
-//                                             sorted by kind so candidate batches are
-//                                             kind-coherent; the ONLY table the sweep's
-//                                             inner loop reads (staged through smem)
-//   bound_shape[j] int32                      shape id of bound j
+//   bound[2p], bound[2p+1]  float4 x 2        conservative bounding spheres of bound slots 2p and
+//                                             2p+1 (sphere / triangle / cube), interleaved for
+//                                             packed FFMA2:  (cx0, cx1, cy0, cy1) (cz0, cz1, W0, W1)
+//                                             with W = |C|^2 - R^2 rounded down.  Slots are grouped
+//                                             into segments (SweepSegs) by error class, each padded
+//                                             to SEG_PAD slots with W = FLT_MAX (passes no ray).
+//                                             The ONLY table the sweep's inner loop reads (whole
+//                                             table resident in shared memory).
+//   bound_shape[j] int32                      shape id of bound slot j, -1 for a pad
 //   shape_meta[s]  int4  (kind, material, plane index, 0)
 //   geom[3*s..]    3 x float4                 sphere/cube/plane: rows 0..2 of inv_transform
 //                                             triangle: v0.xyz v1.x | v1.yz v2.xy | v2.z n.xyz
@@ -41,9 +44,23 @@ struct DevLight { // 32 bytes
     int point_index; // index among the point lights (shadow slot), -1 for ambient lights
 };
 
+constexpr int SEG_PAD = 64;   // every segment of the bound table is a multiple of this many slots
+constexpr int MAX_SEGS = 4;
+
+// Bound slots [begin, end) share one margin factor k: a ray passes slot j iff
+//   b^2 - |L|^2 + |C|^2 + k * 2^-24 * (|O| + cmax)^2  >=  W_j        (sweep.cu)
+struct SweepSegs {
+    int n;
+    int begin[MAX_SEGS], end[MAX_SEGS];
+    float k[MAX_SEGS];
+};
+
 struct DevScene {
     int n_shapes;
-    int n_bounded;
+    int n_bounded;  // bounded shapes (without pads)
+    int n_slots;    // bound slots including pads (multiple of SEG_PAD)
+    float cmax;     // max over bounds of |C| + R, rounded up
+    SweepSegs segs;
     int n_planes;
     int n_lights;
     int n_point_lights;

@@ -3,31 +3,37 @@
 // Replaces Scene::intersect's linear scan (reference src/scene/mod.rs:98-116, called from
 // src/render.rs:47 and, once per light, src/scene/mod.rs:193).  All-pairs, like an N-body
 // sweep:
-//   phase 1  FILTER   each thread keeps R rays in registers and streams the bounding-sphere
-//                     table (one float4 per shape) through shared memory; a 13-instruction
-//                     FMA test decides "this ray certainly misses this shape".  The test is
-//                     conservative: margins cover both its own rounding and the
-//                     reference's, so it only ever rejects pairs the exact
-//                     test would reject too.
+//   phase 1  FILTER   one persistent CTA per SM keeps the whole bounding-sphere table in
+//                     shared memory; each warp fetches batches of 32 R rays, each thread keeps
+//                     R rays in registers and tests them against two bounds at a time with
+//                     packed FFMA2 (fma.rn.f32x2):
+//                     7 FMA per (ray, bound) decide "this ray certainly misses this shape".
+//                     The test is conservative: its margin covers both its own rounding and
+//                     the reference's ("filter margins"), so it only ever rejects
+//                     pairs the exact test would reject too.
 //   phase 2  EXACT    surviving (ray, shape) pairs go to a per-warp queue in shared memory;
 //                     whenever 32 are waiting the warp runs 32 exact tests, one per lane,
 //                     with the reference's own operand order (exact.cuh), and folds the
 //                     result into the ray's 64-bit (t, id) key with an integer atomicMin.
 //   phase 3  PLANES   infinite planes have no bound; every ray tests them exactly.
 // The winner is therefore decided by the exact arithmetic alone, in every case.
+//
+// The filter, for a ray (O, d) and a bound (C, R), with dh = d / |d|, L = C - O:
+//     dist^2(C, line) <= R^2   <=>   (L.dh)^2 - |L|^2 + |C|^2  >=  |C|^2 - R^2 =: W
+// and  (L.dh)^2 - |L|^2 + |C|^2 = b^2 + s  with  b = C.dh - O.dh,  s = C.(2 O) - |O|^2:
+// two 3-FMA chains seeded per ray, one FMA to combine, one compare against the per-bound W.
+// The per-ray seed of s also carries the margin  k 2^-24 (|O| + cmax)^2.
+#include <algorithm>
+#include <cfloat>
+
 #include "kernels.h"
 
 namespace rt {
 
-constexpr int SWEEP_BLOCK = 256;
-constexpr int SWEEP_WARPS = SWEEP_BLOCK / 32;
-constexpr int TILE = 1024;  // bounds per shared-memory tile (16 KB)
-constexpr int CHUNK = 128;  // bounds between two queue checks (== BOUND_PAD)
-constexpr int QCAP = 512;   // queued pairs per warp
-static_assert(CHUNK == BOUND_PAD, "bound table padding must match the sweep chunk");
-
-// conservative-filter margin: 128 units of f32 round-off (2^-24) on b^2 and a*|L|^2
-constexpr float FILTER_MARGIN = 128.0f * 5.9604645e-08f;
+constexpr int QCAP = 256;                // queued pairs per warp
+constexpr int CHUNK_PAIRS = SEG_PAD / 2; // slot pairs between two queue checks
+constexpr float U24 = 5.9604645e-08f;    // 2^-24, unit round-off of f32
+constexpr int SMEM_LIMIT = 232448;       // 227 KB opt-in dynamic shared memory per CTA on sm_100
 
 struct RayRegs {
     float ox, oy, oz, dx, dy, dz;
@@ -47,9 +53,10 @@ RT_DEV RayRegs load_ray(const RaySeg &s0, const RaySeg &s1, int gi) {
 }
 
 // One exact (ray, shape) test; returns the key or KEY_MISS.
-RT_DEV unsigned long long exact_pair(const DevScene &sc, int shape, V3 o, V3 d) {
-    int kind = sc.shape_meta[shape].x;
-    const float4 *g = sc.geom + 3 * shape;
+RT_DEV unsigned long long exact_pair(const int4 *shape_meta, const float4 *geom, const float4 *cube_tris, int shape, V3 o,
+                                     V3 d) {
+    int kind = shape_meta[shape].x;
+    const float4 *g = geom + 3 * shape;
     float t;
     if (kind == KIND_SPHERE) {
         bool entering;
@@ -60,18 +67,19 @@ RT_DEV unsigned long long exact_pair(const DevScene &sc, int shape, V3 o, V3 d) 
     } else { // cube
         float u, v, det;
         int which;
-        if (!exact_cube(load_m34(g), sc.cube_tris, o, d, t, which, u, v, det)) return KEY_MISS;
+        if (!exact_cube(load_m34(g), cube_tris, o, d, t, which, u, v, det)) return KEY_MISS;
     }
     return make_key(t, shape);
 }
 
-RT_DEV unsigned long long plane_keys(const DevScene &sc, V3 o, V3 d, unsigned long long best) {
-    for (int p = 0; p < sc.n_planes; ++p) {
-        int shape = sc.plane_shape[p];
-        const float4 *pd = sc.plane_data + 7 * p;
+__device__ __noinline__ unsigned long long plane_keys(int n_planes, const int *plane_shape, const float4 *plane_data,
+                                                      const float4 *geom, V3 o, V3 d, unsigned long long best) {
+    for (int p = 0; p < n_planes; ++p) {
+        int shape = plane_shape[p];
+        const float4 *pd = plane_data + 7 * p;
         float4 po = pd[0], pn = pd[1];
         float t;
-        if (exact_plane(load_m34(sc.geom + 3 * shape), v3(po.x, po.y, po.z), v3(pn.x, pn.y, pn.z), o, d, t)) {
+        if (exact_plane(load_m34(geom + 3 * shape), v3(po.x, po.y, po.z), v3(pn.x, pn.y, pn.z), o, d, t)) {
             unsigned long long k = make_key(t, shape);
             best = k < best ? k : best;
         }
@@ -79,142 +87,212 @@ RT_DEV unsigned long long plane_keys(const DevScene &sc, V3 o, V3 d, unsigned lo
     return best;
 }
 
-template <int R>
-__global__ void __launch_bounds__(SWEEP_BLOCK)
-sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int n_bound_padded, unsigned long long *exact_counter) {
-    __shared__ float4 tile[TILE];
-    __shared__ unsigned int queue[SWEEP_WARPS][QCAP];
-    __shared__ unsigned long long best[SWEEP_WARPS][32 * R];
-    __shared__ int qcount[SWEEP_WARPS];
+// What the exact stage needs, kept in shared memory so that the filter loop holds none of
+// it in registers (and the compiler cannot hoist the loads of these kernel parameters into it).
+struct SweepCtx {
+    RaySeg s0, s1;
+    const int4 *shape_meta;
+    const float4 *geom;
+    const float4 *cube_tris;
+    const int *bound_shape;
+};
+
+// Run queued pairs 32 at a time, one exact test per lane; a partial batch stays queued unless
+// `all`.  Called by a converged warp.  Returns the number of pairs left in the queue.
+__device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueue, unsigned long long *wbest, int ray0,
+                                        int cnt, int all, unsigned int *n_exact) {
+    const int lane = threadIdx.x & 31;
+    int done = 0;
+    while (cnt - done >= 32 || (all && done < cnt)) {
+        int idx = done + lane;
+        if (idx < cnt) {
+            unsigned int pair = wqueue[idx];
+            int local = pair >> 24; // (ray of the warp batch << 24) | bound slot
+            int j = pair & 0xFFFFFF;
+            RayRegs rr = load_ray(ctx->s0, ctx->s1, ray0 + local);
+            unsigned long long k = exact_pair(ctx->shape_meta, ctx->geom, ctx->cube_tris, ctx->bound_shape[j],
+                                              v3(rr.ox, rr.oy, rr.oz), v3(rr.dx, rr.dy, rr.dz));
+            if (k != KEY_MISS) atomicMin(&wbest[local], k);
+        }
+        done += 32;
+    }
+    if (lane == 0) *n_exact += (unsigned int)min(done, cnt);
+    int left = cnt - done;
+    unsigned int keep = 0;
+    if (left > 0 && lane < left) keep = wqueue[done + lane];
+    __syncwarp();
+    if (left > 0 && lane < left) wqueue[lane] = keep;
+    __syncwarp();
+    return left > 0 ? left : 0;
+}
+
+// Filter coefficients of one ray (8 registers).  A ray the filter cannot bound (zero or
+// non-finite direction length, coordinates beyond 1e15) passes every bound; a dead lane or a
+// NaN ray (handled apart, see KEY_NAN_PREFIX) passes none.
+struct RayCoef {
+    float dx, dy, dz, kb, ox2, oy2, oz2, seed;
+};
+
+RT_DEV RayCoef ray_coef(const RayRegs &r, float k_seg, float cmax, bool usable) {
+    RayCoef c;
+    c.dx = c.dy = c.dz = c.kb = c.ox2 = c.oy2 = c.oz2 = 0.f;
+    c.seed = -3.0e38f;
+    if (!usable) return c;
+    float n = sqrtf(fmaf(r.dx, r.dx, fmaf(r.dy, r.dy, r.dz * r.dz)));
+    float o2 = fmaf(r.ox, r.ox, fmaf(r.oy, r.oy, r.oz * r.oz));
+    float lam = (sqrtf(o2) + cmax) * 1.000001f;
+    if (!(n > 0.f) || !(n < 1e18f) || !(lam < 1e15f)) {
+        c.seed = 3.0e38f;
+        return c;
+    }
+    c.dx = __fdiv_rn(r.dx, n); c.dy = __fdiv_rn(r.dy, n); c.dz = __fdiv_rn(r.dz, n);
+    c.kb = -fmaf(r.ox, c.dx, fmaf(r.oy, c.dy, r.oz * c.dz));
+    c.ox2 = 2.f * r.ox; c.oy2 = 2.f * r.oy; c.oz2 = 2.f * r.oz;
+    c.seed = fmaf(k_seg * U24, lam * lam, -o2);
+    return c;
+}
+
+RT_DEV float2 f2(float x) { return make_float2(x, x); }
+
+// One persistent CTA per SM; slots [slot_begin, slot_end) of the bound table stay in shared
+// memory for the whole launch.  Each WARP fetches its own batches of 32 R rays from
+// batch_counter, so no block barrier follows the table load.  `accumulate`: the keys already
+// hold the result of earlier table chunks; `planes`: this launch also tests the planes.
+template <int R, int SWEEP_THREADS>
+__global__ void __launch_bounds__(SWEEP_THREADS, 1)
+sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, int accumulate, int planes,
+             unsigned int *batch_counter, unsigned long long *exact_counter) {
+    constexpr int SWEEP_WARPS = SWEEP_THREADS / 32;
+    constexpr unsigned int FULL = 0xffffffffu;
+    extern __shared__ float4 smem[];
+    __shared__ SweepCtx ctx;
+    __shared__ unsigned int n_exact[SWEEP_WARPS];
+    const int n_tab = slot_end - slot_begin;
+    float4 *tab = smem;                                                         // n_tab slots
+    unsigned long long *best = (unsigned long long *)(smem + n_tab);            // SWEEP_THREADS * R
+    unsigned int *queue = (unsigned int *)(best + SWEEP_THREADS * R);           // SWEEP_WARPS * QCAP
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = s0.n + s1.n;
-    const int block_ray0 = blockIdx.x * R * SWEEP_BLOCK;
+    unsigned long long *wbest = best + warp * (32 * R);
+    unsigned int *wqueue = queue + warp * QCAP;
+    const unsigned int lt_mask = (1u << lane) - 1u;
 
-    // ---- rays into registers --------------------------------------------------------
-    float ox[R], oy[R], oz[R], dx[R], dy[R], dz[R], a1[R], a2[R];
-    bool live[R], nanray[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-        int gi = block_ray0 + r * SWEEP_BLOCK + tid;
-        live[r] = gi < total;
-        nanray[r] = false;
-        RayRegs rr;
-        if (live[r]) {
-            rr = load_ray(s0, s1, gi);
-            nanray[r] = ray_has_nan(rr);
-        }
-        if (!live[r] || nanray[r]) {
-            // dummy ray that passes no bound: far origin, zero direction
-            ox[r] = oy[r] = oz[r] = 1e18f;
-            dx[r] = dy[r] = dz[r] = 0.f;
-            a1[r] = 1.f; a2[r] = 0.f;
-        } else {
-            ox[r] = rr.ox; oy[r] = rr.oy; oz[r] = rr.oz; dx[r] = rr.dx; dy[r] = rr.dy; dz[r] = rr.dz;
-            float a = fmaf(rr.dx, rr.dx, fmaf(rr.dy, rr.dy, rr.dz * rr.dz));
-            a1[r] = a * ((1.f - FILTER_MARGIN) / (1.f + FILTER_MARGIN));
-            a2[r] = a; // a / (1+m) rounded up: errs on the passing side
-        }
-        best[warp][r * 32 + lane] = KEY_MISS;
+    for (int k = tid; k < n_tab; k += SWEEP_THREADS) tab[k] = sc.bound[slot_begin + k];
+    if (tid == 0) {
+        ctx.s0 = s0; ctx.s1 = s1;
+        ctx.shape_meta = sc.shape_meta; ctx.geom = sc.geom; ctx.cube_tris = sc.cube_tris; ctx.bound_shape = sc.bound_shape;
     }
-    if (lane == 0) qcount[warp] = 0;
-    __syncwarp();
+    if (lane == 0) n_exact[warp] = 0;
+    __syncthreads();
+    const float4 *tab0 = tab - slot_begin; // indexed by absolute slot
 
-    unsigned int n_exact = 0;
+    for (;;) {
+        unsigned int batch = 0;
+        if (lane == 0) batch = atomicAdd(batch_counter, 1u);
+        batch = __shfl_sync(FULL, batch, 0);
+        const long long ray0_ll = (long long)batch * (R * 32);
+        if (ray0_ll >= total) break;
+        const int ray0 = (int)ray0_ll;
 
-    // one queued pair: (local ray << 24) | bound index
-    auto run_pair = [&](unsigned int pair) {
-        int local = pair >> 24;
-        int j = pair & 0xFFFFFF;
-        int gi = block_ray0 + (local >> 5) * SWEEP_BLOCK + warp * 32 + (local & 31);
-        RayRegs rr = load_ray(s0, s1, gi);
-        int shape = sc.bound_shape[j];
-        unsigned long long k = exact_pair(sc, shape, v3(rr.ox, rr.oy, rr.oz), v3(rr.dx, rr.dy, rr.dz));
-        if (k != KEY_MISS) atomicMin(&best[warp][local], k);
-    };
-
-    // run queued pairs 32 at a time; keep a partial batch unless `all`
-    auto flush = [&](bool all) {
-        __syncwarp();
-        int cnt = min(*(volatile int *)&qcount[warp], QCAP);
-        int done = 0;
-        while (cnt - done >= 32 || (all && done < cnt)) {
-            int idx = done + lane;
-            if (idx < cnt) { run_pair(queue[warp][idx]); ++n_exact; }
-            done += 32;
-        }
-        int left = cnt - done;
-        unsigned int keep = 0;
-        if (left > 0 && lane < left) keep = queue[warp][done + lane];
-        __syncwarp();
-        if (left > 0 && lane < left) queue[warp][lane] = keep;
-        if (lane == 0) qcount[warp] = left > 0 ? left : 0;
-        __syncwarp();
-    };
-
-    // ---- phase 1 + 2 ------------------------------------------------------------------
-    for (int base = 0; base < n_bound_padded; base += TILE) {
-        __syncthreads();
-        for (int k = tid; k < TILE; k += SWEEP_BLOCK)
-            if (base + k < n_bound_padded) tile[k] = sc.bound[base + k];
-        __syncthreads();
-        const int tile_n = min(TILE, n_bound_padded - base);
-        for (int c0 = 0; c0 < tile_n; c0 += CHUNK) {
-#pragma unroll 4
-            for (int k = c0; k < c0 + CHUNK; ++k) {
-                const float4 B = tile[k];
-                bool pass[R];
-                bool any = false;
+        // vmask bits 2r, 2r+1: ray r of this lane exists and has no NaN component (it can be
+        // queued); nanmask bit r: it exists and has one
+        unsigned int vmask = 0, nanmask = 0;
 #pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    float lx = B.x - ox[r], ly = B.y - oy[r], lz = B.z - oz[r];
-                    float b = fmaf(lz, dz[r], fmaf(ly, dy[r], lx * dx[r]));
-                    float ll = fmaf(lz, lz, fmaf(ly, ly, lx * lx));
-                    // b^2 (1+m) - a |L|^2 (1-m) + a R^2 >= 0, divided through by (1+m)
-                    float t = fmaf(a2[r], B.w, fmaf(-a1[r], ll, b * b));
-                    pass[r] = t >= 0.f;
-                    any |= pass[r];
-                }
-                if (any) {
+        for (int r = 0; r < R; ++r) {
+            int gi = ray0 + r * 32 + lane;
+            unsigned long long k0 = KEY_MISS;
+            if (gi < total) {
+                if (ray_has_nan(load_ray(s0, s1, gi))) nanmask |= 1u << r;
+                else vmask |= 3u << (2 * r);
+                if (accumulate) k0 = gi < s0.n ? s0.key[gi] : s1.key[gi - s0.n];
+            }
+            wbest[r * 32 + lane] = k0;
+        }
+        __syncwarp();
+        int qn = 0; // queued pairs of this warp (warp-uniform)
+
+        // ---- phase 1 + 2 --------------------------------------------------------------
+        for (int g = 0; g < sc.segs.n; ++g) {
+            const int gb = max(sc.segs.begin[g], slot_begin), ge = min(sc.segs.end[g], slot_end);
+            if (gb >= ge) continue;
+            RayCoef c[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                bool usable = (vmask >> (2 * r)) & 1u;
+                RayRegs rr;
+                rr.ox = rr.oy = rr.oz = rr.dx = rr.dy = rr.dz = 0.f;
+                if (usable) rr = load_ray(s0, s1, ray0 + r * 32 + lane);
+                c[r] = ray_coef(rr, sc.segs.k[g], sc.cmax, usable);
+            }
+            for (int j0 = gb; j0 < ge; j0 += 2 * CHUNK_PAIRS) {
+                const float4 *tp = tab0 + j0;
+#pragma unroll 4
+                for (int i = 0; i < CHUNK_PAIRS; ++i) {
+                    const float4 T0 = tp[2 * i], T1 = tp[2 * i + 1];
+                    const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
+                    float2 e[R];
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
-                        if (pass[r]) {
-                            unsigned int pair = ((unsigned int)(r * 32 + lane) << 24) | (unsigned int)(base + k);
-                            int slot = atomicAdd(&qcount[warp], 1);
-                            if (slot < QCAP) queue[warp][slot] = pair;
-                            else { run_pair(pair); ++n_exact; } // queue full: resolve in place
+                        float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
+                        float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2), f2(c[r].seed))));
+                        e[r] = __ffma2_rn(b, b, s);
+                    }
+                    float m0 = e[0].x, m1 = e[0].y;
+#pragma unroll
+                    for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
+                    if (__any_sync(FULL, m0 >= T1.z || m1 >= T1.w)) { // warp-uniform: some lane has a candidate
+                        unsigned int mask = 0;
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            if (e[r].x >= T1.z) mask |= 1u << (2 * r);
+                            if (e[r].y >= T1.w) mask |= 2u << (2 * r);
+                        }
+                        mask &= vmask;
+                        unsigned int ball;
+                        while ((ball = __ballot_sync(FULL, mask != 0)) != 0) { // one queue slot per lane per round
+                            if (qn > QCAP - 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
+                            if (mask) {
+                                int bit = __ffs(mask) - 1;
+                                mask &= mask - 1;
+                                unsigned int local = (unsigned int)((bit >> 1) * 32 + lane);
+                                wqueue[qn + __popc(ball & lt_mask)] = (local << 24) | (unsigned int)(j0 + 2 * i + (bit & 1));
+                            }
+                            qn += __popc(ball);
+                            __syncwarp();
                         }
                     }
                 }
+                if (qn >= 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
             }
-            __syncwarp();
-            if (*(volatile int *)&qcount[warp] >= 32) flush(false);
         }
-    }
-    flush(true);
+        __syncwarp();
+        sweep_flush(&ctx, wqueue, wbest, ray0, qn, 1, &n_exact[warp]);
 
-    // ---- phase 3 + output ---------------------------------------------------------------
+        // ---- phase 3 + output -----------------------------------------------------------
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-        int gi = block_ray0 + r * SWEEP_BLOCK + tid;
-        if (!live[r]) continue;
-        unsigned long long k;
-        if (nanray[r]) {
-            k = sc.first_nan_shape >= 0
-                    ? (((unsigned long long)KEY_NAN_PREFIX << 32) | (unsigned long long)(uint32_t)sc.first_nan_shape)
-                    : KEY_MISS;
-        } else {
-            k = best[warp][r * 32 + lane];
-            k = plane_keys(sc, v3(ox[r], oy[r], oz[r]), v3(dx[r], dy[r], dz[r]), k);
+        for (int r = 0; r < R; ++r) {
+            int gi = ray0 + r * 32 + lane;
+            if (gi >= total) continue;
+            unsigned long long k;
+            if ((nanmask >> r) & 1u) {
+                k = sc.first_nan_shape >= 0
+                        ? (((unsigned long long)KEY_NAN_PREFIX << 32) | (unsigned long long)(uint32_t)sc.first_nan_shape)
+                        : KEY_MISS;
+            } else {
+                k = wbest[r * 32 + lane];
+                if (planes) {
+                    RayRegs rr = load_ray(s0, s1, gi);
+                    k = plane_keys(sc.n_planes, sc.plane_shape, sc.plane_data, sc.geom, v3(rr.ox, rr.oy, rr.oz),
+                                   v3(rr.dx, rr.dy, rr.dz), k);
+                }
+            }
+            if (gi < s0.n) s0.key[gi] = k;
+            else s1.key[gi - s0.n] = k;
         }
-        if (gi < s0.n) s0.key[gi] = k;
-        else s1.key[gi - s0.n] = k;
+        __syncwarp();
     }
-    if (exact_counter) {
-        unsigned int tot = n_exact;
-        for (int off = 16; off > 0; off >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, off);
-        if (lane == 0 && tot) atomicAdd(exact_counter, (unsigned long long)tot);
-    }
+    if (exact_counter && lane == 0 && n_exact[warp]) atomicAdd(exact_counter, (unsigned long long)n_exact[warp]);
 }
 
 // ---- audit: every pair exact, in shape order (what the reference literally does) --------
@@ -230,30 +308,71 @@ sweep_all_pairs_kernel(DevScene sc, RaySeg s0, RaySeg s1, unsigned long long *ex
         if (sc.first_nan_shape >= 0)
             best = ((unsigned long long)KEY_NAN_PREFIX << 32) | (unsigned long long)(uint32_t)sc.first_nan_shape;
     } else {
-        for (int j = 0; j < sc.n_bounded; ++j) {
-            unsigned long long k = exact_pair(sc, sc.bound_shape[j], o, d);
+        for (int j = 0; j < sc.n_slots; ++j) {
+            int shape = sc.bound_shape[j];
+            if (shape < 0) continue;
+            unsigned long long k = exact_pair(sc.shape_meta, sc.geom, sc.cube_tris, shape, o, d);
             best = k < best ? k : best;
         }
-        best = plane_keys(sc, o, d, best);
+        best = plane_keys(sc.n_planes, sc.plane_shape, sc.plane_data, sc.geom, o, d, best);
     }
     if (gi < s0.n) s0.key[gi] = best;
     else s1.key[gi - s0.n] = best;
     (void)exact_counter; // rays x n_bounded, added by the host
 }
 
-static int padded(int n) { return (n + BOUND_PAD - 1) / BOUND_PAD * BOUND_PAD; }
+template <int R, int T> static size_t sweep_smem_fixed() {
+    return (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int);
+}
 
-void launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, int rays_per_thread, unsigned long long *exact_counter,
-                  cudaStream_t stream) {
-    long long total = (long long)s0.n + s1.n;
-    if (total <= 0) return;
-    int nb = padded(sc.n_bounded);
-    auto blocks = [&](int r) { return (unsigned int)((total + (long long)r * SWEEP_BLOCK - 1) / ((long long)r * SWEEP_BLOCK)); };
-    switch (rays_per_thread) {
-    case 1: sweep_kernel<1><<<blocks(1), SWEEP_BLOCK, 0, stream>>>(sc, s0, s1, nb, exact_counter); break;
-    case 2: sweep_kernel<2><<<blocks(2), SWEEP_BLOCK, 0, stream>>>(sc, s0, s1, nb, exact_counter); break;
-    default: sweep_kernel<4><<<blocks(4), SWEEP_BLOCK, 0, stream>>>(sc, s0, s1, nb, exact_counter); break;
+// Bound slots one launch can keep in shared memory.
+template <int R, int T> static int sweep_table_cap() {
+    return (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T>()) / sizeof(float4)) / SEG_PAD * SEG_PAD;
+}
+
+template <int R, int T>
+static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, long long total, int sm_count,
+                                  unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
+                                  cudaStream_t stream) {
+    constexpr int SWEEP_WARPS = T / 32;
+    const int cap = sweep_table_cap<R, T>();
+    const int n_chunks = std::max(1, (sc.n_slots + cap - 1) / cap);
+    if (n_chunks > n_counters) return cudaErrorInvalidValue;
+    long long batches = (total + 32ll * R - 1) / (32ll * R);
+    unsigned int grid = (unsigned int)std::min<long long>((batches + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)sm_count);
+    for (int c = 0; c < n_chunks; ++c) {
+        // chunks of equal size (rounded to SEG_PAD) rather than cap, cap, ..., rest
+        int per = ((sc.n_slots + n_chunks - 1) / n_chunks + SEG_PAD - 1) / SEG_PAD * SEG_PAD;
+        int b = c * per, e = std::min(sc.n_slots, b + per);
+        const size_t smem = (size_t)std::max(e - b, 1) * sizeof(float4) + sweep_smem_fixed<R, T>();
+        cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess) return err;
+        sweep_kernel<R, T><<<grid, T, smem, stream>>>(sc, s0, s1, b, e, c > 0 ? 1 : 0, c == n_chunks - 1 ? 1 : 0,
+                                                               batch_counters + c, exact_counter);
+        if ((err = cudaGetLastError()) != cudaSuccess) return err;
     }
+    *used = n_chunks;
+    return cudaSuccess;
+}
+
+cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, int rays_per_thread, int sm_count,
+                         unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
+                         cudaStream_t stream) {
+    long long total = (long long)s0.n + s1.n;
+    *used = 0;
+    if (total <= 0) return cudaSuccess;
+    if (sm_count < 1) sm_count = 1;
+    int r = rays_per_thread;
+    if (r <= 0) { // enough warp batches to balance the SMs, else fewer rays per thread
+        const long long want = 4ll * sm_count * 16;
+        r = 4;
+        while (r > 1 && (total + 32ll * r - 1) / (32ll * r) < want) r >>= 1;
+    }
+#define RT_SWEEP(R_, T_) launch_sweep_r<R_, T_>(sc, s0, s1, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
+    if (r >= 4) return RT_SWEEP(4, 512); // 16 warps x <= 128 registers; more warps spill the filter loop
+    if (r >= 2) return RT_SWEEP(2, 512);
+    return RT_SWEEP(1, 512);
+#undef RT_SWEEP
 }
 
 void launch_sweep_all_pairs(const DevScene &sc, RaySeg s0, RaySeg s1, unsigned long long *exact_counter,
