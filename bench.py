@@ -278,15 +278,24 @@ def run_ours(args, wl):
     measured_peak, sms, khz = rt.measure_fp32_peak(local)
     nominal_peak = sms * 128 * 2 * khz * 1e3 / 1e12
     achieved = sweep_flops / (sweep_ms * 1e-3) / 1e12 if sweep_ms > 0 else 0.0
-    # what the kernel really executes per pair in its filter: 3 FADD + 2 FMUL + 7 FFMA = 19 flop
-    # (sweep.cu phase 1), plus the exact tests (<1% of pairs)
-    executed = (pairs * 19.0) / (sweep_ms * 1e-3) / 1e12 if sweep_ms > 0 else 0.0
+    # what the kernel really executes per (ray, bound) pair in its filter: 7 FMA = 14 flop, as 3.5
+    # packed FFMA2 (sweep.cu phase 1), plus the exact tests (~0.2% of pairs)
+    executed = (pairs * 14.0) / (sweep_ms * 1e-3) / 1e12 if sweep_ms > 0 else 0.0
+    traffic = None  # dram bytes of the largest sweep launch, from the committed ncu --set full capture
+    try:
+        with open(os.path.join(ROOT, "profiles", "sweep_ncu_summary.json")) as fh:
+            prof = json.load(fh)
+        if prof.get("workload") == args.workload:
+            traffic = prof.get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        pass
     roofline = {
         "bound": "fp32", "kernel": "sweep_kernel", "achieved": achieved, "peak": measured_peak, "unit": "TFLOP/s",
-        "frac": achieved / measured_peak if measured_peak else None, "traffic": None,
+        "frac": achieved / measured_peak if measured_peak else None, "traffic": traffic,
         "peak_source": "rt_measure_fp32_peak FFMA micro-kernel on this GPU (MEASURED_PEAKS.json has no FP32 figure); "
                        "nominal %d SMs x 128 x 2 x %.0f MHz = %.1f TFLOP/s" % (sms, khz / 1e3, nominal_peak),
-        "achieved_is": "algorithmic flops credited per SURVEY 8d (54/sphere, 30/triangle pair) / sweep time",
+        "achieved_is": "algorithmic flops credited per SURVEY 8d (54 per ray x sphere, 30 per ray x triangle pair resolved) "
+                       "/ sweep time; the kernel itself executes 14 flop per pair (executed_tflops)",
         "executed_tflops": executed, "executed_frac": executed / measured_peak if measured_peak else None,
         "pairs_per_s": pairs / (sweep_ms * 1e-3) if sweep_ms > 0 else None,
         "sweep_ms_per_step": sweep_ms, "sweep_share_of_step": sweep_ms / total_ms if total_ms else None,

@@ -199,6 +199,9 @@ int rt_scene_update_materials(rt_scene *scene, const rt_material *materials, int
  * bracket the work; NULL restores the scene's private stream.  Calls stay synchronous.   */
 int rt_scene_set_stream(rt_scene *scene, void *stream);
 void rt_scene_destroy(rt_scene *scene);
+/* Destroyed scenes and forests leave their ray pools (device memory) cached, one set per
+ * device, for the next scene; rt_trim frees the cache of `device` (-1: every device).     */
+int rt_trim(int32_t device);
 
 /* ---- Basic renderer ------------------------------------------------------------------ */
 

@@ -115,10 +115,11 @@ class Scene:
         check(lib().rt_scene_update_materials(self._h, materials, len(materials)))
 
     def render(self, width, height, depth, spp=1, seed=0, rank=0, world=1, rows_per_tile=8, flags=0,
-               want_f32=True, want_u8=True, out_u8=None):
+               want_f32=True, want_u8=True, out_u8=None, cam=None):
         """Returns (rgb_f32 | None, rgb_u8 | None, stats dict); arrays are [rows, width, 3].
-        out_u8: caller-owned uint8 array of that shape to fill (e.g. a view of pinned memory)."""
-        cam = camera(width, height)
+        out_u8: caller-owned uint8 array of that shape to fill (e.g. a view of pinned memory).
+        cam: an abi.rt_camera to use instead of Camera::new(width, height)."""
+        cam = cam if cam is not None else camera(width, height)
         p = _params(depth, spp, seed, rank, world, rows_per_tile, flags)
         n_rows = len(tile_rows(height, rank, world, rows_per_tile))
         f = np.zeros((n_rows, width, 3), dtype=np.float32) if want_f32 else None
@@ -218,6 +219,11 @@ class Forest:
             self.close()
         except Exception:
             pass
+
+
+def trim(device=-1):
+    """Free the ray pools cached from destroyed scenes (rt_trim); -1 = every device."""
+    check(lib().rt_trim(device))
 
 
 def measure_fp32_peak(device=0):

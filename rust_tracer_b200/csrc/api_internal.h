@@ -36,6 +36,12 @@ struct Workspace {
     void release();
 };
 
+// One released workspace per device is kept instead of freed: its ray pools are gigabytes,
+// and cudaMalloc / cudaFree of them would dominate a create -> render -> destroy call.
+// rt_trim() frees the cache.
+Workspace workspace_take_cached(int device);
+void workspace_give_cached(int device, Workspace &ws);
+
 } // namespace rt
 
 struct rt_scene {

@@ -6,6 +6,7 @@
 #include <climits>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "api_internal.h"
@@ -50,6 +51,48 @@ void Workspace::release() {
     cudaFree(batch_counters); batch_counters = nullptr;
     cudaFree(out_f32); cudaFree(out_u8);
     out_f32 = out_u8 = nullptr; out_f32_cap = out_u8_cap = 0;
+}
+
+// ---- per-device cache of one released workspace --------------------------------------------
+namespace {
+constexpr int MAX_CACHED_DEVICES = 64;
+std::mutex g_cache_mu;
+Workspace g_cache[MAX_CACHED_DEVICES];
+bool g_cache_full[MAX_CACHED_DEVICES];
+long long ws_weight(const Workspace &w) { return (long long)w.pools.t_cap + w.pools.s_cap + w.sample_cap; }
+} // namespace
+
+Workspace workspace_take_cached(int device) {
+    Workspace w;
+    if (device < 0 || device >= MAX_CACHED_DEVICES) return w;
+    std::lock_guard<std::mutex> lock(g_cache_mu);
+    if (g_cache_full[device]) {
+        w = g_cache[device];
+        g_cache[device] = Workspace();
+        g_cache_full[device] = false;
+    }
+    return w;
+}
+
+// Caller has made `device` current.
+void workspace_give_cached(int device, Workspace &ws) {
+    Workspace drop;
+    {
+        std::lock_guard<std::mutex> lock(g_cache_mu);
+        if (device < 0 || device >= MAX_CACHED_DEVICES) {
+            drop = ws;
+        } else if (!g_cache_full[device]) {
+            g_cache[device] = ws;
+            g_cache_full[device] = true;
+        } else if (ws_weight(g_cache[device]) < ws_weight(ws)) {
+            drop = g_cache[device];
+            g_cache[device] = ws;
+        } else {
+            drop = ws;
+        }
+    }
+    ws = Workspace();
+    drop.release();
 }
 
 int Workspace::ensure_pools(long long t_cap, long long s_cap) {
@@ -434,6 +477,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
     rt_forest *f = new (std::nothrow) rt_forest();
     if (!f) return fail(RT_ERR_NOMEM, "out of host memory");
     f->scene = scene;
+    f->ws = workspace_take_cached(scene->device);
     Workspace &ws = f->ws;
     std::vector<int> rows;
     if ((rc = ws.ensure_misc()) != RT_OK || (rc = upload_rows(scene, ws, camera, params, rows)) != RT_OK) {
@@ -493,9 +537,26 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
 
 void rt_forest_destroy(rt_forest *forest) {
     if (!forest) return;
-    if (forest->scene) cudaSetDevice(forest->scene->device);
-    forest->ws.release();
+    if (forest->scene) {
+        cudaSetDevice(forest->scene->device);
+        workspace_give_cached(forest->scene->device, forest->ws);
+    } else {
+        forest->ws.release();
+    }
     delete forest;
+}
+
+int rt_trim(int32_t device) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    for (int d = 0; d < ndev; ++d) {
+        if (device >= 0 && d != device) continue;
+        Workspace w = workspace_take_cached(d);
+        CK(cudaSetDevice(d), "cudaSetDevice");
+        w.release();
+    }
+    return RT_OK;
 }
 
 // shared by rt_forest_eval / rt_forest_eval_filtered

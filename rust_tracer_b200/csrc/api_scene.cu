@@ -391,6 +391,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         return cuda_fail(e, "cudaStreamCreate");
     }
     s->own_stream = s->stream;
+    s->ws = workspace_take_cached(device);
     *out = s;
     return RT_OK;
 }
@@ -419,7 +420,7 @@ int rt_scene_update_materials(rt_scene *scene, const rt_material *materials, int
 void rt_scene_destroy(rt_scene *scene) {
     if (!scene) return;
     cudaSetDevice(scene->device);
-    scene->ws.release();
+    workspace_give_cached(scene->device, scene->ws);
     for (void *p : scene->allocs) cudaFree(p);
     if (scene->own_stream) cudaStreamDestroy(scene->own_stream);
     delete scene;

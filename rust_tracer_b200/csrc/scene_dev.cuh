@@ -44,7 +44,7 @@ struct DevLight { // 32 bytes
     int point_index; // index among the point lights (shadow slot), -1 for ambient lights
 };
 
-constexpr int SEG_PAD = 64;   // every segment of the bound table is a multiple of this many slots
+constexpr int SEG_PAD = 16;   // every segment of the bound table is a multiple of this many slots
 constexpr int MAX_SEGS = 4;
 
 // Bound slots [begin, end) share one margin factor k: a ray passes slot j iff

@@ -25,6 +25,7 @@
 // The per-ray seed of s also carries the margin  k 2^-24 (|O| + cmax)^2.
 #include <algorithm>
 #include <cfloat>
+#include <cstdlib>
 
 #include "kernels.h"
 
@@ -225,11 +226,16 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
                 if (usable) rr = load_ray(s0, s1, ray0 + r * 32 + lane);
                 c[r] = ray_coef(rr, sc.segs.k[g], sc.cmax, usable);
             }
+            float4 N0 = tab0[gb], N1 = tab0[gb + 1]; // next slot pair, fetched one iteration ahead
             for (int j0 = gb; j0 < ge; j0 += 2 * CHUNK_PAIRS) {
                 const float4 *tp = tab0 + j0;
 #pragma unroll 4
                 for (int i = 0; i < CHUNK_PAIRS; ++i) {
-                    const float4 T0 = tp[2 * i], T1 = tp[2 * i + 1];
+                    const float4 T0 = N0, T1 = N1;
+                    {   // the last prefetch of a segment re-reads its first pair instead of running past the table
+                        const float4 *np = (j0 + 2 * i + 2 < ge) ? tp + 2 * i + 2 : tab0 + gb;
+                        N0 = np[0]; N1 = np[1];
+                    }
                     const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
                     float2 e[R];
 #pragma unroll
@@ -335,7 +341,11 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, long
                                   unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
                                   cudaStream_t stream) {
     constexpr int SWEEP_WARPS = T / 32;
-    const int cap = sweep_table_cap<R, T>();
+    int cap = sweep_table_cap<R, T>();
+    if (const char *e = std::getenv("RT_B200_TABLE_CAP")) { // test knob: force several table chunks
+        int v = std::atoi(e) / SEG_PAD * SEG_PAD;
+        if (v >= SEG_PAD && v < cap) cap = v;
+    }
     const int n_chunks = std::max(1, (sc.n_slots + cap - 1) / cap);
     if (n_chunks > n_counters) return cudaErrorInvalidValue;
     long long batches = (total + 32ll * R - 1) / (32ll * R);

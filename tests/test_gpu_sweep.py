@@ -1,0 +1,150 @@
+"""GPU tests of the sweep kernel's own machinery (rust_tracer_b200/csrc/sweep.cu): the
+conservative bound filter must never change the result of Scene::intersect's linear scan
+(reference src/scene/mod.rs:98-116), whatever path a (ray, shape) pair takes through it --
+several shared-memory chunks of the bound table, a full candidate queue, rays or bounds the
+filter cannot bound, anisotropic-transform segments.  Every case is checked against the
+all-pairs audit (every pair through the exact test) and, where the oracle finishes in
+seconds, against the oracle.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import orc
+import rust_tracer_b200 as rt
+from rust_tracer_b200 import abi
+
+pytestmark = pytest.mark.gpu
+
+
+def _render_pair(desc, w, h, depth, cam=None):
+    sc = rt.Scene(desc)
+    try:
+        a = sc.render(w, h, depth, cam=cam)
+        b = sc.render(w, h, depth, cam=cam, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS)
+    finally:
+        sc.close()
+    return a, b
+
+
+def _assert_same(a, b):
+    (f1, u1, s1), (f2, u2, s2) = a, b
+    assert np.array_equal(f1, f2, equal_nan=True)
+    assert (u1 == u2).all()
+    assert s1["rays"] == s2["rays"] and s1["nodes"] == s2["nodes"]
+
+
+def _sphere(L, tx, ty, tz, sx, sy, sz, material, rz=0.0):
+    s = abi.rt_shape()
+    s.kind, s.material = abi.RT_SHAPE_SPHERE, material
+    m = (C.c_float * 16)()
+    L.rt_matrix_compose(*[C.c_float(v) for v in (tx, ty, tz, 0.0, 0.0, rz, sx, sy, sz)], m)
+    inv = (C.c_float * 16)()
+    assert L.rt_matrix_inverse(m, inv) == 0
+    s.transform[:] = list(m)
+    s.inv_transform[:] = list(inv)
+    return s
+
+
+def _scene_with_spheres(spheres):
+    base = rt.SceneDesc.builtin("default")
+    n = len(spheres)
+    shapes = (abi.rt_shape * (n + 1))(*spheres, base.desc.shapes[4])  # + the checkerboard floor
+    shapes[n].material = 3
+    mats = (abi.rt_material * 4)(base.desc.materials[0], base.desc.materials[1], base.desc.materials[2],
+                                 base.desc.materials[4])
+    lights = (abi.rt_light * 3)(*[base.desc.lights[i] for i in range(3)])
+    return rt.SceneDesc.from_arrays(shapes, mats, lights, (0.1, 0.1, 0.1)), base
+
+
+def test_chunked_bound_table_equals_resident_table(monkeypatch):
+    """A bound table larger than shared memory is swept in chunks, one launch each, the keys
+    accumulating in global memory; forced here with a tiny chunk size."""
+    desc = rt.SceneDesc.synthetic(400, 400, 4242, 0.03, 0.1)
+    w, h = 192, 108
+    sc = rt.Scene(desc)
+    f0, u0, s0 = sc.render(w, h, 5)
+    monkeypatch.setenv("RT_B200_TABLE_CAP", "128")
+    f1, u1, s1 = sc.render(w, h, 5)
+    monkeypatch.delenv("RT_B200_TABLE_CAP")
+    sc.close()
+    assert np.array_equal(f0, f1, equal_nan=True) and (u0 == u1).all()
+    assert s0["rays"] == s1["rays"] and s0["exact_tests"] == s1["exact_tests"]
+    assert s1["kernel_launches"] > s0["kernel_launches"]  # the chunks really were separate launches
+    of, ou, oc = orc.render(desc.desc, abi.default_camera(w, h), 5)
+    assert (u1 == ou).all() and s1["rays"] == oc.rays
+
+
+def test_full_candidate_queue_is_flushed_not_dropped():
+    """700 nested spheres: every ray through the middle passes every bound, far more than a
+    warp's queue holds between two scheduled flushes."""
+    L = rt.lib()
+    spheres = [_sphere(L, 0.0, 0.0, 1.0, 0.3 + 0.002 * i, 0.3 + 0.002 * i, 0.3 + 0.002 * i, i % 3) for i in range(700)]
+    desc, _keep = _scene_with_spheres(spheres)
+    w, h = 64, 36
+    a, b = _render_pair(desc, w, h, 3)
+    _assert_same(a, b)
+    assert a[2]["exact_tests"] > 100 * a[2]["rays"] // 4  # the filter let the nest through
+    of, ou, oc = orc.render(desc.desc, abi.default_camera(w, h), 3)
+    assert (a[1] == ou).all() and a[2]["rays"] == oc.rays
+
+
+def test_rays_the_filter_cannot_bound_pass_every_shape():
+    """A camera 4e15 away: |O| + cmax is beyond the filter's f32 range, so its rays must be
+    handed to the exact test for every shape instead of being filtered."""
+    desc = rt.SceneDesc.synthetic(60, 40, 77, 0.05, 0.2)
+    w, h = 48, 27
+    cam = abi.default_camera(w, h)
+    cam.origin[:] = [0.0, 0.0, -4.0e15]
+    a, b = _render_pair(desc, w, h, 3, cam=cam)
+    _assert_same(a, b)
+    of, ou, oc = orc.render(desc.desc, cam, 3)
+    assert (a[1] == ou).all() and a[2]["rays"] == oc.rays
+
+
+def test_bound_beyond_the_filter_range_is_always_a_candidate():
+    """One sphere of radius 3e15 around everything: its slot carries W = -FLT_MAX."""
+    L = rt.lib()
+    spheres = [_sphere(L, 0.0, 0.0, 0.0, 3.0e15, 3.0e15, 3.0e15, 2),
+               _sphere(L, -1.0, 0.0, 0.0, 1.0, 0.25, 1.0, 0, rz=75.0), _sphere(L, 1.0, -1.0, 0.0, 1.0, 1.0, 1.0, 1)]
+    desc, _keep = _scene_with_spheres(spheres)
+    w, h = 64, 36
+    a, b = _render_pair(desc, w, h, 4)
+    _assert_same(a, b)
+    of, ou, oc = orc.render(desc.desc, abi.default_camera(w, h), 4)
+    assert (a[1] == ou).all() and a[2]["rays"] == oc.rays
+
+
+def test_anisotropic_and_similarity_spheres_use_separate_segments():
+    """Spheres squashed up to 16:1 go to the segment with the larger margin; images still equal
+    the audit and the oracle."""
+    L = rt.lib()
+    rng = np.random.default_rng(5)
+    spheres = []
+    for i in range(150):
+        c = rng.uniform([-3, -1.5, -1], [3, 2.5, 5])
+        r = float(rng.uniform(0.05, 0.3))
+        if i % 2:
+            spheres.append(_sphere(L, *c, r, r / float(rng.uniform(2, 16)), r, i % 3, rz=float(rng.uniform(0, 180))))
+        else:
+            spheres.append(_sphere(L, *c, r, r, r, i % 3))
+    desc, _keep = _scene_with_spheres(spheres)
+    w, h = 160, 90
+    a, b = _render_pair(desc, w, h, 4)
+    _assert_same(a, b)
+    of, ou, oc = orc.render(desc.desc, abi.default_camera(w, h), 4)
+    assert (a[1] == ou).all() and a[2]["rays"] == oc.rays
+
+
+def test_ray_pools_are_reused_across_scenes_and_trim_frees_them():
+    desc = rt.SceneDesc.builtin("default")
+    _, u0, _ = rt.Scene(desc).render(96, 54, 5, want_f32=False)
+    for _ in range(3):  # create -> render -> destroy, pools handed from scene to scene
+        sc = rt.Scene(desc)
+        _, u, _ = sc.render(96, 54, 5, want_f32=False)
+        sc.close()
+        assert (u == u0).all()
+    rt.trim()
+    _, u, _ = rt.Scene(desc).render(96, 54, 5, want_f32=False)
+    assert (u == u0).all()
