@@ -111,8 +111,27 @@ def oracle_rate(desc, wl, seconds, threads):
     return c.rays / dt / 1e6, sample, int(c.rays), dt
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout; libraries (NCCL prints its version banner on
+    fd 1) must not add to it.  Everything written to fd 1 from here on goes to stderr; emit()
+    writes to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
 def emit(obj):
-    print(json.dumps(obj), flush=True)
+    line = json.dumps(obj) + "\n"
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line)
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line.encode())
 
 
 def run_reference(args, wl):
@@ -329,6 +348,7 @@ def run_ours(args, wl):
 
 def main():
     args = parse_args()
+    quiet_stdout()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, wl)

@@ -4,6 +4,7 @@
 // then shade from the deepest level up and resolve to RGB.
 #include <algorithm>
 #include <climits>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -181,6 +182,7 @@ struct BandLevels {
 struct Accum {
     unsigned long long tree_rays = 0, shadow_rays = 0, nodes = 0, exact = 0;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> sweep_spans;
+    std::vector<long long> sweep_rays; // rays of each span (RT_B200_TRACE)
 };
 
 static int env_int(const char *name, int dflt, int lo, int hi) {
@@ -231,6 +233,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         }
         cudaEventRecord(e1, st);
         acc.sweep_spans.push_back({e0, e1});
+        acc.sweep_rays.push_back((long long)a.n + b.n);
         scene->launches += 1;
         if (audit) acc.exact += (unsigned long long)(a.n + b.n) * (unsigned long long)sc.n_bounded;
     };
@@ -405,11 +408,16 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
         fill_stats(scene, acc, (unsigned long long)n_pixels, stats);
         float ms = 0.f, sweep = 0.f;
         cudaEventElapsedTime(&ms, ev0, ev1);
-        for (auto &sp : acc.sweep_spans) {
+        const bool trace = std::getenv("RT_B200_TRACE") != nullptr;
+        for (size_t i = 0; i < acc.sweep_spans.size(); ++i) {
             float t = 0.f;
-            cudaEventElapsedTime(&t, sp.first, sp.second);
+            cudaEventElapsedTime(&t, acc.sweep_spans[i].first, acc.sweep_spans[i].second);
             sweep += t;
+            if (trace)
+                std::fprintf(stderr, "[rt_b200] sweep %zu: %lld rays %.3f ms (%.2f Tpairs/s)\n", i, acc.sweep_rays[i], t,
+                             (double)acc.sweep_rays[i] * scene->dev.n_bounded / (t * 1e-3) / 1e12);
         }
+        if (trace) std::fprintf(stderr, "[rt_b200] frame %.3f ms, sweeps %.3f ms\n", ms, sweep);
         stats->total_ms = ms;
         stats->sweep_ms = sweep;
         stats->shade_ms = ms - sweep;

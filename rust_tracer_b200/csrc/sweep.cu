@@ -34,6 +34,7 @@ namespace rt {
 constexpr int QCAP = 256;                // queued pairs per warp
 constexpr int CHUNK_PAIRS = SEG_PAD / 2; // slot pairs between two queue checks
 constexpr float U24 = 5.9604645e-08f;    // 2^-24, unit round-off of f32
+constexpr int MIN_SLICE_SLOTS = 256;     // smallest table slice of a work item
 constexpr int SMEM_LIMIT = 232448;       // 227 KB opt-in dynamic shared memory per CTA on sm_100
 
 struct RayRegs {
@@ -156,13 +157,16 @@ RT_DEV RayCoef ray_coef(const RayRegs &r, float k_seg, float cmax, bool usable) 
 RT_DEV float2 f2(float x) { return make_float2(x, x); }
 
 // One persistent CTA per SM; slots [slot_begin, slot_end) of the bound table stay in shared
-// memory for the whole launch.  Each WARP fetches its own batches of 32 R rays from
-// batch_counter, so no block barrier follows the table load.  `accumulate`: the keys already
-// hold the result of earlier table chunks; `planes`: this launch also tests the planes.
+// memory for the whole launch.  A work item is (batch of 32 R rays) x (slice of the resident
+// slots); each WARP fetches its own items from batch_counter, so no block barrier follows the
+// table load, and small launches still spread over every warp of the GPU (n_slices > 1).
+// `merge`: keys are folded into global memory with atomicMin (they were initialised to
+// KEY_MISS or hold the result of earlier table chunks) instead of stored; `planes`: this
+// launch also tests the planes (slice 0 does).
 template <int R, int SWEEP_THREADS>
 __global__ void __launch_bounds__(SWEEP_THREADS, 1)
-sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, int accumulate, int planes,
-             unsigned int *batch_counter, unsigned long long *exact_counter) {
+sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, int n_slices, int slice_slots, int merge,
+             int planes, unsigned int *batch_counter, unsigned long long *exact_counter) {
     constexpr int SWEEP_WARPS = SWEEP_THREADS / 32;
     constexpr unsigned int FULL = 0xffffffffu;
     extern __shared__ float4 smem[];
@@ -189,12 +193,15 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
     const float4 *tab0 = tab - slot_begin; // indexed by absolute slot
 
     for (;;) {
-        unsigned int batch = 0;
-        if (lane == 0) batch = atomicAdd(batch_counter, 1u);
-        batch = __shfl_sync(FULL, batch, 0);
+        unsigned int item = 0;
+        if (lane == 0) item = atomicAdd(batch_counter, 1u);
+        item = __shfl_sync(FULL, item, 0);
+        const unsigned int batch = item / (unsigned int)n_slices;
+        const int slice = (int)(item - batch * (unsigned int)n_slices);
         const long long ray0_ll = (long long)batch * (R * 32);
         if (ray0_ll >= total) break;
         const int ray0 = (int)ray0_ll;
+        const int sb = slot_begin + slice * slice_slots, se = min(slot_end, sb + slice_slots);
 
         // vmask bits 2r, 2r+1: ray r of this lane exists and has no NaN component (it can be
         // queued); nanmask bit r: it exists and has one
@@ -202,20 +209,18 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             int gi = ray0 + r * 32 + lane;
-            unsigned long long k0 = KEY_MISS;
             if (gi < total) {
                 if (ray_has_nan(load_ray(s0, s1, gi))) nanmask |= 1u << r;
                 else vmask |= 3u << (2 * r);
-                if (accumulate) k0 = gi < s0.n ? s0.key[gi] : s1.key[gi - s0.n];
             }
-            wbest[r * 32 + lane] = k0;
+            wbest[r * 32 + lane] = KEY_MISS;
         }
         __syncwarp();
         int qn = 0; // queued pairs of this warp (warp-uniform)
 
         // ---- phase 1 + 2 --------------------------------------------------------------
         for (int g = 0; g < sc.segs.n; ++g) {
-            const int gb = max(sc.segs.begin[g], slot_begin), ge = min(sc.segs.end[g], slot_end);
+            const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
             if (gb >= ge) continue;
             RayCoef c[R];
 #pragma unroll
@@ -287,14 +292,15 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
                         : KEY_MISS;
             } else {
                 k = wbest[r * 32 + lane];
-                if (planes) {
+                if (planes && slice == 0) {
                     RayRegs rr = load_ray(s0, s1, gi);
                     k = plane_keys(sc.n_planes, sc.plane_shape, sc.plane_data, sc.geom, v3(rr.ox, rr.oy, rr.oz),
                                    v3(rr.dx, rr.dy, rr.dz), k);
                 }
             }
-            if (gi < s0.n) s0.key[gi] = k;
-            else s1.key[gi - s0.n] = k;
+            unsigned long long *kp = gi < s0.n ? s0.key + gi : s1.key + (gi - s0.n);
+            if (!merge) *kp = k;
+            else if (k != KEY_MISS) atomicMin(kp, k);
         }
         __syncwarp();
     }
@@ -348,17 +354,34 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, long
     }
     const int n_chunks = std::max(1, (sc.n_slots + cap - 1) / cap);
     if (n_chunks > n_counters) return cudaErrorInvalidValue;
-    long long batches = (total + 32ll * R - 1) / (32ll * R);
-    unsigned int grid = (unsigned int)std::min<long long>((batches + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)sm_count);
+    // chunks of equal size (rounded to SEG_PAD) rather than cap, cap, ..., rest
+    const int per = ((sc.n_slots + n_chunks - 1) / n_chunks + SEG_PAD - 1) / SEG_PAD * SEG_PAD;
+    const long long batches = (total + 32ll * R - 1) / (32ll * R);
+    // Work items = ray batches x table slices.  A launch with few rays is cut into slices of
+    // the table so that every warp of the GPU still gets several items (a ray batch against the
+    // whole m10k table is ~1 ms of one warp: too coarse a grain for a short launch).
+    const long long want_items = 48ll * sm_count * SWEEP_WARPS; // measured: tools/trace_tile.py, RT_B200_SLICES
+    int n_slices = (int)std::min<long long>((want_items + batches - 1) / batches, std::max(1, per / MIN_SLICE_SLOTS));
+    if (const char *e = std::getenv("RT_B200_SLICES")) n_slices = std::max(1, std::min(std::atoi(e), std::max(1, per / SEG_PAD)));
+    n_slices = std::max(n_slices, 1);
+    const int slice_slots = std::max(SEG_PAD, ((per + n_slices - 1) / n_slices + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
+    n_slices = std::max(1, (per + slice_slots - 1) / slice_slots);
+    const int merge = (n_slices > 1 || n_chunks > 1) ? 1 : 0;
+    if (merge) { // every item folds its keys in with atomicMin: start from "no hit"
+        cudaError_t err = cudaSuccess;
+        if (s0.n > 0) err = cudaMemsetAsync(s0.key, 0xFF, sizeof(unsigned long long) * (size_t)s0.n, stream);
+        if (err == cudaSuccess && s1.n > 0) err = cudaMemsetAsync(s1.key, 0xFF, sizeof(unsigned long long) * (size_t)s1.n, stream);
+        if (err != cudaSuccess) return err;
+    }
+    const long long items = batches * n_slices;
+    unsigned int grid = (unsigned int)std::min<long long>((items + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)sm_count);
     for (int c = 0; c < n_chunks; ++c) {
-        // chunks of equal size (rounded to SEG_PAD) rather than cap, cap, ..., rest
-        int per = ((sc.n_slots + n_chunks - 1) / n_chunks + SEG_PAD - 1) / SEG_PAD * SEG_PAD;
         int b = c * per, e = std::min(sc.n_slots, b + per);
         const size_t smem = (size_t)std::max(e - b, 1) * sizeof(float4) + sweep_smem_fixed<R, T>();
         cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
-        sweep_kernel<R, T><<<grid, T, smem, stream>>>(sc, s0, s1, b, e, c > 0 ? 1 : 0, c == n_chunks - 1 ? 1 : 0,
-                                                               batch_counters + c, exact_counter);
+        sweep_kernel<R, T><<<grid, T, smem, stream>>>(sc, s0, s1, b, e, n_slices, slice_slots, merge, c == n_chunks - 1 ? 1 : 0,
+                                                      batch_counters + c, exact_counter);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
     }
     *used = n_chunks;
@@ -373,10 +396,11 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, int rays_per_
     if (total <= 0) return cudaSuccess;
     if (sm_count < 1) sm_count = 1;
     int r = rays_per_thread;
-    if (r <= 0) { // enough warp batches to balance the SMs, else fewer rays per thread
-        const long long want = 4ll * sm_count * 16;
+    if (r <= 0) { // fewer rays per thread only when even table slicing cannot occupy the warps
+        const long long want = 2ll * sm_count * 16;
+        const long long max_slices = std::max(1, sc.n_slots / MIN_SLICE_SLOTS);
         r = 4;
-        while (r > 1 && (total + 32ll * r - 1) / (32ll * r) < want) r >>= 1;
+        while (r > 1 && ((total + 32ll * r - 1) / (32ll * r)) * max_slices < want) r >>= 1;
     }
 #define RT_SWEEP(R_, T_) launch_sweep_r<R_, T_>(sc, s0, s1, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
     if (r >= 4) return RT_SWEEP(4, 512); // 16 warps x <= 128 registers; more warps spill the filter loop
