@@ -29,6 +29,7 @@ WORKLOADS = {
     "c2": dict(scene="default", width=1920, height=1080, depth=3, spp=1, desc="my_scene.rs 1920x1080 depth 3"),
     "c3": dict(scene="s1k", width=3840, height=2160, depth=5, spp=1, desc="1,000 spheres + plane, 4 lights, 3840x2160 depth 5"),
     "c4": dict(scene="m10k", width=3840, height=2160, depth=5, spp=1, desc="10k mixed spheres/triangles, 4 lights, 3840x2160 depth 5"),
+    "c5": dict(scene="m10k", width=7680, height=4320, depth=8, spp=4, desc="8K, 10k prims, 4 spp jittered, depth 8 (whole-box config)"),
     "c5s": dict(scene="m10k", width=3840, height=2160, depth=8, spp=4, desc="config 5 at 4K instead of 8K: 10k prims, 4 spp, depth 8"),
 }
 ROWS_PER_TILE = 8
