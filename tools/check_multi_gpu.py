@@ -1,0 +1,34 @@
+"""torchrun --nproc-per-node N tools/check_multi_gpu.py : the row-tiled, NCCL-gathered frame of N
+GPUs must equal rank 0's own single-GPU frame bit for bit (pixels are independent; the gather is
+the only exchange, rust_tracer_b200/distributed.py)."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+import rust_tracer_b200 as rt
+from rust_tracer_b200.distributed import gather_rows
+
+rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=dev)
+ok = True
+for name, w, h, depth, spp in (("default", 1920, 1080, 3, 1), ("m10k", 960, 540, 5, 1), ("s1k", 640, 360, 8, 4)):
+    sc = rt.Scene(rt.SceneDesc.builtin(name), device=local)
+    n_rows = len(rt.tile_rows(h, rank, world, 8))
+    tile = torch.empty((n_rows, w, 3), dtype=torch.uint8, device=dev)
+    sc.render_device(w, h, depth, d_rgb_u8=tile.data_ptr(), spp=spp, seed=3, rank=rank, world=world, rows_per_tile=8)
+    full = gather_rows(tile, h, w, rank, world, 8)
+    if rank == 0:
+        ref = torch.empty((h, w, 3), dtype=torch.uint8, device=dev)
+        sc.render_device(w, h, depth, d_rgb_u8=ref.data_ptr(), spp=spp, seed=3)
+        same = bool((full == ref).all())
+        ok &= same
+        print("%s %dx%d d%d spp%d world %d: gathered == single-GPU frame: %s" % (name, w, h, depth, spp, world, same), flush=True)
+    sc.close()
+if world > 1:
+    dist.barrier()
+    dist.destroy_process_group()
+sys.exit(0 if ok else 1)
