@@ -298,9 +298,10 @@ def run_ours(args, wl):
     measured_peak, sms, khz = rt.measure_fp32_peak(local)
     nominal_peak = sms * 128 * 2 * khz * 1e3 / 1e12
     achieved = sweep_flops / (sweep_ms * 1e-3) / 1e12 if sweep_ms > 0 else 0.0
-    # what the kernel really executes per (ray, bound) pair in its filter: 7 FMA = 14 flop, as 3.5
-    # packed FFMA2 (sweep.cu phase 1), plus the exact tests (~0.2% of pairs)
-    executed = (pairs * 14.0) / (sweep_ms * 1e-3) / 1e12 if sweep_ms > 0 else 0.0
+    # what the kernel really executes per (ray, bound) pair in its filter, counted by the library
+    # (rt_stats.filter_flops): 7 FMA for a general ray, 4 for a primary or shadow ray swept against
+    # its origin table, as packed FFMA2 (sweep.cu phase 1); the exact tests (~0.2% of pairs) not counted
+    executed = r0["filter_flops"] / (sweep_ms * 1e-3) / 1e12 if sweep_ms > 0 else 0.0
     traffic = None  # dram bytes of the largest sweep launch, from the committed ncu --set full capture
     try:
         with open(os.path.join(ROOT, "profiles", "sweep_ncu_summary.json")) as fh:
@@ -314,11 +315,13 @@ def run_ours(args, wl):
         "frac": executed / measured_peak if measured_peak else None, "traffic": traffic,
         "peak_source": "of measured: rt_measure_fp32_peak FFMA micro-kernel on this GPU (MEASURED_PEAKS.json has no FP32 "
                        "figure); nominal %d SMs x 128 x 2 x %.0f MHz = %.1f TFLOP/s" % (sms, khz / 1e3, nominal_peak),
-        "achieved_is": "algorithmic flop of the kernel's own method: 14 flop (7 FMA) per (ray, shape) pair resolved by the "
-                       "filter (DESIGN.md 4.3) / sweep time from CUDA events; exact tests (<1%) not counted",
+        "achieved_is": "flop the kernel's filter executes: 14 (7 FMA) per (ray, shape) pair, 8 (4 FMA) for primary and shadow "
+                       "rays swept against their origin table (DESIGN.md 4.3) / sweep time from CUDA events; exact tests "
+                       "(<1%) not counted",
+        "filter_flop_per_pair": r0["filter_flops"] / pairs if pairs else None,
         "credited_8d_tflops": achieved, "credited_8d_frac": achieved / measured_peak if measured_peak else None,
         "credited_8d_is": "SURVEY 8(d) reference-side credit: 54 flop per ray x sphere, 30 per ray x triangle, every pair "
-                          "resolved; > 1 because the filter resolves a pair in 14 flop",
+                          "resolved; > 1 because the filter resolves a pair in 8-14 flop",
         "pairs_per_s": pairs / (sweep_ms * 1e-3) if sweep_ms > 0 else None,
         "sweep_ms_per_step": sweep_ms, "sweep_share_of_step": sweep_ms / total_ms if total_ms else None,
     }

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 1
+#define RT_B200_ABI_VERSION 2
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -168,6 +168,8 @@ typedef struct rt_stats {
     float    shade_ms;      /* device time in ray generation, spawn and shading           */
     float    total_ms;      /* device time of the whole call                              */
     uint32_t kernel_launches; /* kernels of this library launched by the call             */
+    double   filter_flops;  /* flop the sweeps' bounding-sphere filters executed: 2 x (7 FMA per
+                               ray x bound pair, 4 for rays swept against an origin table)  */
 } rt_stats;
 
 typedef struct rt_scene rt_scene;   /* opaque: device-resident scene tables */

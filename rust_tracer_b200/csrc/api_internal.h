@@ -39,6 +39,13 @@ struct Workspace {
 // One released workspace per device is kept instead of freed: its ray pools are gigabytes,
 // and cudaMalloc / cudaFree of them would dominate a create -> render -> destroy call.
 // rt_trim() frees the cache.
+// Host copy of one bound slot (api_scene.cu: make_bound), kept to re-centre the table.
+struct HostSlot {
+    float cx, cy, cz;
+    double rf;  // radius incl. slack
+    int kind;   // 0 bound, 1 pad (passes no ray), 2 beyond the filter's range (passes every ray)
+};
+
 Workspace workspace_take_cached(int device);
 void workspace_give_cached(int device, Workspace &ws);
 
@@ -57,7 +64,22 @@ struct rt_scene {
     cudaStream_t own_stream = nullptr; // created with the scene
     unsigned int launches = 0;         // kernels launched by the current call
     rt::Workspace ws;
+    // origin tables (kernels.h: OriginTable): one per point light, built with the scene, and
+    // one for the camera origin of the last render.  Empty when the table is too small to pay.
+    std::vector<rt::HostSlot> slots;
+    std::vector<rt::OriginTable> light_tabs; // by DevLight::point_index
+    float4 *cam_tab = nullptr;
+    rt::OriginTable cam;                     // bound == cam_tab once built
+    float cam_origin[3] = {0.f, 0.f, 0.f};
 };
+
+namespace rt {
+// Re-centre the scene's bound table on `o` (paired layout of DevScene::bound) and fill every
+// field of *tab but `bound`; toward: the table serves shadow rays travelling towards `o`.
+void build_origin_table(const rt_scene *scene, const float o[3], std::vector<float4> &out, OriginTable *tab, bool toward);
+// Make scene->cam the table of this camera origin (no-op when origin tables are off).
+int prepare_camera_table(rt_scene *scene, const float origin[3]);
+} // namespace rt
 
 struct rt_forest {
     rt_scene *scene = nullptr;

@@ -16,7 +16,7 @@ namespace rt {
 
 // ---- workspace --------------------------------------------------------------------------
 
-constexpr int BATCH_COUNTERS = 2048; // one per sweep launch of a band: (depth + 1 <= 31) x table chunks
+constexpr int BATCH_COUNTERS = 8192; // one per sweep launch of a band: (depth + 1 <= 31) x (1 + lights) x table chunks
 
 template <typename T> static int dev_alloc(T **p, size_t n, const char *what) {
     *p = nullptr;
@@ -183,6 +183,7 @@ struct Accum {
     unsigned long long tree_rays = 0, shadow_rays = 0, nodes = 0, exact = 0;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> sweep_spans;
     std::vector<long long> sweep_rays; // rays of each span (RT_B200_TRACE)
+    double filter_fma = 0.0;           // FMAs executed by the sweeps' filters
 };
 
 static int env_int(const char *name, int dflt, int lo, int hi) {
@@ -218,18 +219,19 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     launch_raygen(fp, p, sample0, n, st);
     scene->launches += 1;
 
-    auto sweep = [&](RaySeg a, RaySeg b) {
+    auto sweep = [&](RaySeg a, RaySeg b, OriginTable ot) {
         if (a.n + b.n == 0) return;
         cudaEvent_t e0 = events.get(), e1 = events.get();
         cudaEventRecord(e0, st);
         if (audit) launch_sweep_all_pairs(sc, a, b, ws.exact_counter, st);
         else {
             int used = 0;
-            cudaError_t e = launch_sweep(sc, a, b, rpt, scene->sm_count, ws.batch_counters + ws.batch_next,
+            cudaError_t e = launch_sweep(sc, a, b, ot, rpt, scene->sm_count, ws.batch_counters + ws.batch_next,
                                          BATCH_COUNTERS - ws.batch_next, &used, ws.exact_counter, st);
             ws.batch_next += used;
             scene->launches += used > 0 ? used - 1 : 0;
             if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
+            acc.filter_fma += (double)(a.n + b.n) * sc.n_bounded * (ot.bound ? FILTER_FMA_ORIGIN : FILTER_FMA_GENERAL);
         }
         cudaEventRecord(e1, st);
         acc.sweep_spans.push_back({e0, e1});
@@ -239,10 +241,31 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     };
     auto tree_seg = [&](int b, int e) { return RaySeg{p.t_a + b, p.t_b + b, p.t_key + b, e - b}; };
     auto shadow_seg = [&](int b, int e) { return RaySeg{p.s_a + b, p.s_b + b, p.s_key + b, e - b}; };
+    const RaySeg none{nullptr, nullptr, nullptr, 0};
+    const OriginTable general{};
+    // Origin tables: primary rays against the camera's table, the shadow rays of each light
+    // (one column of the [node][light] pool) against that light's; the rest as one general sweep.
+    const bool by_origin = !audit && !scene->light_tabs.empty() && scene->cam.bound;
+    const int npl = std::max(sc.n_point_lights, 1);
+    auto sweep_level = [&](int level, int tb, int te, int sb, int se) {
+        if (!by_origin) {
+            sweep(tree_seg(tb, te), shadow_seg(sb, se), general);
+            return;
+        }
+        sweep(tree_seg(tb, te), none, level == 0 ? scene->cam : general);
+        if (se > sb) {
+            cudaError_t e = cudaMemsetAsync(p.s_key + sb, 0xFF, sizeof(unsigned long long) * (size_t)(se - sb), st);
+            if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
+            for (int l = 0; l < sc.n_point_lights; ++l)
+                sweep(RaySeg{p.s_a + sb + l, p.s_b + sb + l, p.s_key + sb + l, (se - sb) / npl, npl, 1}, none,
+                      scene->light_tabs[l]);
+        }
+    };
 
     int tb = 0, te = n, sb = 0, se = 0; // current tree level, previous level's shadows
-    for (int k = 0; k < fp.depth; ++k) {
-        sweep(tree_seg(tb, te), shadow_seg(sb, se));
+    int k = 0;
+    for (; k < fp.depth; ++k) {
+        sweep_level(k, tb, te, sb, se);
         launch_spawn(sc, fp, p, tb, te, (k + 1 < fp.depth) ? 1 : 0, st);
         if (te > tb) scene->launches += 1;
         CK(cudaMemcpyAsync(ws.h_counters, p.counters, 4 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st), "counters readback");
@@ -255,7 +278,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         tb = te; te = new_te;
         if (tb == te && sb == se) break; // nothing left to cast
     }
-    sweep(RaySeg{nullptr, nullptr, nullptr, 0}, shadow_seg(sb, se)); // shadows of the last level
+    sweep_level(-1, 0, 0, sb, se); // shadows of the last level
     lv.nodes = ws.h_counters[2];
     CK(sweep_err, "sweep launch");
     CK(cudaGetLastError(), "wavefront launch");
@@ -305,6 +328,7 @@ static void fill_stats(rt_scene *scene, const Accum &acc, unsigned long long pix
     double per_ray = 54.0 * c[RT_SHAPE_SPHERE] + 30.0 * c[RT_SHAPE_TRIANGLE] + 393.0 * c[RT_SHAPE_CUBE] +
                      47.0 * (c[RT_SHAPE_PLANE] - scene->planes_identity) + 14.0 * scene->planes_identity;
     st->algorithmic_flops = (double)rays * per_ray + (double)acc.nodes * (60.0 + 70.0 * scene->dev.n_lights);
+    st->filter_flops = 2.0 * acc.filter_fma;
 }
 
 static int check_params(const rt_scene *scene, const rt_camera *cam, const rt_render_params *pr) {
@@ -361,6 +385,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
     int rc = check_params(scene, cam, pr);
     if (rc != RT_OK) return rc;
     CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    if ((rc = prepare_camera_table(scene, cam->origin)) != RT_OK) return rc;
     Workspace &ws = scene->ws;
     if ((rc = ws.ensure_misc()) != RT_OK) return rc;
     cudaStream_t st = scene->stream;
@@ -482,6 +507,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
     if (params->spp != 1) return fail(RT_ERR_UNSUPPORTED, "the ray forest keeps one tree per pixel: spp must be 1");
     if (params->depth < 1) return fail(RT_ERR_INVALID, "forest depth must be >= 1");
     CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    if ((rc = prepare_camera_table(scene, camera->origin)) != RT_OK) return rc;
     rt_forest *f = new (std::nothrow) rt_forest();
     if (!f) return fail(RT_ERR_NOMEM, "out of host memory");
     f->scene = scene;

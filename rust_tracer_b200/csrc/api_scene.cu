@@ -109,6 +109,7 @@ static float round_down_f32(double x) {
 struct Bound {
     float cx, cy, cz, w;
     double reach;
+    double rf = 0.0; // the radius W was built from
 };
 static Bound make_bound(const double c[3], double r, double scale) {
     double cn = std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
@@ -119,6 +120,7 @@ static Bound make_bound(const double c[3], double r, double scale) {
     rf += std::sqrt(dx * dx + dy * dy + dz * dz);
     double c2 = (double)b.cx * b.cx + (double)b.cy * b.cy + (double)b.cz * b.cz;
     b.reach = std::sqrt(c2) + rf;
+    b.rf = rf;
     if (!(b.reach < 1e15)) {
         b.cx = b.cy = b.cz = 0.f;
         b.w = -3.402823466e+38f;
@@ -132,6 +134,65 @@ static Bound make_bound(const double c[3], double r, double scale) {
 // Margin factor of a segment ("filter margins"): 1.5 x (32 for the filter's own
 // rounding + 25 for the reference's object-space ray + 15 aniso^2 for its discriminant).
 static float seg_margin(double aniso) { return round_up_f32(1.5 * (57.0 + 15.0 * aniso * aniso)); }
+// Its share for the reference's exact test alone (origin tables, sweep.cu: ray_coef_origin).
+static float seg_margin_exact(double aniso) { return round_up_f32(1.5 * (25.0 + 15.0 * aniso * aniso)); }
+
+static bool origin_tables_wanted(int n_slots) {
+    if (const char *e = std::getenv("RT_B200_NO_ORIGIN")) if (std::atoi(e)) return false;
+    int min_slots = 256; // below this a sweep is launch-bound and one general launch per level is cheaper
+    if (const char *e = std::getenv("RT_B200_ORIGIN_MIN_SLOTS")) min_slots = std::atoi(e);
+    return n_slots >= min_slots;
+}
+
+void build_origin_table(const rt_scene *scene, const float o[3], std::vector<float4> &out, OriginTable *tab, bool toward) {
+    const std::vector<HostSlot> &slots = scene->slots;
+    const int n = (int)slots.size();
+    out.resize(n);
+    struct S { float x, y, z, w; };
+    double rmax = 0.0;
+    bool clip = toward;
+    auto one = [&](const HostSlot &h) {
+        if (h.kind == 1) return S{0.f, 0.f, 0.f, 3.402823466e+38f};
+        if (h.kind == 0) {
+            double x = (double)h.cx - o[0], y = (double)h.cy - o[1], z = (double)h.cz - o[2];
+            float fx = (float)x, fy = (float)y, fz = (float)z;
+            double dx = x - fx, dy = y - fy, dz = z - fz;
+            double rf = h.rf + std::sqrt(dx * dx + dy * dy + dz * dz);
+            double c2 = (double)fx * fx + (double)fy * fy + (double)fz * fz;
+            if (std::sqrt(c2) + rf < 1e15) {
+                rmax = std::max(rmax, rf);
+                return S{fx, fy, fz, round_down_f32(c2 - rf * rf * (1.0 + 1e-6))};
+            }
+        }
+        clip = false; // a bound every ray must pass: no far clip in this table
+        return S{0.f, 0.f, 0.f, -3.402823466e+38f};
+    };
+    for (int j = 0; j + 1 < n; j += 2) {
+        S a = one(slots[j]), b = one(slots[j + 1]);
+        out[j] = make_float4(a.x, b.x, a.y, b.y);
+        out[j + 1] = make_float4(a.z, b.z, a.w, b.w);
+    }
+    double on = std::sqrt((double)o[0] * o[0] + (double)o[1] * o[1] + (double)o[2] * o[2]);
+    double r = (on + (double)scene->dev.cmax) * (1.0 + 1e-6);
+    tab->reach = std::isfinite(r) && r < 3e38 ? round_up_f32(r) : 3.0e38f;
+    tab->ox = o[0]; tab->oy = o[1]; tab->oz = o[2];
+    tab->rmax = (clip && rmax > 0.0 && rmax < 1e15) ? round_up_f32(rmax * (1.0 + 1e-6)) : 0.f;
+}
+
+int prepare_camera_table(rt_scene *scene, const float origin[3]) {
+    if (!scene->cam_tab) return RT_OK; // origin tables are off for this scene
+    if (scene->cam.bound && std::memcmp(scene->cam_origin, origin, 3 * sizeof(float)) == 0) return RT_OK;
+    std::vector<float4> host;
+    OriginTable t;
+    build_origin_table(scene, origin, host, &t, false);
+    cudaError_t e = cudaMemcpyAsync(scene->cam_tab, host.data(), host.size() * sizeof(float4), cudaMemcpyHostToDevice, scene->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "camera table upload");
+    if ((e = cudaStreamSynchronize(scene->stream)) != cudaSuccess) return cuda_fail(e, "camera table upload");
+    t.bound = scene->cam_tab;
+    scene->cam = t;
+    std::memcpy(scene->cam_origin, origin, 3 * sizeof(float));
+    return RT_OK;
+}
 
 template <typename T> static int upload(rt_scene *s, const std::vector<T> &host, const T **dev) {
     *dev = nullptr;
@@ -337,6 +398,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         while (slots.size() % SEG_PAD) { slots.push_back(pad); bound_shape.push_back(-1); }
         segs.end[g] = (int)slots.size();
         segs.k[g] = seg_margin(aniso);
+        segs.kx[g] = seg_margin_exact(aniso);
     }
     const int n_slots = (int)slots.size();
     std::vector<float4> bound(n_slots);
@@ -391,6 +453,32 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         return cuda_fail(e, "cudaStreamCreate");
     }
     s->own_stream = s->stream;
+    if (origin_tables_wanted(n_slots)) {
+        s->slots.resize(n_slots);
+        for (int j = 0; j < n_slots; ++j) {
+            const Bound &b = slots[j];
+            s->slots[j] = HostSlot{b.cx, b.cy, b.cz, b.rf, bound_shape[j] < 0 ? 1 : (b.w == -3.402823466e+38f ? 2 : 0)};
+        }
+        s->light_tabs.resize(n_point);
+        std::vector<float4> host;
+        for (int l = 0; l < desc->n_lights; ++l) {
+            if (lights[l].point_index < 0) continue;
+            const float o[3] = {lights[l].px, lights[l].py, lights[l].pz};
+            OriginTable &t = s->light_tabs[lights[l].point_index];
+            build_origin_table(s, o, host, &t, true);
+            if ((rc = upload(s, host, &t.bound)) != RT_OK) {
+                rt_scene_destroy(s);
+                return rc;
+            }
+        }
+        void *ct = nullptr;
+        if ((e = cudaMalloc(&ct, (size_t)n_slots * sizeof(float4))) != cudaSuccess) {
+            rt_scene_destroy(s);
+            return cuda_fail(e, "cudaMalloc(camera table)");
+        }
+        s->allocs.push_back(ct);
+        s->cam_tab = (float4 *)ct;
+    }
     s->ws = workspace_take_cached(device);
     *out = s;
     return RT_OK;

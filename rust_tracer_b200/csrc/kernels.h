@@ -7,13 +7,31 @@
 
 namespace rt {
 
-// A contiguous run of rays: a[i] = (ox, oy, oz, dx), b[i] = (dy, dz, -, -); key[i] receives
-// the nearest hit (exact.cuh: make_key) or KEY_MISS.
+// A run of n rays: a[i * stride] = (ox, oy, oz, dx), b[i * stride] = (dy, dz, -, -);
+// key[i * stride] receives the nearest hit (exact.cuh: make_key) or KEY_MISS.  stride > 1
+// picks the shadow rays of one light out of the [node][light] shadow pool; only the first
+// segment of a sweep may be strided.
 struct RaySeg {
     const float4 *a;
     const float4 *b;
     unsigned long long *key;
     int n;
+    int stride = 1;
+    int preset = 0; // the caller has already set every key to KEY_MISS (required when stride > 1)
+};
+
+// The bound table seen from one point O' (a light, the camera): slot j holds
+// (C_j - O', W'_j = |C_j - O'|^2 - R_j^2 rounded down), same slot order, pairing and padding
+// as DevScene::bound.  Every ray of a launch that uses it lies on a line through O' (up to
+// rounding), so the filter needs the ray's direction only: 4 FMA per pair instead of 7.
+struct OriginTable {
+    const float4 *bound = nullptr; // null: no table, use the general filter
+    float reach = 0.f;             // |O'| + cmax, rounded up
+    float ox = 0.f, oy = 0.f, oz = 0.f; // O'
+    // > 0: the rays are shadow rays travelling TOWARDS O' (a light); a bound whose centre lies
+    // more than |O' - ray origin| + rmax from O' along the ray cannot hold a hit between the ray
+    // origin and the light and is skipped (rmax = largest bound radius, rounded up).  0: no clip.
+    float rmax = 0.f;
 };
 
 // Nearest-hit query for every ray of s0 then s1 (Scene::intersect, scene/mod.rs:98-116).
@@ -21,9 +39,12 @@ struct RaySeg {
 // n_counters zeroed words) hand ray batches to the persistent warps, one word per launch;
 // *used receives the number consumed (one per shared-memory chunk of the bound table).
 // exact_counter (device, may be null) accumulates the number of exact pair tests.
-cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, int rays_per_thread, int sm_count,
+// origin.bound != null: every ray passes through origin's point; s1 must be empty.
+cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable origin, int rays_per_thread, int sm_count,
                          unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
                          cudaStream_t stream);
+// FMA per (ray, bound) pair of the two filters (for the executed-flop count)
+constexpr int FILTER_FMA_GENERAL = 7, FILTER_FMA_ORIGIN = 4;
 // Same result, every (ray, shape) pair through the exact test in shape order (audit).
 void launch_sweep_all_pairs(const DevScene &sc, RaySeg s0, RaySeg s1, unsigned long long *exact_counter,
                             cudaStream_t stream);

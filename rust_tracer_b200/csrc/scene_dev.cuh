@@ -49,10 +49,13 @@ constexpr int MAX_SEGS = 4;
 
 // Bound slots [begin, end) share one margin factor k: a ray passes slot j iff
 //   b^2 - |L|^2 + |C|^2 + k * 2^-24 * (|O| + cmax)^2  >=  W_j        (sweep.cu)
+// With an origin table (kernels.h: OriginTable; A = |O| + cmax, B = |O'| + cmax):
+//   (C'.dh)^2 + 2^-24 * (kx A^2 + 26 B^2 + 8 A B)  >=  W'_j
 struct SweepSegs {
     int n;
     int begin[MAX_SEGS], end[MAX_SEGS];
     float k[MAX_SEGS];
+    float kx[MAX_SEGS]; // the reference's exact-test share of k: 1.5 x (25 + 15 aniso^2)
 };
 
 struct DevScene {

@@ -23,9 +23,15 @@
 // and  (L.dh)^2 - |L|^2 + |C|^2 = b^2 + s  with  b = C.dh - O.dh,  s = C.(2 O) - |O|^2:
 // two 3-FMA chains seeded per ray, one FMA to combine, one compare against the per-bound W.
 // The per-ray seed of s also carries the margin  k 2^-24 (|O| + cmax)^2.
+//
+// Rays that share a point O' -- primary rays (the camera) and the shadow rays of one light --
+// are swept against the table re-centred on O' (kernels.h: OriginTable): with C' = C - O',
+//     dist^2(C, line) <= R^2   <=>   (C'.dh)^2  >=  |C'|^2 - R^2 =: W'
+// one 3-FMA chain and one FMA that squares it and adds the per-ray margin: 4 FMA per pair.
 #include <algorithm>
 #include <cfloat>
 #include <cstdlib>
+#include <type_traits>
 
 #include "kernels.h"
 
@@ -47,7 +53,7 @@ RT_DEV bool ray_has_nan(const RayRegs &r) {
 
 RT_DEV RayRegs load_ray(const RaySeg &s0, const RaySeg &s1, int gi) {
     float4 a, b;
-    if (gi < s0.n) { a = s0.a[gi]; b = s0.b[gi]; }
+    if (gi < s0.n) { a = s0.a[(long long)gi * s0.stride]; b = s0.b[(long long)gi * s0.stride]; }
     else { a = s1.a[gi - s0.n]; b = s1.b[gi - s0.n]; }
     RayRegs r;
     r.ox = a.x; r.oy = a.y; r.oz = a.z; r.dx = a.w; r.dy = b.x; r.dz = b.y;
@@ -154,6 +160,42 @@ RT_DEV RayCoef ray_coef(const RayRegs &r, float k_seg, float cmax, bool usable) 
     return c;
 }
 
+// Same for a launch with an origin table: direction and margin only (4 registers).
+// mu = 2^-24 (kx A^2 + 26 B^2 + 8 A B), A = |O| + cmax, B = |O'| + cmax: the reference's exact
+// test, the filter's own rounding, and the distance of O' from the ray's line (a shadow ray's
+// direction is the rounded, normalised  light - origin).  DESIGN.md, "filter margins".
+// tf: far clip of a shadow ray in units of e = (C'.dh)^2 + mu -- a bound with e > tf lies wholly
+// behind the ray's origin, or beyond the light by more than the origin-light distance; neither
+// can shadow (PointLight::get_energy, scene/mod.rs:195-204, compares the hit with the light).
+struct RayCoefO {
+    float dx, dy, dz, mu, tf;
+};
+
+RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, const OriginTable &ot, bool usable) {
+    const float reach = ot.reach;
+    RayCoefO c;
+    c.dx = c.dy = c.dz = 0.f;
+    c.mu = -3.0e38f;
+    c.tf = 3.4e38f;
+    if (!usable) return c;
+    float n = sqrtf(fmaf(r.dx, r.dx, fmaf(r.dy, r.dy, r.dz * r.dz)));
+    float o2 = fmaf(r.ox, r.ox, fmaf(r.oy, r.oy, r.oz * r.oz));
+    float A = (sqrtf(o2) + cmax) * 1.000001f;
+    if (!(n > 0.f) || !(n < 1e18f) || !(A < 1e15f) || !(reach < 1e15f)) {
+        c.mu = 3.0e38f;
+        return c;
+    }
+    c.dx = __fdiv_rn(r.dx, n); c.dy = __fdiv_rn(r.dy, n); c.dz = __fdiv_rn(r.dz, n);
+    c.mu = U24 * 1.000001f * fmaf(kx_seg * A, A, fmaf(26.f * reach, reach, 8.f * A * reach));
+    if (ot.rmax > 0.f) {
+        float lx = ot.ox - r.ox, ly = ot.oy - r.oy, lz = ot.oz - r.oz;
+        float D = fmaf(1.0001f, sqrtf(fmaf(lx, lx, fmaf(ly, ly, lz * lz))) + ot.rmax, 1e-4f * reach);
+        float t = fmaf(D, D, c.mu) * 1.0001f;
+        if (t < 3.0e38f) c.tf = t; // NaN or overflow: no clip
+    }
+    return c;
+}
+
 RT_DEV float2 f2(float x) { return make_float2(x, x); }
 
 // One persistent CTA per SM; slots [slot_begin, slot_end) of the bound table stay in shared
@@ -163,18 +205,19 @@ RT_DEV float2 f2(float x) { return make_float2(x, x); }
 // `merge`: keys are folded into global memory with atomicMin (they were initialised to
 // KEY_MISS or hold the result of earlier table chunks) instead of stored; `planes`: this
 // launch also tests the planes (slice 0 does).
-template <int R, int SWEEP_THREADS>
+// ORIGIN: the table is `ot` (all rays pass through its point), filter of 4 FMA per pair.
+template <int R, int SWEEP_THREADS, bool ORIGIN>
 __global__ void __launch_bounds__(SWEEP_THREADS, 1)
-sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, int n_slices, int slice_slots, int merge,
-             int planes, unsigned int *batch_counter, unsigned long long *exact_counter) {
+sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, int slot_end, int n_slices, int slice_slots,
+             int merge, int planes, unsigned int *batch_counter, unsigned long long *exact_counter) {
     constexpr int SWEEP_WARPS = SWEEP_THREADS / 32;
     constexpr unsigned int FULL = 0xffffffffu;
     extern __shared__ float4 smem[];
     __shared__ SweepCtx ctx;
     __shared__ unsigned int n_exact[SWEEP_WARPS];
     const int n_tab = slot_end - slot_begin;
-    float4 *tab = smem;                                                         // n_tab slots
-    unsigned long long *best = (unsigned long long *)(smem + n_tab);            // SWEEP_THREADS * R
+    float4 *tab = smem;                                                         // n_tab slots + one slack pair
+    unsigned long long *best = (unsigned long long *)(smem + n_tab + 2);        // SWEEP_THREADS * R
     unsigned int *queue = (unsigned int *)(best + SWEEP_THREADS * R);           // SWEEP_WARPS * QCAP
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -183,7 +226,11 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
     unsigned int *wqueue = queue + warp * QCAP;
     const unsigned int lt_mask = (1u << lane) - 1u;
 
-    for (int k = tid; k < n_tab; k += SWEEP_THREADS) tab[k] = sc.bound[slot_begin + k];
+    {
+        const float4 *src = (ORIGIN ? ot.bound : sc.bound) + slot_begin;
+        for (int k = tid; k < n_tab; k += SWEEP_THREADS) tab[k] = src[k];
+        if (tid < 2) tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f); // prefetched past the end, never used
+    }
     if (tid == 0) {
         ctx.s0 = s0; ctx.s1 = s1;
         ctx.shape_meta = sc.shape_meta; ctx.geom = sc.geom; ctx.cube_tris = sc.cube_tris; ctx.bound_shape = sc.bound_shape;
@@ -222,14 +269,15 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
         for (int g = 0; g < sc.segs.n; ++g) {
             const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
             if (gb >= ge) continue;
-            RayCoef c[R];
+            typename std::conditional<ORIGIN, RayCoefO, RayCoef>::type c[R];
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 bool usable = (vmask >> (2 * r)) & 1u;
                 RayRegs rr;
                 rr.ox = rr.oy = rr.oz = rr.dx = rr.dy = rr.dz = 0.f;
                 if (usable) rr = load_ray(s0, s1, ray0 + r * 32 + lane);
-                c[r] = ray_coef(rr, sc.segs.k[g], sc.cmax, usable);
+                if constexpr (ORIGIN) c[r] = ray_coef_origin(rr, sc.segs.kx[g], sc.cmax, ot, usable);
+                else c[r] = ray_coef(rr, sc.segs.k[g], sc.cmax, usable);
             }
             float4 N0 = tab0[gb], N1 = tab0[gb + 1]; // next slot pair, fetched one iteration ahead
             for (int j0 = gb; j0 < ge; j0 += 2 * CHUNK_PAIRS) {
@@ -237,17 +285,19 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
 #pragma unroll 4
                 for (int i = 0; i < CHUNK_PAIRS; ++i) {
                     const float4 T0 = N0, T1 = N1;
-                    {   // the last prefetch of a segment re-reads its first pair instead of running past the table
-                        const float4 *np = (j0 + 2 * i + 2 < ge) ? tp + 2 * i + 2 : tab0 + gb;
-                        N0 = np[0]; N1 = np[1];
-                    }
+                    N0 = tp[2 * i + 2]; N1 = tp[2 * i + 3]; // past the last pair: the next segment's, or the table's slack pair
                     const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
                     float2 e[R];
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
-                        float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
-                        float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2), f2(c[r].seed))));
-                        e[r] = __ffma2_rn(b, b, s);
+                        if constexpr (ORIGIN) {
+                            float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __fmul2_rn(cz, f2(c[r].dz))));
+                            e[r] = __ffma2_rn(b, b, f2(c[r].mu));
+                        } else {
+                            float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
+                            float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2), f2(c[r].seed))));
+                            e[r] = __ffma2_rn(b, b, s);
+                        }
                     }
                     float m0 = e[0].x, m1 = e[0].y;
 #pragma unroll
@@ -256,8 +306,13 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
                         unsigned int mask = 0;
 #pragma unroll
                         for (int r = 0; r < R; ++r) {
-                            if (e[r].x >= T1.z) mask |= 1u << (2 * r);
-                            if (e[r].y >= T1.w) mask |= 2u << (2 * r);
+                            if constexpr (ORIGIN) {
+                                if (e[r].x >= T1.z && e[r].x <= c[r].tf) mask |= 1u << (2 * r);
+                                if (e[r].y >= T1.w && e[r].y <= c[r].tf) mask |= 2u << (2 * r);
+                            } else {
+                                if (e[r].x >= T1.z) mask |= 1u << (2 * r);
+                                if (e[r].y >= T1.w) mask |= 2u << (2 * r);
+                            }
                         }
                         mask &= vmask;
                         unsigned int ball;
@@ -298,7 +353,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, int slot_begin, int slot_end, in
                                    v3(rr.dx, rr.dy, rr.dz), k);
                 }
             }
-            unsigned long long *kp = gi < s0.n ? s0.key + gi : s1.key + (gi - s0.n);
+            unsigned long long *kp = gi < s0.n ? s0.key + (long long)gi * s0.stride : s1.key + (gi - s0.n);
             if (!merge) *kp = k;
             else if (k != KEY_MISS) atomicMin(kp, k);
         }
@@ -328,13 +383,13 @@ sweep_all_pairs_kernel(DevScene sc, RaySeg s0, RaySeg s1, unsigned long long *ex
         }
         best = plane_keys(sc.n_planes, sc.plane_shape, sc.plane_data, sc.geom, o, d, best);
     }
-    if (gi < s0.n) s0.key[gi] = best;
+    if (gi < s0.n) s0.key[(long long)gi * s0.stride] = best;
     else s1.key[gi - s0.n] = best;
     (void)exact_counter; // rays x n_bounded, added by the host
 }
 
 template <int R, int T> static size_t sweep_smem_fixed() {
-    return (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int);
+    return 2 * sizeof(float4) + (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int);
 }
 
 // Bound slots one launch can keep in shared memory.
@@ -342,8 +397,8 @@ template <int R, int T> static int sweep_table_cap() {
     return (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T>()) / sizeof(float4)) / SEG_PAD * SEG_PAD;
 }
 
-template <int R, int T>
-static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, long long total, int sm_count,
+template <int R, int T, bool ORIGIN>
+static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, long long total, int sm_count,
                                   unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
                                   cudaStream_t stream) {
     constexpr int SWEEP_WARPS = T / 32;
@@ -369,7 +424,10 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, long
     const int merge = (n_slices > 1 || n_chunks > 1) ? 1 : 0;
     if (merge) { // every item folds its keys in with atomicMin: start from "no hit"
         cudaError_t err = cudaSuccess;
-        if (s0.n > 0) err = cudaMemsetAsync(s0.key, 0xFF, sizeof(unsigned long long) * (size_t)s0.n, stream);
+        if (s0.n > 0 && !s0.preset) {
+            if (s0.stride != 1) return cudaErrorInvalidValue; // the caller presets the keys of a strided segment
+            err = cudaMemsetAsync(s0.key, 0xFF, sizeof(unsigned long long) * (size_t)s0.n, stream);
+        }
         if (err == cudaSuccess && s1.n > 0) err = cudaMemsetAsync(s1.key, 0xFF, sizeof(unsigned long long) * (size_t)s1.n, stream);
         if (err != cudaSuccess) return err;
     }
@@ -378,22 +436,23 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, long
     for (int c = 0; c < n_chunks; ++c) {
         int b = c * per, e = std::min(sc.n_slots, b + per);
         const size_t smem = (size_t)std::max(e - b, 1) * sizeof(float4) + sweep_smem_fixed<R, T>();
-        cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
-        sweep_kernel<R, T><<<grid, T, smem, stream>>>(sc, s0, s1, b, e, n_slices, slice_slots, merge, c == n_chunks - 1 ? 1 : 0,
-                                                      batch_counters + c, exact_counter);
+        sweep_kernel<R, T, ORIGIN><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, n_slices, slice_slots, merge,
+                                                              c == n_chunks - 1 ? 1 : 0, batch_counters + c, exact_counter);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
     }
     *used = n_chunks;
     return cudaSuccess;
 }
 
-cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, int rays_per_thread, int sm_count,
+cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, int rays_per_thread, int sm_count,
                          unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
                          cudaStream_t stream) {
     long long total = (long long)s0.n + s1.n;
     *used = 0;
     if (total <= 0) return cudaSuccess;
+    if (ot.bound && s1.n > 0) return cudaErrorInvalidValue;
     if (sm_count < 1) sm_count = 1;
     int r = rays_per_thread;
     if (r <= 0) { // fewer rays per thread only when even table slicing cannot occupy the warps
@@ -402,10 +461,18 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, int rays_per_
         r = 4;
         while (r > 1 && ((total + 32ll * r - 1) / (32ll * r)) * max_slices < want) r >>= 1;
     }
-#define RT_SWEEP(R_, T_) launch_sweep_r<R_, T_>(sc, s0, s1, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
-    if (r >= 4) return RT_SWEEP(4, 512); // 16 warps x <= 128 registers; more warps spill the filter loop
-    if (r >= 2) return RT_SWEEP(2, 512);
-    return RT_SWEEP(1, 512);
+#define RT_SWEEP(R_, T_, O_) \
+    launch_sweep_r<R_, T_, O_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
+    if (ot.bound) {
+        if (const char *e = std::getenv("RT_B200_ORIGIN_R")) // test knob: 8 rays per thread
+            if (std::atoi(e) == 8 && r >= 4) return RT_SWEEP(8, 512, true);
+        if (r >= 4) return RT_SWEEP(4, 512, true);
+        if (r >= 2) return RT_SWEEP(2, 512, true);
+        return RT_SWEEP(1, 512, true);
+    }
+    if (r >= 4) return RT_SWEEP(4, 512, false); // 16 warps x <= 128 registers; more warps spill the filter loop
+    if (r >= 2) return RT_SWEEP(2, 512, false);
+    return RT_SWEEP(1, 512, false);
 #undef RT_SWEEP
 }
 

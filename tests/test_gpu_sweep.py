@@ -148,3 +148,74 @@ def test_ray_pools_are_reused_across_scenes_and_trim_frees_them():
     rt.trim()
     _, u, _ = rt.Scene(desc).render(96, 54, 5, want_f32=False)
     assert (u == u0).all()
+
+
+def _moved_camera(w, h, origin):
+    cam = abi.default_camera(w, h)
+    cam.origin[:] = list(origin)
+    return cam
+
+
+@pytest.mark.parametrize("origin", [(0.0, 0.0, -8.0), (0.5, 0.7, 1.5), (300.0, -120.0, -4000.0)])
+def test_origin_tables_equal_general_filter_and_audit(monkeypatch, origin):
+    """Primary rays are swept against the bound table re-centred on the camera, the shadow rays
+    of each light against the table re-centred on that light (4 FMA per pair instead of 7);
+    the nearest hits must be those of the general filter and of the all-pairs audit -- also
+    for a camera inside the cloud of shapes and one far outside it."""
+    desc = rt.SceneDesc.synthetic(500, 500, 777, 0.03, 0.1)
+    w, h, depth = 224, 126, 4
+    cam = _moved_camera(w, h, origin)
+    sc = rt.Scene(desc)
+    try:
+        a = sc.render(w, h, depth, cam=cam)
+        b = sc.render(w, h, depth, cam=cam, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS)
+        a4 = sc.render(w, h, depth, cam=cam, spp=4, seed=11)
+        b4 = sc.render(w, h, depth, cam=cam, spp=4, seed=11, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS)
+    finally:
+        sc.close()
+    monkeypatch.setenv("RT_B200_NO_ORIGIN", "1")
+    sc = rt.Scene(desc)
+    try:
+        g = sc.render(w, h, depth, cam=cam)
+    finally:
+        sc.close()
+    _assert_same(a, b)
+    _assert_same(a4, b4)
+    _assert_same(a, g)
+    # the origin tables really were used: fewer filter flops for the same pairs
+    assert a[2]["filter_flops"] < 0.8 * g[2]["filter_flops"]
+    assert a[2]["kernel_launches"] > g[2]["kernel_launches"]
+
+
+def test_origin_tables_follow_the_camera():
+    """The camera table is rebuilt when the origin changes between calls on one scene."""
+    desc = rt.SceneDesc.synthetic(300, 300, 99, 0.04, 0.12)
+    w, h = 160, 90
+    sc = rt.Scene(desc)
+    try:
+        for origin in ((0.0, 0.0, -8.0), (2.0, 1.0, -3.0), (0.0, 0.0, -8.0)):
+            cam = _moved_camera(w, h, origin)
+            _assert_same(sc.render(w, h, 3, cam=cam), sc.render(w, h, 3, cam=cam, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS))
+    finally:
+        sc.close()
+
+
+def test_origin_tables_with_a_light_inside_a_shape_and_far_lights():
+    """A light at the centre of a sphere (W' < 0: every shadow ray of that light is a candidate
+    of that sphere), one on a surface, one 1e6 away, one beyond the filter's range."""
+    base = rt.SceneDesc.synthetic(300, 300, 5, 0.04, 0.12)
+    n = base.desc.n_shapes
+    shapes = (abi.rt_shape * n)(*[base.desc.shapes[i] for i in range(n)])
+    mats = (abi.rt_material * base.desc.n_materials)(*[base.desc.materials[i] for i in range(base.desc.n_materials)])
+    s1 = shapes[1]  # a sphere: centre = translation column of its transform
+    centre = (s1.transform[3], s1.transform[7], s1.transform[11])
+    lights = (abi.rt_light * 4)(*[base.desc.lights[i] for i in range(4)])
+    lights[0].pos[:] = list(centre)
+    lights[1].pos[:] = [centre[0] + abs(s1.transform[0]), centre[1], centre[2]]
+    lights[2].pos[:] = [1.0e6, 2.0e6, -1.5e6]
+    lights[3].pos[:] = [0.0, 4.0e15, 0.0]
+    desc = rt.SceneDesc.from_arrays(shapes, mats, lights, (0.1, 0.1, 0.1))
+    a, b = _render_pair(desc, 160, 90, 3)
+    _assert_same(a, b)
+    of, ou, oc = orc.render(desc.desc, abi.default_camera(160, 90), 3)
+    assert (a[1] == ou).all() and a[2]["rays"] == oc.rays
