@@ -169,7 +169,8 @@ typedef struct rt_stats {
     float    total_ms;      /* device time of the whole call                              */
     uint32_t kernel_launches; /* kernels of this library launched by the call             */
     double   filter_flops;  /* flop the sweeps' bounding-sphere filters executed: 2 x (7 FMA per
-                               ray x bound pair, 4 for rays swept against an origin table)  */
+                               ray x sphere evaluated, 4 for rays swept against an origin table);
+                               spheres = bounds and group spheres, skipped groups not counted */
 } rt_stats;
 
 typedef struct rt_scene rt_scene;   /* opaque: device-resident scene tables */

@@ -146,10 +146,10 @@ int Workspace::ensure_mask(long long n) {
 int Workspace::ensure_misc() {
     int rc;
     if (!pools.counters && (rc = dev_alloc(&pools.counters, 4, "counters"))) return rc;
-    if (!exact_counter && (rc = dev_alloc(&exact_counter, 1, "exact_counter"))) return rc;
+    if (!exact_counter && (rc = dev_alloc(&exact_counter, 3, "exact_counter"))) return rc;
     if (!batch_counters && (rc = dev_alloc(&batch_counters, BATCH_COUNTERS, "batch_counters"))) return rc;
     if (!h_counters) {
-        cudaError_t e = cudaMallocHost((void **)&h_counters, 4 * sizeof(unsigned int) + sizeof(unsigned long long));
+        cudaError_t e = cudaMallocHost((void **)&h_counters, 4 * sizeof(unsigned int) + 3 * sizeof(unsigned long long));
         if (e != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
     }
     return RT_OK;
@@ -185,6 +185,15 @@ struct Accum {
     std::vector<long long> sweep_rays; // rays of each span (RT_B200_TRACE)
     double filter_fma = 0.0;           // FMAs executed by the sweeps' filters
 };
+
+// exact-test count and filter FMA count of the sweeps, from the device counters read back into
+// ws.h_counters + 4: [0] exact tests, [1] pairs through the general filter, [2] through the origin filter
+static void read_sweep_counters(const Workspace &ws, Accum &acc) {
+    unsigned long long c[3];
+    std::memcpy(c, ws.h_counters + 4, sizeof(c));
+    acc.exact = c[0];
+    acc.filter_fma = (double)c[1] * FILTER_FMA_GENERAL + (double)c[2] * FILTER_FMA_ORIGIN;
+}
 
 static int env_int(const char *name, int dflt, int lo, int hi) {
     const char *e = std::getenv(name);
@@ -231,7 +240,6 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
             ws.batch_next += used;
             scene->launches += used > 0 ? used - 1 : 0;
             if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
-            acc.filter_fma += (double)(a.n + b.n) * sc.n_bounded * (ot.bound ? FILTER_FMA_ORIGIN : FILTER_FMA_GENERAL);
         }
         cudaEventRecord(e1, st);
         acc.sweep_spans.push_back({e0, e1});
@@ -375,7 +383,7 @@ static int cast_band_sized(rt_scene *scene, Workspace &ws, const FrameParams &fp
         if (rc != RT_OK) return rc;
         rc = cast_band(scene, ws, fp, sample0, n, flags, lv, acc, events);
         if (rc <= 0) return rc;
-        cudaMemsetAsync(ws.exact_counter, 0, sizeof(unsigned long long), scene->stream); // the band is recast
+        cudaMemsetAsync(ws.exact_counter, 0, 3 * sizeof(unsigned long long), scene->stream); // the band is recast
         if (t_cap >= worst) return fail(RT_ERR_INTERNAL, "ray pool overflow at the worst-case size");
         t_cap = std::min(worst, t_cap * 2);
     }
@@ -398,7 +406,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
     EventPool events;
     cudaEvent_t ev0 = events.get(), ev1 = events.get();
     scene->launches = 0;
-    CK(cudaMemsetAsync(ws.exact_counter, 0, sizeof(unsigned long long), st), "exact counter");
+    CK(cudaMemsetAsync(ws.exact_counter, 0, 3 * sizeof(unsigned long long), st), "exact counter");
     cudaEventRecord(ev0, st);
 
     Accum acc;
@@ -425,10 +433,10 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
         if (n > 0) scene->launches += 1;
     }
     cudaEventRecord(ev1, st);
-    CK(cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
+    CK(cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
     CK(cudaStreamSynchronize(st), "render");
     CK(cudaGetLastError(), "render");
-    if (!(pr->flags & RT_FLAG_AUDIT_ALL_PAIRS)) std::memcpy(&acc.exact, ws.h_counters + 4, sizeof(unsigned long long));
+    if (!(pr->flags & RT_FLAG_AUDIT_ALL_PAIRS)) read_sweep_counters(ws, acc);
     if (stats) {
         fill_stats(scene, acc, (unsigned long long)n_pixels, stats);
         float ms = 0.f, sweep = 0.f;
@@ -532,7 +540,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
     EventPool events;
     cudaEvent_t ev0 = events.get(), ev1 = events.get();
     cudaStream_t st = scene->stream;
-    cudaMemsetAsync(ws.exact_counter, 0, sizeof(unsigned long long), st);
+    cudaMemsetAsync(ws.exact_counter, 0, 3 * sizeof(unsigned long long), st);
     cudaEventRecord(ev0, st);
     Accum acc;
     BandLevels lv;
@@ -541,7 +549,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
         return rc;
     }
     cudaEventRecord(ev1, st);
-    cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) {
         rt_forest_destroy(f);
@@ -554,7 +562,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
         acc.tree_rays = (unsigned long long)f->total_tree_rays;
         acc.shadow_rays = lv.se.empty() ? 0 : (unsigned long long)lv.se.back();
         acc.nodes = lv.nodes;
-        if (!(pr.flags & RT_FLAG_AUDIT_ALL_PAIRS)) std::memcpy(&acc.exact, ws.h_counters + 4, sizeof(unsigned long long));
+        if (!(pr.flags & RT_FLAG_AUDIT_ALL_PAIRS)) read_sweep_counters(ws, acc);
         fill_stats(scene, acc, (unsigned long long)n, stats);
         float ms = 0.f, sweep = 0.f;
         cudaEventElapsedTime(&ms, ev0, ev1);

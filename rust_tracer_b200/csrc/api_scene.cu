@@ -111,9 +111,13 @@ struct Bound {
     double reach;
     double rf = 0.0; // the radius W was built from
 };
+static Bound bound_from(const double c[3], double rf);
 static Bound make_bound(const double c[3], double r, double scale) {
     double cn = std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
-    double rf = r * scale + 64.0 * 1.1920929e-07 * (cn + r);
+    return bound_from(c, r * scale + 64.0 * 1.1920929e-07 * (cn + r));
+}
+// Sphere (c, rf) as a table entry: the radius grows by the displacement of the f32 centre.
+static Bound bound_from(const double c[3], double rf) {
     Bound b;
     b.cx = (float)c[0]; b.cy = (float)c[1]; b.cz = (float)c[2];
     double dx = c[0] - b.cx, dy = c[1] - b.cy, dz = c[2] - b.cz;
@@ -131,6 +135,43 @@ static Bound make_bound(const double c[3], double r, double scale) {
     return b;
 }
 
+// Sphere around the bounds of one group of GROUP_SLOTS slots (pads skipped): centre G = mean of
+// the members' centres.  A group with a member every ray must pass is itself passed by every
+// ray; a group of pads by none.
+// Margins: a member (C, R) at distance a from G passes a ray when dist^2(C, line) <= R^2 + mu;
+// then dist(G, line) <= a + sqrt(R^2 + mu), and (a + sqrt(R^2 + mu))^2 <= (a + R)^2 + (1 + a / R) mu.
+// The group radius therefore counts every member as at least a / 16 wide, and the sweep gives
+// group spheres 17 times the margin mu of a bound (sweep.cu: GROUP_MARGIN).
+static Bound make_group(const Bound *slots, const int *shape, int n) {
+    double c[3] = {0.0, 0.0, 0.0};
+    int m = 0;
+    for (int j = 0; j < n; ++j) {
+        if (shape[j] < 0) continue;
+        if (slots[j].w == -3.402823466e+38f) return Bound{0.f, 0.f, 0.f, -3.402823466e+38f, 0.0, 0.0};
+        c[0] += slots[j].cx; c[1] += slots[j].cy; c[2] += slots[j].cz;
+        ++m;
+    }
+    if (m == 0) return Bound{0.f, 0.f, 0.f, 3.402823466e+38f, 0.0, 0.0};
+    c[0] /= m; c[1] /= m; c[2] /= m;
+    double rg = 0.0;
+    for (int j = 0; j < n; ++j) {
+        if (shape[j] < 0) continue;
+        double dx = slots[j].cx - c[0], dy = slots[j].cy - c[1], dz = slots[j].cz - c[2];
+        double a = std::sqrt(dx * dx + dy * dy + dz * dz);
+        rg = std::max(rg, a + std::max(slots[j].rf, a / 16.0));
+    }
+    return bound_from(c, rg * (1.0 + 1e-9));
+}
+
+static uint32_t spread3(uint32_t x) { // 10 bits -> every third bit
+    x &= 0x3ffu;
+    x = (x | (x << 16)) & 0x030000ffu;
+    x = (x | (x << 8)) & 0x0300f00fu;
+    x = (x | (x << 4)) & 0x030c30c3u;
+    x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+
 // Margin factor of a segment ("filter margins"): 1.5 x (32 for the filter's own
 // rounding + 25 for the reference's object-space ray + 15 aniso^2 for its discriminant).
 static float seg_margin(double aniso) { return round_up_f32(1.5 * (57.0 + 15.0 * aniso * aniso)); }
@@ -145,9 +186,6 @@ static bool origin_tables_wanted(int n_slots) {
 }
 
 void build_origin_table(const rt_scene *scene, const float o[3], std::vector<float4> &out, OriginTable *tab, bool toward) {
-    const std::vector<HostSlot> &slots = scene->slots;
-    const int n = (int)slots.size();
-    out.resize(n);
     struct S { float x, y, z, w; };
     double rmax = 0.0;
     bool clip = toward;
@@ -167,11 +205,18 @@ void build_origin_table(const rt_scene *scene, const float o[3], std::vector<flo
         clip = false; // a bound every ray must pass: no far clip in this table
         return S{0.f, 0.f, 0.f, -3.402823466e+38f};
     };
-    for (int j = 0; j + 1 < n; j += 2) {
-        S a = one(slots[j]), b = one(slots[j + 1]);
-        out[j] = make_float4(a.x, b.x, a.y, b.y);
-        out[j + 1] = make_float4(a.z, b.z, a.w, b.w);
-    }
+    // slots, then groups (both paired); rmax covers the groups too
+    const size_t ns = scene->slots.size(), ng = scene->groups.size();
+    out.resize(ns + ng);
+    auto fill = [&](const std::vector<HostSlot> &v, float4 *dst) {
+        for (size_t j = 0; j + 1 < v.size(); j += 2) {
+            S a = one(v[j]), b = one(v[j + 1]);
+            dst[j] = make_float4(a.x, b.x, a.y, b.y);
+            dst[j + 1] = make_float4(a.z, b.z, a.w, b.w);
+        }
+    };
+    fill(scene->slots, out.data());
+    fill(scene->groups, out.data() + ns);
     double on = std::sqrt((double)o[0] * o[0] + (double)o[1] * o[1] + (double)o[2] * o[2]);
     double r = (on + (double)scene->dev.cmax) * (1.0 + 1e-6);
     tab->reach = std::isfinite(r) && r < 3e38 ? round_up_f32(r) : 3.0e38f;
@@ -189,6 +234,7 @@ int prepare_camera_table(rt_scene *scene, const float origin[3]) {
     if (e != cudaSuccess) return cuda_fail(e, "camera table upload");
     if ((e = cudaStreamSynchronize(scene->stream)) != cudaSuccess) return cuda_fail(e, "camera table upload");
     t.bound = scene->cam_tab;
+    t.group = scene->cam_tab + scene->slots.size();
     scene->cam = t;
     std::memcpy(scene->cam_origin, origin, 3 * sizeof(float));
     return RT_OK;
@@ -317,7 +363,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     std::vector<int> plane_shape;
     std::vector<float4> plane_data;
     // error class of a bound: 0 similarity-transformed spheres, 1 triangles, 2 the rest
-    struct B { Bound b; int shape; int cls; double aniso; };
+    struct B { Bound b; int shape; int cls; double aniso; uint32_t morton; };
     std::vector<B> bounds;
     const float tri_scale = tri_bound_scale();
     int counts[4] = {0, 0, 0, 0}, planes_identity = 0, first_nan = -1;
@@ -375,8 +421,33 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         }
         }
     }
-    // segments by error class, each padded to SEG_PAD slots; slot pairs interleaved for FFMA2
-    std::stable_sort(bounds.begin(), bounds.end(), [](const B &a, const B &b) { return a.cls < b.cls; });
+    // segments by error class, each padded to SEG_PAD slots; within a class in Morton order of
+    // the centres, so that the GROUP_SLOTS slots of a group are neighbours in space; slot pairs
+    // interleaved for FFMA2
+    {
+        double lo[3][3], hi[3][3];
+        for (int c = 0; c < 3; ++c)
+            for (int a = 0; a < 3; ++a) { lo[c][a] = 1e300; hi[c][a] = -1e300; }
+        for (const B &x : bounds) {
+            if (x.b.w == -3.402823466e+38f) continue;
+            const double p[3] = {x.b.cx, x.b.cy, x.b.cz};
+            for (int a = 0; a < 3; ++a) { lo[x.cls][a] = std::min(lo[x.cls][a], p[a]); hi[x.cls][a] = std::max(hi[x.cls][a], p[a]); }
+        }
+        for (B &x : bounds) {
+            x.morton = 0xffffffffu;
+            if (x.b.w == -3.402823466e+38f) continue;
+            const double p[3] = {x.b.cx, x.b.cy, x.b.cz};
+            uint32_t q[3];
+            for (int a = 0; a < 3; ++a) {
+                double ext = hi[x.cls][a] - lo[x.cls][a];
+                double t = ext > 0.0 ? (p[a] - lo[x.cls][a]) / ext : 0.0;
+                q[a] = (uint32_t)std::min(1023.0, std::max(0.0, t * 1024.0));
+            }
+            x.morton = spread3(q[0]) | (spread3(q[1]) << 1) | (spread3(q[2]) << 2);
+        }
+    }
+    std::stable_sort(bounds.begin(), bounds.end(),
+                     [](const B &a, const B &b) { return a.cls != b.cls ? a.cls < b.cls : a.morton < b.morton; });
     const int nb = (int)bounds.size();
     SweepSegs segs;
     std::memset(&segs, 0, sizeof(segs));
@@ -401,12 +472,22 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         segs.kx[g] = seg_margin_exact(aniso);
     }
     const int n_slots = (int)slots.size();
-    std::vector<float4> bound(n_slots);
-    for (int j = 0; j < n_slots; j += 2) {
-        const Bound &a = slots[j], &b = slots[j + 1];
-        bound[j] = make_float4(a.cx, b.cx, a.cy, b.cy);
-        bound[j + 1] = make_float4(a.cz, b.cz, a.w, b.w);
+    const int n_groups = n_slots / GROUP_SLOTS; // even: SEG_PAD is two groups
+    std::vector<Bound> groups(n_groups);
+    for (int g = 0; g < n_groups; ++g) {
+        groups[g] = make_group(&slots[(size_t)g * GROUP_SLOTS], &bound_shape[(size_t)g * GROUP_SLOTS], GROUP_SLOTS);
+        cmax = std::max(cmax, groups[g].reach); // a group sphere may reach beyond its members
     }
+    auto paired = [](const std::vector<Bound> &v) {
+        std::vector<float4> out(v.size());
+        for (size_t j = 0; j + 1 < v.size(); j += 2) {
+            const Bound &a = v[j], &b = v[j + 1];
+            out[j] = make_float4(a.cx, b.cx, a.cy, b.cy);
+            out[j + 1] = make_float4(a.cz, b.cz, a.w, b.w);
+        }
+        return out;
+    };
+    std::vector<float4> bound = paired(slots), group = paired(groups);
 
     std::vector<DevMaterial> mats;
     int rc = convert_materials(desc->materials, desc->n_materials, mats);
@@ -438,7 +519,8 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     d.n_lights = desc->n_lights; d.n_point_lights = n_point; d.first_nan_shape = first_nan;
     d.amb_r = desc->ambient[0]; d.amb_g = desc->ambient[1]; d.amb_b = desc->ambient[2];
     const DevMaterial *dm = nullptr;
-    if ((rc = upload(s, bound, &d.bound)) != RT_OK || (rc = upload(s, bound_shape, &d.bound_shape)) != RT_OK ||
+    if ((rc = upload(s, bound, &d.bound)) != RT_OK || (rc = upload(s, group, &d.group)) != RT_OK ||
+        (rc = upload(s, bound_shape, &d.bound_shape)) != RT_OK ||
         (rc = upload(s, meta, &d.shape_meta)) != RT_OK || (rc = upload(s, geom, &d.geom)) != RT_OK ||
         (rc = upload(s, plane_shape, &d.plane_shape)) != RT_OK || (rc = upload(s, plane_data, &d.plane_data)) != RT_OK ||
         (rc = upload(s, ctris, &d.cube_tris)) != RT_OK || (rc = upload(s, mats, &dm)) != RT_OK ||
@@ -454,11 +536,11 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     }
     s->own_stream = s->stream;
     if (origin_tables_wanted(n_slots)) {
-        s->slots.resize(n_slots);
-        for (int j = 0; j < n_slots; ++j) {
-            const Bound &b = slots[j];
-            s->slots[j] = HostSlot{b.cx, b.cy, b.cz, b.rf, bound_shape[j] < 0 ? 1 : (b.w == -3.402823466e+38f ? 2 : 0)};
-        }
+        auto host_slot = [](const Bound &b) {
+            return HostSlot{b.cx, b.cy, b.cz, b.rf, b.w == 3.402823466e+38f ? 1 : (b.w == -3.402823466e+38f ? 2 : 0)};
+        };
+        for (const Bound &b : slots) s->slots.push_back(host_slot(b));
+        for (const Bound &b : groups) s->groups.push_back(host_slot(b));
         s->light_tabs.resize(n_point);
         std::vector<float4> host;
         for (int l = 0; l < desc->n_lights; ++l) {
@@ -470,9 +552,10 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
                 rt_scene_destroy(s);
                 return rc;
             }
+            t.group = t.bound + n_slots;
         }
         void *ct = nullptr;
-        if ((e = cudaMalloc(&ct, (size_t)n_slots * sizeof(float4))) != cudaSuccess) {
+        if ((e = cudaMalloc(&ct, (size_t)(n_slots + n_groups) * sizeof(float4))) != cudaSuccess) {
             rt_scene_destroy(s);
             return cuda_fail(e, "cudaMalloc(camera table)");
         }

@@ -22,10 +22,11 @@ struct RaySeg {
 
 // The bound table seen from one point O' (a light, the camera): slot j holds
 // (C_j - O', W'_j = |C_j - O'|^2 - R_j^2 rounded down), same slot order, pairing and padding
-// as DevScene::bound.  Every ray of a launch that uses it lies on a line through O' (up to
+// as DevScene::bound (and DevScene::group for the group spheres).  Every ray of a launch that uses it lies on a line through O' (up to
 // rounding), so the filter needs the ray's direction only: 4 FMA per pair instead of 7.
 struct OriginTable {
     const float4 *bound = nullptr; // null: no table, use the general filter
+    const float4 *group = nullptr; // the group spheres (DevScene::group) re-centred likewise
     float reach = 0.f;             // |O'| + cmax, rounded up
     float ox = 0.f, oy = 0.f, oz = 0.f; // O'
     // > 0: the rays are shadow rays travelling TOWARDS O' (a light); a bound whose centre lies

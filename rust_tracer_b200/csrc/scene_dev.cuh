@@ -10,6 +10,11 @@
 //                                             to SEG_PAD slots with W = FLT_MAX (passes no ray).
 //                                             The ONLY table the sweep's inner loop reads (whole
 //                                             table resident in shared memory).
+//   group[2q], group[2q+1]  float4 x 2        bounding spheres of slot groups 2q and 2q+1, same
+//                                             packing: group g encloses the bounds of slots
+//                                             [GROUP_SLOTS g, GROUP_SLOTS (g + 1)), which are
+//                                             neighbours in space (Morton order within a segment).
+//                                             A warp skips a group none of its rays can touch.
 //   bound_shape[j] int32                      shape id of bound slot j, -1 for a pad
 //   shape_meta[s]  int4  (kind, material, plane index, 0)
 //   geom[3*s..]    3 x float4                 sphere/cube/plane: rows 0..2 of inv_transform
@@ -44,7 +49,8 @@ struct DevLight { // 32 bytes
     int point_index; // index among the point lights (shadow slot), -1 for ambient lights
 };
 
-constexpr int SEG_PAD = 16;   // every segment of the bound table is a multiple of this many slots
+constexpr int GROUP_SLOTS = 16; // bound slots per group
+constexpr int SEG_PAD = 32;     // every segment of the bound table is a multiple of this many slots (a pair of groups)
 constexpr int MAX_SEGS = 4;
 
 // Bound slots [begin, end) share one margin factor k: a ray passes slot j iff
@@ -70,6 +76,7 @@ struct DevScene {
     int first_nan_shape; // first sphere/triangle/cube in id order, -1 if none (NaN rays)
     float amb_r, amb_g, amb_b;
     const float4 *bound;
+    const float4 *group;    // n_slots / GROUP_SLOTS group spheres, paired like bound
     const int *bound_shape;
     const int4 *shape_meta; // (kind, material, plane index or -1, 0)
     const float4 *geom;

@@ -38,8 +38,8 @@
 namespace rt {
 
 constexpr int QCAP = 256;                // queued pairs per warp
-constexpr int CHUNK_PAIRS = SEG_PAD / 2; // slot pairs between two queue checks
 constexpr float U24 = 5.9604645e-08f;    // 2^-24, unit round-off of f32
+constexpr float GROUP_MARGIN = 17.f;     // margin of a group sphere / margin of a bound (make_group: a / rho <= 16)
 constexpr int MIN_SLICE_SLOTS = 256;     // smallest table slice of a work item
 constexpr int SMEM_LIMIT = 232448;       // 227 KB opt-in dynamic shared memory per CTA on sm_100
 
@@ -137,26 +137,29 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
 // Filter coefficients of one ray (8 registers).  A ray the filter cannot bound (zero or
 // non-finite direction length, coordinates beyond 1e15) passes every bound; a dead lane or a
 // NaN ray (handled apart, see KEY_NAN_PREFIX) passes none.
+// seed_g: the seed for a group sphere, its margin GROUP_MARGIN times larger (see make_group in
+// api_scene.cu: a ray within a member's margin must also be within its group's).
 struct RayCoef {
-    float dx, dy, dz, kb, ox2, oy2, oz2, seed;
+    float dx, dy, dz, kb, ox2, oy2, oz2, seed, seed_g;
 };
 
 RT_DEV RayCoef ray_coef(const RayRegs &r, float k_seg, float cmax, bool usable) {
     RayCoef c;
     c.dx = c.dy = c.dz = c.kb = c.ox2 = c.oy2 = c.oz2 = 0.f;
-    c.seed = -3.0e38f;
+    c.seed = c.seed_g = -3.0e38f;
     if (!usable) return c;
     float n = sqrtf(fmaf(r.dx, r.dx, fmaf(r.dy, r.dy, r.dz * r.dz)));
     float o2 = fmaf(r.ox, r.ox, fmaf(r.oy, r.oy, r.oz * r.oz));
     float lam = (sqrtf(o2) + cmax) * 1.000001f;
     if (!(n > 0.f) || !(n < 1e18f) || !(lam < 1e15f)) {
-        c.seed = 3.0e38f;
+        c.seed = c.seed_g = 3.0e38f;
         return c;
     }
     c.dx = __fdiv_rn(r.dx, n); c.dy = __fdiv_rn(r.dy, n); c.dz = __fdiv_rn(r.dz, n);
     c.kb = -fmaf(r.ox, c.dx, fmaf(r.oy, c.dy, r.oz * c.dz));
     c.ox2 = 2.f * r.ox; c.oy2 = 2.f * r.oy; c.oz2 = 2.f * r.oz;
     c.seed = fmaf(k_seg * U24, lam * lam, -o2);
+    c.seed_g = fmaf(GROUP_MARGIN * k_seg * U24, lam * lam, -o2);
     return c;
 }
 
@@ -168,25 +171,26 @@ RT_DEV RayCoef ray_coef(const RayRegs &r, float k_seg, float cmax, bool usable) 
 // behind the ray's origin, or beyond the light by more than the origin-light distance; neither
 // can shadow (PointLight::get_energy, scene/mod.rs:195-204, compares the hit with the light).
 struct RayCoefO {
-    float dx, dy, dz, mu, tf;
+    float dx, dy, dz, mu, mu_g, tf;
 };
 
 RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, const OriginTable &ot, bool usable) {
     const float reach = ot.reach;
     RayCoefO c;
     c.dx = c.dy = c.dz = 0.f;
-    c.mu = -3.0e38f;
+    c.mu = c.mu_g = -3.0e38f;
     c.tf = 3.4e38f;
     if (!usable) return c;
     float n = sqrtf(fmaf(r.dx, r.dx, fmaf(r.dy, r.dy, r.dz * r.dz)));
     float o2 = fmaf(r.ox, r.ox, fmaf(r.oy, r.oy, r.oz * r.oz));
     float A = (sqrtf(o2) + cmax) * 1.000001f;
     if (!(n > 0.f) || !(n < 1e18f) || !(A < 1e15f) || !(reach < 1e15f)) {
-        c.mu = 3.0e38f;
+        c.mu = c.mu_g = 3.0e38f;
         return c;
     }
     c.dx = __fdiv_rn(r.dx, n); c.dy = __fdiv_rn(r.dy, n); c.dz = __fdiv_rn(r.dz, n);
     c.mu = U24 * 1.000001f * fmaf(kx_seg * A, A, fmaf(26.f * reach, reach, 8.f * A * reach));
+    c.mu_g = GROUP_MARGIN * c.mu;
     if (ot.rmax > 0.f) {
         float lx = ot.ox - r.ox, ly = ot.oy - r.oy, lz = ot.oz - r.oz;
         float D = fmaf(1.0001f, sqrtf(fmaf(lx, lx, fmaf(ly, ly, lz * lz))) + ot.rmax, 1e-4f * reach);
@@ -215,9 +219,11 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
     extern __shared__ float4 smem[];
     __shared__ SweepCtx ctx;
     __shared__ unsigned int n_exact[SWEEP_WARPS];
-    const int n_tab = slot_end - slot_begin;
+    __shared__ unsigned long long n_iters[SWEEP_WARPS];
+    const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS;
     float4 *tab = smem;                                                         // n_tab slots + one slack pair
-    unsigned long long *best = (unsigned long long *)(smem + n_tab + 2);        // SWEEP_THREADS * R
+    float4 *gtab = tab + n_tab + 2;                                             // n_gtab groups + one slack pair
+    unsigned long long *best = (unsigned long long *)(gtab + n_gtab + 2);       // SWEEP_THREADS * R
     unsigned int *queue = (unsigned int *)(best + SWEEP_THREADS * R);           // SWEEP_WARPS * QCAP
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -229,15 +235,21 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
     {
         const float4 *src = (ORIGIN ? ot.bound : sc.bound) + slot_begin;
         for (int k = tid; k < n_tab; k += SWEEP_THREADS) tab[k] = src[k];
-        if (tid < 2) tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f); // prefetched past the end, never used
+        const float4 *gsrc = (ORIGIN ? ot.group : sc.group) + slot_begin / GROUP_SLOTS;
+        for (int k = tid; k < n_gtab; k += SWEEP_THREADS) gtab[k] = gsrc[k];
+        if (tid < 2) { // prefetched past the end, never used
+            tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
+            gtab[n_gtab + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
     }
     if (tid == 0) {
         ctx.s0 = s0; ctx.s1 = s1;
         ctx.shape_meta = sc.shape_meta; ctx.geom = sc.geom; ctx.cube_tris = sc.cube_tris; ctx.bound_shape = sc.bound_shape;
     }
-    if (lane == 0) n_exact[warp] = 0;
+    if (lane == 0) { n_exact[warp] = 0; n_iters[warp] = 0; }
     __syncthreads();
-    const float4 *tab0 = tab - slot_begin; // indexed by absolute slot
+    const float4 *tab0 = tab - slot_begin;                 // indexed by absolute slot
+    const float4 *gtab0 = gtab - slot_begin / GROUP_SLOTS; // indexed by absolute group
 
     for (;;) {
         unsigned int item = 0;
@@ -266,6 +278,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
         int qn = 0; // queued pairs of this warp (warp-uniform)
 
         // ---- phase 1 + 2 --------------------------------------------------------------
+        unsigned int iters = 0; // pair-of-slots (or pair-of-groups) filter iterations of this item
         for (int g = 0; g < sc.segs.n; ++g) {
             const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
             if (gb >= ge) continue;
@@ -279,59 +292,83 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                 if constexpr (ORIGIN) c[r] = ray_coef_origin(rr, sc.segs.kx[g], sc.cmax, ot, usable);
                 else c[r] = ray_coef(rr, sc.segs.k[g], sc.cmax, usable);
             }
-            float4 N0 = tab0[gb], N1 = tab0[gb + 1]; // next slot pair, fetched one iteration ahead
-            for (int j0 = gb; j0 < ge; j0 += 2 * CHUNK_PAIRS) {
-                const float4 *tp = tab0 + j0;
-#pragma unroll 4
-                for (int i = 0; i < CHUNK_PAIRS; ++i) {
-                    const float4 T0 = N0, T1 = N1;
-                    N0 = tp[2 * i + 2]; N1 = tp[2 * i + 3]; // past the last pair: the next segment's, or the table's slack pair
-                    const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
-                    float2 e[R];
+            // e[r] = (filter value of ray r against the two spheres packed in T0, T1)
+            auto pair_e = [&](const float4 &T0, const float4 &T1, float2 (&e)[R], bool group) {
+                const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
 #pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        if constexpr (ORIGIN) {
-                            float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __fmul2_rn(cz, f2(c[r].dz))));
-                            e[r] = __ffma2_rn(b, b, f2(c[r].mu));
-                        } else {
-                            float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
-                            float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2), f2(c[r].seed))));
-                            e[r] = __ffma2_rn(b, b, s);
-                        }
+                for (int r = 0; r < R; ++r) {
+                    if constexpr (ORIGIN) {
+                        float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __fmul2_rn(cz, f2(c[r].dz))));
+                        e[r] = __ffma2_rn(b, b, f2(group ? c[r].mu_g : c[r].mu));
+                    } else {
+                        float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
+                        float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2), f2(group ? c[r].seed_g : c[r].seed))));
+                        e[r] = __ffma2_rn(b, b, s);
                     }
+                }
+            };
+            float4 G0 = gtab0[gb >> 4], G1 = gtab0[(gb >> 4) + 1]; // next pair of groups, fetched one step ahead
+            for (int j0 = gb; j0 < ge; j0 += 2 * GROUP_SLOTS) {
+                // which of the two groups can any ray of this warp touch?
+                unsigned int pass;
+                {
+                    const float4 T0 = G0, T1 = G1;
+                    G0 = gtab0[(j0 >> 4) + 2]; G1 = gtab0[(j0 >> 4) + 3]; // past the end: the slack pair
+                    float2 e[R];
+                    pair_e(T0, T1, e, true);
                     float m0 = e[0].x, m1 = e[0].y;
 #pragma unroll
                     for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
-                    if (__any_sync(FULL, m0 >= T1.z || m1 >= T1.w)) { // warp-uniform: some lane has a candidate
-                        unsigned int mask = 0;
+                    pass = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
+                    ++iters;
+                }
+                for (int h = 0; h < 2; ++h) {
+                    if (!((pass >> h) & 1u)) continue;
+                    const int jg = j0 + h * GROUP_SLOTS;
+                    const float4 *tp = tab0 + jg;
+                    float4 N0 = tp[0], N1 = tp[1]; // next slot pair, fetched one iteration ahead
+                    iters += GROUP_SLOTS / 2;
+#pragma unroll 4
+                    for (int i = 0; i < GROUP_SLOTS / 2; ++i) {
+                        const float4 T0 = N0, T1 = N1;
+                        N0 = tp[2 * i + 2]; N1 = tp[2 * i + 3]; // past the group: the next one's, or the table's slack pair
+                        float2 e[R];
+                        pair_e(T0, T1, e, false);
+                        float m0 = e[0].x, m1 = e[0].y;
 #pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            if constexpr (ORIGIN) {
-                                if (e[r].x >= T1.z && e[r].x <= c[r].tf) mask |= 1u << (2 * r);
-                                if (e[r].y >= T1.w && e[r].y <= c[r].tf) mask |= 2u << (2 * r);
-                            } else {
-                                if (e[r].x >= T1.z) mask |= 1u << (2 * r);
-                                if (e[r].y >= T1.w) mask |= 2u << (2 * r);
+                        for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
+                        if (__any_sync(FULL, m0 >= T1.z || m1 >= T1.w)) { // warp-uniform: some lane has a candidate
+                            unsigned int mask = 0;
+#pragma unroll
+                            for (int r = 0; r < R; ++r) {
+                                if constexpr (ORIGIN) {
+                                    if (e[r].x >= T1.z && e[r].x <= c[r].tf) mask |= 1u << (2 * r);
+                                    if (e[r].y >= T1.w && e[r].y <= c[r].tf) mask |= 2u << (2 * r);
+                                } else {
+                                    if (e[r].x >= T1.z) mask |= 1u << (2 * r);
+                                    if (e[r].y >= T1.w) mask |= 2u << (2 * r);
+                                }
                             }
-                        }
-                        mask &= vmask;
-                        unsigned int ball;
-                        while ((ball = __ballot_sync(FULL, mask != 0)) != 0) { // one queue slot per lane per round
-                            if (qn > QCAP - 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
-                            if (mask) {
-                                int bit = __ffs(mask) - 1;
-                                mask &= mask - 1;
-                                unsigned int local = (unsigned int)((bit >> 1) * 32 + lane);
-                                wqueue[qn + __popc(ball & lt_mask)] = (local << 24) | (unsigned int)(j0 + 2 * i + (bit & 1));
+                            mask &= vmask;
+                            unsigned int ball;
+                            while ((ball = __ballot_sync(FULL, mask != 0)) != 0) { // one queue slot per lane per round
+                                if (qn > QCAP - 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
+                                if (mask) {
+                                    int bit = __ffs(mask) - 1;
+                                    mask &= mask - 1;
+                                    unsigned int local = (unsigned int)((bit >> 1) * 32 + lane);
+                                    wqueue[qn + __popc(ball & lt_mask)] = (local << 24) | (unsigned int)(jg + 2 * i + (bit & 1));
+                                }
+                                qn += __popc(ball);
+                                __syncwarp();
                             }
-                            qn += __popc(ball);
-                            __syncwarp();
                         }
                     }
+                    if (qn >= 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
                 }
-                if (qn >= 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
             }
         }
+        if (lane == 0) n_iters[warp] += iters;
         __syncwarp();
         sweep_flush(&ctx, wqueue, wbest, ray0, qn, 1, &n_exact[warp]);
 
@@ -359,7 +396,11 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
         }
         __syncwarp();
     }
-    if (exact_counter && lane == 0 && n_exact[warp]) atomicAdd(exact_counter, (unsigned long long)n_exact[warp]);
+    if (exact_counter && lane == 0) {
+        if (n_exact[warp]) atomicAdd(exact_counter, (unsigned long long)n_exact[warp]);
+        // (ray, sphere) pairs the filter evaluated: 2 spheres x 32 R rays per iteration
+        if (n_iters[warp]) atomicAdd(exact_counter + (ORIGIN ? 2 : 1), n_iters[warp] * (unsigned long long)(64 * R));
+    }
 }
 
 // ---- audit: every pair exact, in shape order (what the reference literally does) --------
@@ -389,12 +430,13 @@ sweep_all_pairs_kernel(DevScene sc, RaySeg s0, RaySeg s1, unsigned long long *ex
 }
 
 template <int R, int T> static size_t sweep_smem_fixed() {
-    return 2 * sizeof(float4) + (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int);
+    return 4 * sizeof(float4) + (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int);
 }
 
 // Bound slots one launch can keep in shared memory.
 template <int R, int T> static int sweep_table_cap() {
-    return (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T>()) / sizeof(float4)) / SEG_PAD * SEG_PAD;
+    // per slot: its float4 and 1/GROUP_SLOTS of its group's
+    return (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T>()) * GROUP_SLOTS / (sizeof(float4) * (GROUP_SLOTS + 1))) / SEG_PAD * SEG_PAD;
 }
 
 template <int R, int T, bool ORIGIN>
@@ -435,7 +477,7 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
     unsigned int grid = (unsigned int)std::min<long long>((items + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)sm_count);
     for (int c = 0; c < n_chunks; ++c) {
         int b = c * per, e = std::min(sc.n_slots, b + per);
-        const size_t smem = (size_t)std::max(e - b, 1) * sizeof(float4) + sweep_smem_fixed<R, T>();
+        const size_t smem = (size_t)((e - b) + (e - b) / GROUP_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T>();
         cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
         sweep_kernel<R, T, ORIGIN><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, n_slices, slice_slots, merge,
@@ -464,8 +506,6 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
 #define RT_SWEEP(R_, T_, O_) \
     launch_sweep_r<R_, T_, O_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
     if (ot.bound) {
-        if (const char *e = std::getenv("RT_B200_ORIGIN_R")) // test knob: 8 rays per thread
-            if (std::atoi(e) == 8 && r >= 4) return RT_SWEEP(8, 512, true);
         if (r >= 4) return RT_SWEEP(4, 512, true);
         if (r >= 2) return RT_SWEEP(2, 512, true);
         return RT_SWEEP(1, 512, true);
