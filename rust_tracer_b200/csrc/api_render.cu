@@ -33,16 +33,18 @@ template <typename T> static int dev_alloc(T **p, size_t n, const char *what) {
 void Workspace::release_pools() {
     Pools &p = pools;
     cudaFree(p.t_a); cudaFree(p.t_b); cudaFree(p.t_key); cudaFree(p.t_parent); cudaFree(p.t_sbase);
-    cudaFree(p.t_crefl); cudaFree(p.t_crefr); cudaFree(p.t_root); cudaFree(p.t_hitid);
+    cudaFree(p.t_crefl); cudaFree(p.t_crefr); cudaFree(p.t_root); cudaFree(p.t_hitid); cudaFree(p.t_order);
     cudaFree(p.s_a); cudaFree(p.s_b); cudaFree(p.s_key);
-    unsigned int *c = p.counters;
+    unsigned int *c = p.counters, *b = p.bins;
     std::memset(&p, 0, sizeof(p));
     p.counters = c;
+    p.bins = b;
 }
 
 void Workspace::release() {
     release_pools();
     cudaFree(pools.counters); pools.counters = nullptr;
+    cudaFree(pools.bins); pools.bins = nullptr;
     cudaFree(sample_rgb); sample_rgb = nullptr; sample_cap = 0;
     cudaFree(rows); rows = nullptr; rows_cap = 0;
     cudaFree(mask); mask = nullptr; mask_cap = 0;
@@ -107,6 +109,7 @@ int Workspace::ensure_pools(long long t_cap, long long s_cap) {
         (rc = dev_alloc(&p.t_parent, t, "t_parent")) || (rc = dev_alloc(&p.t_sbase, t, "t_sbase")) ||
         (rc = dev_alloc(&p.t_crefl, t, "t_crefl")) || (rc = dev_alloc(&p.t_crefr, t, "t_crefr")) ||
         (rc = dev_alloc(&p.t_root, t, "t_root")) || (rc = dev_alloc(&p.t_hitid, t, "t_hitid")) ||
+        (rc = dev_alloc(&p.t_order, t, "t_order")) ||
         (rc = dev_alloc(&p.s_a, s, "s_a")) || (rc = dev_alloc(&p.s_b, s, "s_b")) || (rc = dev_alloc(&p.s_key, s, "s_key"))) {
         release_pools();
         return rc;
@@ -146,6 +149,7 @@ int Workspace::ensure_mask(long long n) {
 int Workspace::ensure_misc() {
     int rc;
     if (!pools.counters && (rc = dev_alloc(&pools.counters, 4, "counters"))) return rc;
+    if (!pools.bins && (rc = dev_alloc(&pools.bins, NODE_BINS + 2, "bins"))) return rc;
     if (!exact_counter && (rc = dev_alloc(&exact_counter, 3, "exact_counter"))) return rc;
     if (!batch_counters && (rc = dev_alloc(&batch_counters, BATCH_COUNTERS, "batch_counters"))) return rc;
     if (!h_counters) {
@@ -274,8 +278,8 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     int k = 0;
     for (; k < fp.depth; ++k) {
         sweep_level(k, tb, te, sb, se);
-        launch_spawn(sc, fp, p, tb, te, (k + 1 < fp.depth) ? 1 : 0, st);
-        if (te > tb) scene->launches += 1;
+        launch_spawn(sc, fp, p, tb, te, (k + 1 < fp.depth) ? 1 : 0, by_origin ? 1 : 0, se, st);
+        if (te > tb) scene->launches += by_origin ? 4 : 1;
         CK(cudaMemcpyAsync(ws.h_counters, p.counters, 4 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st), "counters readback");
         CK(cudaStreamSynchronize(st), "wavefront level");
         if (ws.h_counters[3]) return 1; // pool overflow

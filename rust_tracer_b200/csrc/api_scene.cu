@@ -515,6 +515,20 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     std::memset(&d, 0, sizeof(d));
     d.n_shapes = n; d.n_bounded = nb; d.n_planes = (int)plane_shape.size();
     d.n_slots = n_slots; d.segs = segs; d.cmax = round_up_f32(cmax * (1.0 + 1e-6));
+    { // node cells: the box around the bounded shapes, NODE_BIN_BITS bits per axis (hit points outside are clamped)
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (const Bound &b : slots) {
+            if (b.w == 3.402823466e+38f || b.w == -3.402823466e+38f) continue;
+            const double c[3] = {b.cx, b.cy, b.cz};
+            for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], c[a] - b.rf); hi[a] = std::max(hi[a], c[a] + b.rf); }
+        }
+        for (int a = 0; a < 3; ++a) {
+            double ext = hi[a] - lo[a];
+            bool ok = ext > 0.0 && std::isfinite(ext) && ext < 1e30;
+            d.bin_lo[a] = ok ? (float)lo[a] : 0.f;
+            d.bin_scale[a] = ok ? (float)((double)(1 << NODE_BIN_BITS) / ext) : 0.f;
+        }
+    }
     cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
     d.n_lights = desc->n_lights; d.n_point_lights = n_point; d.first_nan_shape = first_nan;
     d.amb_r = desc->ambient[0]; d.amb_g = desc->ambient[1]; d.amb_b = desc->ambient[2];

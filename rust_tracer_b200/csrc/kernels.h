@@ -63,6 +63,10 @@ struct Pools {
     int *t_root;                  // sample index of the tree this ray belongs to (forest mode)
     int *t_hitid;                 // Intersection::id of the node (cube: inner triangle), -1 on a miss; may be null
     int t_cap;
+    // node order (may be null: tree-ray order): the tree rays of the level being spawned, hits
+    // first in Morton order of their hit points, then the misses; bins[] is its histogram
+    int *t_order;
+    unsigned int *bins;           // NODE_BINS + 2 words
     // shadow rays
     float4 *s_a, *s_b;
     unsigned long long *s_key;
@@ -82,12 +86,20 @@ struct FrameParams {
     int forest_shading;
 };
 
+constexpr int NODE_BIN_BITS = 5;                    // per axis
+constexpr int NODE_BINS = 1 << (3 * NODE_BIN_BITS); // + one bin for the rays that missed
+
 // Primary rays for samples [s0, s0 + n) of this call into tree rays [0, n).
 void launch_raygen(const FrameParams &fp, const Pools &p, long long sample0, int n, cudaStream_t stream);
 // Level k: for every tree ray in [begin, end) that hit, allocate its shadow rays and (if
 // spawn_children) its reflect / refract children.
+// ordered: first sort the level's nodes by the cell of their hit point (p.t_order, p.bins), so
+// that consecutive nodes -- and with them consecutive shadow rays of each light and consecutive
+// child rays -- are neighbours in space; node number r of the level then owns shadow rays
+// [s_begin + r L, s_begin + (r + 1) L) and counters[1] = s_begin + hits L.  Not ordered: shadow
+// blocks are handed out by atomicAdd on counters[1] (which must hold s_begin).
 void launch_spawn(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int spawn_children,
-                  cudaStream_t stream);
+                  int ordered, int s_begin, cudaStream_t stream);
 // Level k, deepest first: colour of every node in [begin, end) -> parent slot, or
 // sample_rgb[sample - sample0] at level 0.
 void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level,

@@ -75,6 +75,7 @@ struct DevScene {
     int n_point_lights;
     int first_nan_shape; // first sphere/triangle/cube in id order, -1 if none (NaN rays)
     float amb_r, amb_g, amb_b;
+    float bin_lo[3], bin_scale[3]; // node cell = (hit point - bin_lo) * bin_scale, clamped (wavefront.cu)
     const float4 *bound;
     const float4 *group;    // n_slots / GROUP_SLOTS group spheres, paired like bound
     const int *bound_shape;

@@ -61,10 +61,89 @@ RT_DEV void load_tree_ray(const Pools &p, int i, V3 &o, V3 &d) {
     d = v3(a.w, b.x, b.y);
 }
 
-__global__ void __launch_bounds__(WF_BLOCK)
-spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn_children) {
+// ---- node order: counting sort of a level's tree rays by the cell of their hit point ----------
+RT_DEV unsigned int spread3_dev(unsigned int x) { // NODE_BIN_BITS <= 10 bits -> every third bit
+    x &= 0x3ffu;
+    x = (x | (x << 16)) & 0x030000ffu;
+    x = (x | (x << 8)) & 0x0300f00fu;
+    x = (x | (x << 4)) & 0x030c30c3u;
+    x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+
+__global__ void __launch_bounds__(256) node_bin_kernel(DevScene sc, Pools p, int begin, int end) {
     int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
+    unsigned long long key = p.t_key[i];
+    unsigned int bin = NODE_BINS; // miss
+    if (key != KEY_MISS) {
+        V3 o, d;
+        float4 a = p.t_a[i], b = p.t_b[i];
+        o = v3(a.x, a.y, a.z);
+        d = v3(a.w, b.x, b.y);
+        float t = key_t(key); // only a sort key: any point near the hit will do
+        const float top = (float)((1 << NODE_BIN_BITS) - 1);
+        float qx = fminf(fmaxf((fmaf(t, d.x, o.x) - sc.bin_lo[0]) * sc.bin_scale[0], 0.f), top);
+        float qy = fminf(fmaxf((fmaf(t, d.y, o.y) - sc.bin_lo[1]) * sc.bin_scale[1], 0.f), top);
+        float qz = fminf(fmaxf((fmaf(t, d.z, o.z) - sc.bin_lo[2]) * sc.bin_scale[2], 0.f), top);
+        bin = spread3_dev((unsigned int)qx) | (spread3_dev((unsigned int)qy) << 1) | (spread3_dev((unsigned int)qz) << 2);
+    }
+    p.t_sbase[i] = (int)bin; // parked here until spawn_kernel overwrites it
+    atomicAdd(&p.bins[bin], 1u);
+}
+
+// One block: exclusive scan of bins[0 .. NODE_BINS] in place; counters[1] = end of the level's shadow rays.
+__global__ void __launch_bounds__(1024) node_scan_kernel(Pools p, int s_begin, int n_point_lights) {
+    __shared__ unsigned int warp_sum[32];
+    __shared__ unsigned int carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < NODE_BINS + 1; base += 1024) {
+        int j = base + tid;
+        unsigned int v = j < NODE_BINS + 1 ? p.bins[j] : 0u, x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sum[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned int w = warp_sum[lane], z = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                unsigned int y = __shfl_up_sync(0xffffffffu, z, o);
+                if (lane >= o) z += y;
+            }
+            warp_sum[lane] = z - w; // exclusive
+        }
+        __syncthreads();
+        unsigned int excl = carry + warp_sum[warp] + x - v;
+        if (j < NODE_BINS + 1) p.bins[j] = excl;
+        if (j == NODE_BINS) { // excl = number of hits
+            unsigned long long s_end = (unsigned long long)s_begin + (unsigned long long)excl * (unsigned long long)n_point_lights;
+            if (s_end > (unsigned long long)p.s_cap) p.counters[3] = 1u;
+            else p.counters[1] = (unsigned int)s_end;
+        }
+        __syncthreads();
+        if (tid == 1023) carry = excl + v;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) node_scatter_kernel(Pools p, int begin, int end) {
+    int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= end) return;
+    unsigned int pos = atomicAdd(&p.bins[p.t_sbase[i]], 1u);
+    p.t_order[begin + pos] = i;
+}
+
+__global__ void __launch_bounds__(WF_BLOCK)
+spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn_children, int ordered, int s_begin) {
+    const int rank = blockIdx.x * blockDim.x + threadIdx.x; // node number within the level when ordered
+    if (begin + rank >= end) return;
+    const int i = ordered ? p.t_order[begin + rank] : begin + rank;
     p.t_sbase[i] = -1;
     p.t_crefl[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     p.t_crefr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -83,8 +162,9 @@ spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn
 
     // shadow rays: p = point + 0.0002 * normal (render.rs:147); one per point light
     if (sc.n_point_lights > 0) {
-        unsigned int sb = atomicAdd(&p.counters[1], (unsigned int)sc.n_point_lights);
-        if (sb + (unsigned int)sc.n_point_lights <= (unsigned int)p.s_cap) {
+        unsigned long long sb = ordered ? (unsigned long long)s_begin + (unsigned long long)rank * (unsigned int)sc.n_point_lights
+                                        : (unsigned long long)atomicAdd(&p.counters[1], (unsigned int)sc.n_point_lights);
+        if (sb + (unsigned int)sc.n_point_lights <= (unsigned long long)p.s_cap) {
             p.t_sbase[i] = (int)sb;
             V3 sp = vadd(h.point, vscale(h.normal, 0.0002f));
             for (int l = 0; l < sc.n_lights; ++l) {
@@ -259,9 +339,15 @@ void launch_raygen(const FrameParams &fp, const Pools &p, long long sample0, int
     if (n > 0) raygen_kernel<<<nblk(n, WF_BLOCK), WF_BLOCK, 0, stream>>>(fp, p, sample0, n);
 }
 void launch_spawn(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int spawn_children,
-                  cudaStream_t stream) {
-    if (end > begin)
-        spawn_kernel<<<nblk(end - begin, WF_BLOCK), WF_BLOCK, 0, stream>>>(sc, fp, p, begin, end, spawn_children);
+                  int ordered, int s_begin, cudaStream_t stream) {
+    if (end <= begin) return;
+    if (ordered) {
+        cudaMemsetAsync(p.bins, 0, (NODE_BINS + 2) * sizeof(unsigned int), stream);
+        node_bin_kernel<<<nblk(end - begin, 256), 256, 0, stream>>>(sc, p, begin, end);
+        node_scan_kernel<<<1, 1024, 0, stream>>>(p, s_begin, sc.n_point_lights);
+        node_scatter_kernel<<<nblk(end - begin, 256), 256, 0, stream>>>(p, begin, end);
+    }
+    spawn_kernel<<<nblk(end - begin, WF_BLOCK), WF_BLOCK, 0, stream>>>(sc, fp, p, begin, end, spawn_children, ordered, s_begin);
 }
 void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level,
                   float4 *sample_rgb, const unsigned char *sample_mask, cudaStream_t stream) {
