@@ -135,24 +135,38 @@ static Bound bound_from(const double c[3], double rf) {
     return b;
 }
 
-// Sphere around the bounds of one group of GROUP_SLOTS slots (pads skipped): centre G = mean of
-// the members' centres.  A group with a member every ray must pass is itself passed by every
+// Sphere around the bounds of one group of GROUP_SLOTS slots (pads skipped): centre G = centre
+// of the members' box, moved a few times towards the member that reaches furthest.  A group with a member every ray must pass is itself passed by every
 // ray; a group of pads by none.
 // Margins: a member (C, R) at distance a from G passes a ray when dist^2(C, line) <= R^2 + mu;
 // then dist(G, line) <= a + sqrt(R^2 + mu), and (a + sqrt(R^2 + mu))^2 <= (a + R)^2 + (1 + a / R) mu.
 // The group radius therefore counts every member as at least a / 16 wide, and the sweep gives
 // group spheres 17 times the margin mu of a bound (sweep.cu: GROUP_MARGIN).
 static Bound make_group(const Bound *slots, const int *shape, int n) {
-    double c[3] = {0.0, 0.0, 0.0};
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
     int m = 0;
     for (int j = 0; j < n; ++j) {
         if (shape[j] < 0) continue;
         if (slots[j].w == -3.402823466e+38f) return Bound{0.f, 0.f, 0.f, -3.402823466e+38f, 0.0, 0.0};
-        c[0] += slots[j].cx; c[1] += slots[j].cy; c[2] += slots[j].cz;
+        const double p[3] = {slots[j].cx, slots[j].cy, slots[j].cz};
+        for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p[a] - slots[j].rf); hi[a] = std::max(hi[a], p[a] + slots[j].rf); }
         ++m;
     }
     if (m == 0) return Bound{0.f, 0.f, 0.f, 3.402823466e+38f, 0.0, 0.0};
-    c[0] /= m; c[1] /= m; c[2] /= m;
+    double c[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
+    for (int it = 0; it < 8 && m > 1; ++it) { // shrink: step towards the furthest-reaching member by half its lead
+        double far1 = -1.0, far2 = -1.0, dir[3] = {0.0, 0.0, 0.0}, dist1 = 0.0;
+        for (int j = 0; j < n; ++j) {
+            if (shape[j] < 0) continue;
+            double dx = slots[j].cx - c[0], dy = slots[j].cy - c[1], dz = slots[j].cz - c[2];
+            double a = std::sqrt(dx * dx + dy * dy + dz * dz), reach = a + slots[j].rf;
+            if (reach > far1) { far2 = far1; far1 = reach; dir[0] = dx; dir[1] = dy; dir[2] = dz; dist1 = a; }
+            else if (reach > far2) far2 = reach;
+        }
+        if (!(dist1 > 1e-12) || far2 < 0.0) break;
+        double step = std::min(0.5 * (far1 - far2), dist1) / dist1;
+        c[0] += dir[0] * step; c[1] += dir[1] * step; c[2] += dir[2] * step;
+    }
     double rg = 0.0;
     for (int j = 0; j < n; ++j) {
         if (shape[j] < 0) continue;
@@ -161,15 +175,6 @@ static Bound make_group(const Bound *slots, const int *shape, int n) {
         rg = std::max(rg, a + std::max(slots[j].rf, a / 16.0));
     }
     return bound_from(c, rg * (1.0 + 1e-9));
-}
-
-static uint32_t spread3(uint32_t x) { // 10 bits -> every third bit
-    x &= 0x3ffu;
-    x = (x | (x << 16)) & 0x030000ffu;
-    x = (x | (x << 8)) & 0x0300f00fu;
-    x = (x | (x << 4)) & 0x030c30c3u;
-    x = (x | (x << 2)) & 0x09249249u;
-    return x;
 }
 
 // Margin factor of a segment ("filter margins"): 1.5 x (32 for the filter's own
@@ -363,7 +368,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     std::vector<int> plane_shape;
     std::vector<float4> plane_data;
     // error class of a bound: 0 similarity-transformed spheres, 1 triangles, 2 the rest
-    struct B { Bound b; int shape; int cls; double aniso; uint32_t morton; };
+    struct B { Bound b; int shape; int cls; double aniso; };
     std::vector<B> bounds;
     const float tri_scale = tri_bound_scale();
     int counts[4] = {0, 0, 0, 0}, planes_identity = 0, first_nan = -1;
@@ -421,33 +426,41 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         }
         }
     }
-    // segments by error class, each padded to SEG_PAD slots; within a class in Morton order of
-    // the centres, so that the GROUP_SLOTS slots of a group are neighbours in space; slot pairs
-    // interleaved for FFMA2
+    // segments by error class, each padded to SEG_PAD slots; within a class the bounds are put in
+    // the leaf order of a median-split tree whose leaves hold exactly GROUP_SLOTS bounds, so that
+    // the slots of a group are neighbours in space; slot pairs interleaved for FFMA2
+    std::stable_sort(bounds.begin(), bounds.end(), [](const B &a, const B &b) {
+        bool fa = a.b.w != -3.402823466e+38f, fb = b.b.w != -3.402823466e+38f; // beyond-range bounds last in their class
+        return a.cls != b.cls ? a.cls < b.cls : (fa && !fb);
+    });
     {
-        double lo[3][3], hi[3][3];
-        for (int c = 0; c < 3; ++c)
-            for (int a = 0; a < 3; ++a) { lo[c][a] = 1e300; hi[c][a] = -1e300; }
-        for (const B &x : bounds) {
-            if (x.b.w == -3.402823466e+38f) continue;
-            const double p[3] = {x.b.cx, x.b.cy, x.b.cz};
-            for (int a = 0; a < 3; ++a) { lo[x.cls][a] = std::min(lo[x.cls][a], p[a]); hi[x.cls][a] = std::max(hi[x.cls][a], p[a]); }
+        auto coord = [](const B &x, int ax) { return ax == 0 ? x.b.cx : (ax == 1 ? x.b.cy : x.b.cz); };
+        std::vector<std::pair<int, int>> work; // [begin, end) ranges still to split
+        for (size_t i = 0; i < bounds.size();) {
+            size_t j = i;
+            while (j < bounds.size() && bounds[j].cls == bounds[i].cls && bounds[j].b.w != -3.402823466e+38f) ++j;
+            if (j > i) work.push_back({(int)i, (int)j});
+            while (j < bounds.size() && bounds[j].cls == bounds[i].cls) ++j;
+            i = j;
         }
-        for (B &x : bounds) {
-            x.morton = 0xffffffffu;
-            if (x.b.w == -3.402823466e+38f) continue;
-            const double p[3] = {x.b.cx, x.b.cy, x.b.cz};
-            uint32_t q[3];
-            for (int a = 0; a < 3; ++a) {
-                double ext = hi[x.cls][a] - lo[x.cls][a];
-                double t = ext > 0.0 ? (p[a] - lo[x.cls][a]) / ext : 0.0;
-                q[a] = (uint32_t)std::min(1023.0, std::max(0.0, t * 1024.0));
-            }
-            x.morton = spread3(q[0]) | (spread3(q[1]) << 1) | (spread3(q[2]) << 2);
+        while (!work.empty()) {
+            auto [lo, hi] = work.back();
+            work.pop_back();
+            const int n = hi - lo;
+            if (n <= GROUP_SLOTS) continue;
+            float mn[3] = {3.4e38f, 3.4e38f, 3.4e38f}, mx[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+            for (int i = lo; i < hi; ++i)
+                for (int ax = 0; ax < 3; ++ax) { mn[ax] = std::min(mn[ax], coord(bounds[i], ax)); mx[ax] = std::max(mx[ax], coord(bounds[i], ax)); }
+            int ax = 0;
+            if (mx[1] - mn[1] > mx[ax] - mn[ax]) ax = 1;
+            if (mx[2] - mn[2] > mx[ax] - mn[ax]) ax = 2;
+            const int groups = (n + GROUP_SLOTS - 1) / GROUP_SLOTS, left = (groups / 2) * GROUP_SLOTS;
+            std::nth_element(bounds.begin() + lo, bounds.begin() + lo + left, bounds.begin() + hi,
+                             [&](const B &a, const B &b) { return coord(a, ax) < coord(b, ax); });
+            work.push_back({lo, lo + left});
+            work.push_back({lo + left, hi});
         }
     }
-    std::stable_sort(bounds.begin(), bounds.end(),
-                     [](const B &a, const B &b) { return a.cls != b.cls ? a.cls < b.cls : a.morton < b.morton; });
     const int nb = (int)bounds.size();
     SweepSegs segs;
     std::memset(&segs, 0, sizeof(segs));
