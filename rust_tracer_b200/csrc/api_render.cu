@@ -187,6 +187,7 @@ struct Accum {
     unsigned long long tree_rays = 0, shadow_rays = 0, nodes = 0, exact = 0;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> sweep_spans;
     std::vector<long long> sweep_rays; // rays of each span (RT_B200_TRACE)
+    std::vector<unsigned long long> sweep_counts; // device counters after each span: exact, general evals, origin evals (trace only)
     double filter_fma = 0.0;           // FMAs executed by the sweeps' filters
 };
 
@@ -222,6 +223,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     Pools &p = ws.pools;
     const int rpt = env_int("RT_B200_RAYS_PER_THREAD", 0, 0, 4);
     const bool audit = (flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
+    const bool trace = std::getenv("RT_B200_TRACE") != nullptr;
     lv = BandLevels();
 
     unsigned int init[4] = {(unsigned int)n, 0u, 0u, 0u};
@@ -248,6 +250,12 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         cudaEventRecord(e1, st);
         acc.sweep_spans.push_back({e0, e1});
         acc.sweep_rays.push_back((long long)a.n + b.n);
+        if (trace) { // per-sweep counters: costs a synchronisation per sweep, tracing only
+            unsigned long long c[3] = {0, 0, 0};
+            cudaMemcpyAsync(c, ws.exact_counter, sizeof(c), cudaMemcpyDeviceToHost, st);
+            cudaStreamSynchronize(st);
+            acc.sweep_counts.insert(acc.sweep_counts.end(), c, c + 3);
+        }
         scene->launches += 1;
         if (audit) acc.exact += (unsigned long long)(a.n + b.n) * (unsigned long long)sc.n_bounded;
     };
@@ -451,8 +459,17 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
             cudaEventElapsedTime(&t, acc.sweep_spans[i].first, acc.sweep_spans[i].second);
             sweep += t;
             if (trace)
-                std::fprintf(stderr, "[rt_b200] sweep %zu: %lld rays %.3f ms (%.2f Tpairs/s)\n", i, acc.sweep_rays[i], t,
-                             (double)acc.sweep_rays[i] * scene->dev.n_bounded / (t * 1e-3) / 1e12);
+            {
+                double ex = 0, ev = 0;
+                if (acc.sweep_counts.size() >= 3 * (i + 1)) {
+                    const unsigned long long *c = &acc.sweep_counts[3 * i], zero[3] = {0, 0, 0}, *q = i ? c - 3 : zero;
+                    ex = (double)(c[0] - q[0]); ev = (double)(c[1] - q[1]) + (double)(c[2] - q[2]);
+                    if (c[0] < q[0]) { ex = (double)c[0]; ev = (double)c[1] + (double)c[2]; } // counters were reset (band recast)
+                }
+                std::fprintf(stderr, "[rt_b200] sweep %zu: %lld rays %.3f ms (%.2f Tpairs/s) evals/ray %.0f exact/ray %.1f\n", i,
+                             acc.sweep_rays[i], t, (double)acc.sweep_rays[i] * scene->dev.n_bounded / (t * 1e-3) / 1e12,
+                             ev / (double)acc.sweep_rays[i], ex / (double)acc.sweep_rays[i]);
+            }
         }
         if (trace) std::fprintf(stderr, "[rt_b200] frame %.3f ms, sweeps %.3f ms\n", ms, sweep);
         stats->total_ms = ms;

@@ -501,6 +501,13 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         return out;
     };
     std::vector<float4> bound = paired(slots), group = paired(groups);
+    std::vector<int2> slot_meta(n_slots);
+    std::vector<float4> slot_geom(3 * (size_t)n_slots, make_float4(0.f, 0.f, 0.f, 0.f));
+    for (int j = 0; j < n_slots; ++j) {
+        const int sh = bound_shape[j];
+        slot_meta[j] = make_int2(sh >= 0 ? meta[sh].x : -1, sh);
+        if (sh >= 0) for (int k = 0; k < 3; ++k) slot_geom[3 * (size_t)j + k] = geom[3 * (size_t)sh + k];
+    }
 
     std::vector<DevMaterial> mats;
     int rc = convert_materials(desc->materials, desc->n_materials, mats);
@@ -536,10 +543,10 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
             for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], c[a] - b.rf); hi[a] = std::max(hi[a], c[a] + b.rf); }
         }
         for (int a = 0; a < 3; ++a) {
-            double ext = hi[a] - lo[a];
+            double ext = (hi[a] - lo[a]) * 1.5; // half as large again: the floor under and around the shapes is inside
             bool ok = ext > 0.0 && std::isfinite(ext) && ext < 1e30;
-            d.bin_lo[a] = ok ? (float)lo[a] : 0.f;
-            d.bin_scale[a] = ok ? (float)((double)(1 << NODE_BIN_BITS) / ext) : 0.f;
+            d.bin_lo[a] = ok ? (float)(lo[a] - ext / 6.0) : 0.f;
+            d.bin_scale[a] = ok ? (float)(2.0 / ext) : 0.f; // (x - lo) * scale - 1 in [-1, 1] inside the box
         }
     }
     cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
@@ -547,7 +554,8 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     d.amb_r = desc->ambient[0]; d.amb_g = desc->ambient[1]; d.amb_b = desc->ambient[2];
     const DevMaterial *dm = nullptr;
     if ((rc = upload(s, bound, &d.bound)) != RT_OK || (rc = upload(s, group, &d.group)) != RT_OK ||
-        (rc = upload(s, bound_shape, &d.bound_shape)) != RT_OK ||
+        (rc = upload(s, bound_shape, &d.bound_shape)) != RT_OK || (rc = upload(s, slot_meta, &d.slot_meta)) != RT_OK ||
+        (rc = upload(s, slot_geom, &d.slot_geom)) != RT_OK ||
         (rc = upload(s, meta, &d.shape_meta)) != RT_OK || (rc = upload(s, geom, &d.geom)) != RT_OK ||
         (rc = upload(s, plane_shape, &d.plane_shape)) != RT_OK || (rc = upload(s, plane_data, &d.plane_data)) != RT_OK ||
         (rc = upload(s, ctris, &d.cube_tris)) != RT_OK || (rc = upload(s, mats, &dm)) != RT_OK ||

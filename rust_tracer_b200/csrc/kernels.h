@@ -86,8 +86,9 @@ struct FrameParams {
     int forest_shading;
 };
 
-constexpr int NODE_BIN_BITS = 5;                    // per axis
-constexpr int NODE_BINS = 1 << (3 * NODE_BIN_BITS); // + one bin for the rays that missed
+constexpr int NODE_BIN_BITS = 5, NODE_FAR_BITS = 4; // per axis: hit points inside / outside the shapes' box
+constexpr int NODE_FAR_BINS = 1 << (3 * NODE_FAR_BITS);
+constexpr int NODE_BINS = NODE_FAR_BINS + (1 << (3 * NODE_BIN_BITS)); // + one bin for the rays that missed
 
 // Primary rays for samples [s0, s0 + n) of this call into tree rays [0, n).
 void launch_raygen(const FrameParams &fp, const Pools &p, long long sample0, int n, cudaStream_t stream);

@@ -16,6 +16,10 @@
 //                                             neighbours in space (Morton order within a segment).
 //                                             A warp skips a group none of its rays can touch.
 //   bound_shape[j] int32                      shape id of bound slot j, -1 for a pad
+//   slot_meta[j]   int2  (kind, shape id)     and
+//   slot_geom[3*j..] 3 x float4               copies of shape_meta / geom in SLOT order: the exact
+//                                             stage of the sweep reads them straight from the queued
+//                                             slot number, in one round trip instead of three
 //   shape_meta[s]  int4  (kind, material, plane index, 0)
 //   geom[3*s..]    3 x float4                 sphere/cube/plane: rows 0..2 of inv_transform
 //                                             triangle: v0.xyz v1.x | v1.yz v2.xy | v2.z n.xyz
@@ -75,10 +79,12 @@ struct DevScene {
     int n_point_lights;
     int first_nan_shape; // first sphere/triangle/cube in id order, -1 if none (NaN rays)
     float amb_r, amb_g, amb_b;
-    float bin_lo[3], bin_scale[3]; // node cell = (hit point - bin_lo) * bin_scale, clamped (wavefront.cu)
+    float bin_lo[3], bin_scale[3]; // (hit point - bin_lo) * bin_scale - 1 is in [-1, 1] inside the box of the bounded shapes (wavefront.cu: node cells)
     const float4 *bound;
     const float4 *group;    // n_slots / GROUP_SLOTS group spheres, paired like bound
     const int *bound_shape;
+    const int2 *slot_meta;
+    const float4 *slot_geom;
     const int4 *shape_meta; // (kind, material, plane index or -1, 0)
     const float4 *geom;
     const int *plane_shape;

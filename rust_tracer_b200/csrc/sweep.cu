@@ -80,6 +80,23 @@ RT_DEV unsigned long long exact_pair(const int4 *shape_meta, const float4 *geom,
     return make_key(t, shape);
 }
 
+// The same from a slot's own copy of (kind, shape id, geometry).
+RT_DEV unsigned long long exact_slot(int kind, int shape, const float4 *g, const float4 *cube_tris, V3 o, V3 d) {
+    float t;
+    if (kind == KIND_SPHERE) {
+        bool entering;
+        if (!exact_sphere(load_m34(g), o, d, t, entering)) return KEY_MISS;
+    } else if (kind == KIND_TRIANGLE) {
+        float u, v, det;
+        if (!exact_triangle(load_tri(g), o, d, t, u, v, det)) return KEY_MISS;
+    } else { // cube
+        float u, v, det;
+        int which;
+        if (!exact_cube(load_m34(g), cube_tris, o, d, t, which, u, v, det)) return KEY_MISS;
+    }
+    return make_key(t, shape);
+}
+
 __device__ __noinline__ unsigned long long plane_keys(int n_planes, const int *plane_shape, const float4 *plane_data,
                                                       const float4 *geom, V3 o, V3 d, unsigned long long best) {
     for (int p = 0; p < n_planes; ++p) {
@@ -99,10 +116,9 @@ __device__ __noinline__ unsigned long long plane_keys(int n_planes, const int *p
 // it in registers (and the compiler cannot hoist the loads of these kernel parameters into it).
 struct SweepCtx {
     RaySeg s0, s1;
-    const int4 *shape_meta;
-    const float4 *geom;
+    const int2 *slot_meta;
+    const float4 *slot_geom;
     const float4 *cube_tris;
-    const int *bound_shape;
 };
 
 // Run queued pairs 32 at a time, one exact test per lane; a partial batch stays queued unless
@@ -117,9 +133,12 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
             unsigned int pair = wqueue[idx];
             int local = pair >> 24; // (ray of the warp batch << 24) | bound slot
             int j = pair & 0xFFFFFF;
+            // ray, kind and geometry are all addressed by the queue entry: independent loads, one round trip
+            const int2 sm = ctx->slot_meta[j];
+            const float4 *gp = ctx->slot_geom + 3 * j;
+            const float4 g[3] = {gp[0], gp[1], gp[2]};
             RayRegs rr = load_ray(ctx->s0, ctx->s1, ray0 + local);
-            unsigned long long k = exact_pair(ctx->shape_meta, ctx->geom, ctx->cube_tris, ctx->bound_shape[j],
-                                              v3(rr.ox, rr.oy, rr.oz), v3(rr.dx, rr.dy, rr.dz));
+            unsigned long long k = exact_slot(sm.x, sm.y, g, ctx->cube_tris, v3(rr.ox, rr.oy, rr.oz), v3(rr.dx, rr.dy, rr.dz));
             if (k != KEY_MISS) atomicMin(&wbest[local], k);
         }
         done += 32;
@@ -213,7 +232,7 @@ RT_DEV float2 f2(float x) { return make_float2(x, x); }
 template <int R, int SWEEP_THREADS, bool ORIGIN>
 __global__ void __launch_bounds__(SWEEP_THREADS, 1)
 sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, int slot_end, int n_slices, int slice_slots,
-             int merge, int planes, unsigned int *batch_counter, unsigned long long *exact_counter) {
+             int merge, int planes, int item_max, unsigned int *batch_counter, unsigned long long *exact_counter) {
     constexpr int SWEEP_WARPS = SWEEP_THREADS / 32;
     constexpr unsigned int FULL = 0xffffffffu;
     extern __shared__ float4 smem[];
@@ -244,7 +263,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
     }
     if (tid == 0) {
         ctx.s0 = s0; ctx.s1 = s1;
-        ctx.shape_meta = sc.shape_meta; ctx.geom = sc.geom; ctx.cube_tris = sc.cube_tris; ctx.bound_shape = sc.bound_shape;
+        ctx.slot_meta = sc.slot_meta; ctx.slot_geom = sc.slot_geom; ctx.cube_tris = sc.cube_tris;
     }
     if (lane == 0) { n_exact[warp] = 0; n_iters[warp] = 0; }
     __syncthreads();
@@ -278,7 +297,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
         int qn = 0; // queued pairs of this warp (warp-uniform)
 
         // ---- phase 1 + 2 --------------------------------------------------------------
-        unsigned int iters = 0; // pair-of-slots (or pair-of-groups) filter iterations of this item
+        unsigned int evals = 0; // filter evaluations of this item, in units of 32 (one per lane)
         for (int g = 0; g < sc.segs.n; ++g) {
             const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
             if (gb >= ge) continue;
@@ -310,7 +329,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
             float4 G0 = gtab0[gb >> 4], G1 = gtab0[(gb >> 4) + 1]; // next pair of groups, fetched one step ahead
             for (int j0 = gb; j0 < ge; j0 += 2 * GROUP_SLOTS) {
                 // which of the two groups can any ray of this warp touch?
-                unsigned int pass;
+                unsigned int ball0, ball1, pm = 0;
                 {
                     const float4 T0 = G0, T1 = G1;
                     G0 = gtab0[(j0 >> 4) + 2]; G1 = gtab0[(j0 >> 4) + 3]; // past the end: the slack pair
@@ -319,15 +338,70 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                     float m0 = e[0].x, m1 = e[0].y;
 #pragma unroll
                     for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
-                    pass = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
-                    ++iters;
+                    ball0 = __ballot_sync(FULL, m0 >= T1.z);
+                    ball1 = __ballot_sync(FULL, m1 >= T1.w);
+                    evals += 2 * R;
+                    const int p0 = __popc(ball0), p1 = __popc(ball1);
+                    if ((p0 && p0 <= item_max) || (p1 && p1 <= item_max)) { // bit 2r + h of pm: ray r of this lane may touch group h
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            if (e[r].x >= T1.z) pm |= 1u << (2 * r);
+                            if (e[r].y >= T1.w) pm |= 2u << (2 * r);
+                        }
+                        pm &= vmask;
+                    }
                 }
                 for (int h = 0; h < 2; ++h) {
-                    if (!((pass >> h) & 1u)) continue;
+                    const unsigned int gball = h ? ball1 : ball0; // lanes with a ray that may touch group h
+                    if (!gball) continue;
                     const int jg = j0 + h * GROUP_SLOTS;
+                    if (__popc(gball) <= item_max) {
+                        // Few (ray, group) pairs: one pair per half warp, lane = slot of the group.
+                        const int js = jg + (lane & (GROUP_SLOTS - 1));
+                        const float *ts = (const float *)(tab0 + (js & ~1)) + (js & 1);
+                        const float scx = ts[0], scy = ts[2], scz = ts[4], sw = ts[6];
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            unsigned int ball = __ballot_sync(FULL, (pm >> (2 * r + h)) & 1u);
+                            while (ball) {
+                                const int l0 = __ffs(ball) - 1;
+                                ball &= ball - 1;
+                                int l1 = -1;
+                                if (ball) { l1 = __ffs(ball) - 1; ball &= ball - 1; }
+                                const int src = (lane < 16 || l1 < 0) ? l0 : l1;
+                                float ev, clip = 3.4e38f;
+                                if constexpr (ORIGIN) {
+                                    const float dx = __shfl_sync(FULL, c[r].dx, src), dy = __shfl_sync(FULL, c[r].dy, src),
+                                                dz = __shfl_sync(FULL, c[r].dz, src), mu = __shfl_sync(FULL, c[r].mu, src);
+                                    clip = __shfl_sync(FULL, c[r].tf, src);
+                                    const float b = fmaf(scx, dx, fmaf(scy, dy, scz * dz));
+                                    ev = fmaf(b, b, mu);
+                                } else {
+                                    const float dx = __shfl_sync(FULL, c[r].dx, src), dy = __shfl_sync(FULL, c[r].dy, src),
+                                                dz = __shfl_sync(FULL, c[r].dz, src), kb = __shfl_sync(FULL, c[r].kb, src);
+                                    const float ox2 = __shfl_sync(FULL, c[r].ox2, src), oy2 = __shfl_sync(FULL, c[r].oy2, src),
+                                                oz2 = __shfl_sync(FULL, c[r].oz2, src), seed = __shfl_sync(FULL, c[r].seed, src);
+                                    const float b = fmaf(scx, dx, fmaf(scy, dy, fmaf(scz, dz, kb)));
+                                    const float sv = fmaf(scx, ox2, fmaf(scy, oy2, fmaf(scz, oz2, seed)));
+                                    ev = fmaf(b, b, sv);
+                                }
+                                ++evals;
+                                const bool cand = ev >= sw && ev <= clip && (lane < 16 || l1 >= 0);
+                                const unsigned int cball = __ballot_sync(FULL, cand);
+                                if (cball) {
+                                    if (qn > QCAP - 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
+                                    if (cand) wqueue[qn + __popc(cball & lt_mask)] = ((unsigned int)(r * 32 + src) << 24) | (unsigned int)js;
+                                    qn += __popc(cball);
+                                    __syncwarp();
+                                }
+                            }
+                        }
+                        if (qn >= 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
+                        continue;
+                    }
                     const float4 *tp = tab0 + jg;
                     float4 N0 = tp[0], N1 = tp[1]; // next slot pair, fetched one iteration ahead
-                    iters += GROUP_SLOTS / 2;
+                    evals += (GROUP_SLOTS / 2) * 2 * R;
 #pragma unroll 4
                     for (int i = 0; i < GROUP_SLOTS / 2; ++i) {
                         const float4 T0 = N0, T1 = N1;
@@ -368,7 +442,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                 }
             }
         }
-        if (lane == 0) n_iters[warp] += iters;
+        if (lane == 0) n_iters[warp] += evals;
         __syncwarp();
         sweep_flush(&ctx, wqueue, wbest, ray0, qn, 1, &n_exact[warp]);
 
@@ -399,7 +473,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
     if (exact_counter && lane == 0) {
         if (n_exact[warp]) atomicAdd(exact_counter, (unsigned long long)n_exact[warp]);
         // (ray, sphere) pairs the filter evaluated: 2 spheres x 32 R rays per iteration
-        if (n_iters[warp]) atomicAdd(exact_counter + (ORIGIN ? 2 : 1), n_iters[warp] * (unsigned long long)(64 * R));
+        if (n_iters[warp]) atomicAdd(exact_counter + (ORIGIN ? 2 : 1), n_iters[warp] * 32ull);
     }
 }
 
@@ -451,6 +525,11 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
     }
     const int n_chunks = std::max(1, (sc.n_slots + cap - 1) / cap);
     if (n_chunks > n_counters) return cudaErrorInvalidValue;
+    // lanes of a warp with a ray touching a group up to which the group is swept (ray, group)
+    // pair by pair (lane = slot) rather than all 32 R rays against all its slots: about where the
+    // two cost the same
+    int item_max = 16;
+    if (const char *e = std::getenv("RT_B200_ITEM_MAX")) item_max = std::atoi(e);
     // chunks of equal size (rounded to SEG_PAD) rather than cap, cap, ..., rest
     const int per = ((sc.n_slots + n_chunks - 1) / n_chunks + SEG_PAD - 1) / SEG_PAD * SEG_PAD;
     const long long batches = (total + 32ll * R - 1) / (32ll * R);
@@ -481,7 +560,7 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
         cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
         sweep_kernel<R, T, ORIGIN><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, n_slices, slice_slots, merge,
-                                                              c == n_chunks - 1 ? 1 : 0, batch_counters + c, exact_counter);
+                                                              c == n_chunks - 1 ? 1 : 0, item_max, batch_counters + c, exact_counter);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
     }
     *used = n_chunks;

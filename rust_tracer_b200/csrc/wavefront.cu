@@ -82,11 +82,26 @@ __global__ void __launch_bounds__(256) node_bin_kernel(DevScene sc, Pools p, int
         o = v3(a.x, a.y, a.z);
         d = v3(a.w, b.x, b.y);
         float t = key_t(key); // only a sort key: any point near the hit will do
-        const float top = (float)((1 << NODE_BIN_BITS) - 1);
-        float qx = fminf(fmaxf((fmaf(t, d.x, o.x) - sc.bin_lo[0]) * sc.bin_scale[0], 0.f), top);
-        float qy = fminf(fmaxf((fmaf(t, d.y, o.y) - sc.bin_lo[1]) * sc.bin_scale[1], 0.f), top);
-        float qz = fminf(fmaxf((fmaf(t, d.z, o.z) - sc.bin_lo[2]) * sc.bin_scale[2], 0.f), top);
-        bin = spread3_dev((unsigned int)qx) | (spread3_dev((unsigned int)qy) << 1) | (spread3_dev((unsigned int)qz) << 2);
+        // u in [-1, 1]^3 inside the box of the bounded shapes: NODE_BIN_BITS bits per axis, Morton
+        // order.  Hit points outside (the far reaches of a plane) get coarser cells of u / (1 + |u|)
+        // and come FIRST: their rays carry large margins and are the expensive ones, so the
+        // sweeps start them early instead of finishing on them.
+        const float ux = fmaf(fmaf(t, d.x, o.x) - sc.bin_lo[0], sc.bin_scale[0], -1.f);
+        const float uy = fmaf(fmaf(t, d.y, o.y) - sc.bin_lo[1], sc.bin_scale[1], -1.f);
+        const float uz = fmaf(fmaf(t, d.z, o.z) - sc.bin_lo[2], sc.bin_scale[2], -1.f);
+        const bool inside = fabsf(ux) <= 1.f && fabsf(uy) <= 1.f && fabsf(uz) <= 1.f; // false for NaN
+        if (inside) {
+            const float half = (float)(1 << (NODE_BIN_BITS - 1)), top = 2.f * half - 1.f;
+            auto cell = [=](float u) { return (unsigned int)fminf(fmaxf((u + 1.f) * half, 0.f), top); };
+            bin = NODE_FAR_BINS + (spread3_dev(cell(ux)) | (spread3_dev(cell(uy)) << 1) | (spread3_dev(cell(uz)) << 2));
+        } else {
+            auto cell = [](float u) {
+                float c = u / (1.f + fabsf(u)); // (-1, 1); NaN -> cell 0 below
+                float q = (c + 1.f) * (float)(1 << (NODE_FAR_BITS - 1));
+                return !(q >= 0.f) ? 0u : (unsigned int)fminf(q, (float)((1 << NODE_FAR_BITS) - 1));
+            };
+            bin = spread3_dev(cell(ux)) | (spread3_dev(cell(uy)) << 1) | (spread3_dev(cell(uz)) << 2);
+        }
     }
     p.t_sbase[i] = (int)bin; // parked here until spawn_kernel overwrites it
     atomicAdd(&p.bins[bin], 1u);
