@@ -148,12 +148,12 @@ int Workspace::ensure_mask(long long n) {
 
 int Workspace::ensure_misc() {
     int rc;
-    if (!pools.counters && (rc = dev_alloc(&pools.counters, 4, "counters"))) return rc;
+    if (!pools.counters && (rc = dev_alloc(&pools.counters, N_COUNTERS, "counters"))) return rc;
     if (!pools.bins && (rc = dev_alloc(&pools.bins, NODE_BINS + 2, "bins"))) return rc;
     if (!exact_counter && (rc = dev_alloc(&exact_counter, 3, "exact_counter"))) return rc;
     if (!batch_counters && (rc = dev_alloc(&batch_counters, BATCH_COUNTERS, "batch_counters"))) return rc;
     if (!h_counters) {
-        cudaError_t e = cudaMallocHost((void **)&h_counters, 4 * sizeof(unsigned int) + 3 * sizeof(unsigned long long));
+        cudaError_t e = cudaMallocHost((void **)&h_counters, N_COUNTERS * sizeof(unsigned int) + 3 * sizeof(unsigned long long));
         if (e != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
     }
     return RT_OK;
@@ -192,10 +192,10 @@ struct Accum {
 };
 
 // exact-test count and filter FMA count of the sweeps, from the device counters read back into
-// ws.h_counters + 4: [0] exact tests, [1] pairs through the general filter, [2] through the origin filter
+// ws.h_counters + N_COUNTERS: [0] exact tests, [1] pairs through the general filter, [2] through the origin filter
 static void read_sweep_counters(const Workspace &ws, Accum &acc) {
     unsigned long long c[3];
-    std::memcpy(c, ws.h_counters + 4, sizeof(c));
+    std::memcpy(c, ws.h_counters + N_COUNTERS, sizeof(c));
     acc.exact = c[0];
     acc.filter_fma = (double)c[1] * FILTER_FMA_GENERAL + (double)c[2] * FILTER_FMA_ORIGIN;
 }
@@ -226,7 +226,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     const bool trace = std::getenv("RT_B200_TRACE") != nullptr;
     lv = BandLevels();
 
-    unsigned int init[4] = {(unsigned int)n, 0u, 0u, 0u};
+    unsigned int init[N_COUNTERS] = {(unsigned int)n, 0u, 0u, 0u, 0u, 0u};
     CK(cudaMemcpyAsync(p.counters, init, sizeof(init), cudaMemcpyHostToDevice, st), "counters init");
     CK(cudaMemsetAsync(ws.batch_counters, 0, BATCH_COUNTERS * sizeof(unsigned int), st), "batch counters");
     ws.batch_next = 0;
@@ -267,28 +267,35 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     // (one column of the [node][light] pool) against that light's; the rest as one general sweep.
     const bool by_origin = !audit && !scene->light_tabs.empty() && scene->cam.bound;
     const int npl = std::max(sc.n_point_lights, 1);
-    auto sweep_level = [&](int level, int tb, int te, int sb, int se) {
+    // heavy_tree / heavy_nodes: how many of the level's first tree rays / of the previous level's
+    // first nodes start far outside the scene (counters[4], [5]); their sweeps get finer work items
+    auto sweep_level = [&](int level, int tb, int te, int sb, int se, int heavy_tree, int heavy_nodes) {
         if (!by_origin) {
             sweep(tree_seg(tb, te), shadow_seg(sb, se), general);
             return;
         }
-        sweep(tree_seg(tb, te), none, level == 0 ? scene->cam : general);
+        RaySeg tree = tree_seg(tb, te);
+        tree.heavy = std::min(heavy_tree, tree.n);
+        sweep(tree, none, level == 0 ? scene->cam : general);
         if (se > sb) {
             cudaError_t e = cudaMemsetAsync(p.s_key + sb, 0xFF, sizeof(unsigned long long) * (size_t)(se - sb), st);
             if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
-            for (int l = 0; l < sc.n_point_lights; ++l)
-                sweep(RaySeg{p.s_a + sb + l, p.s_b + sb + l, p.s_key + sb + l, (se - sb) / npl, npl, 1}, none,
-                      scene->light_tabs[l]);
+            for (int l = 0; l < sc.n_point_lights; ++l) {
+                RaySeg sh{p.s_a + sb + l, p.s_b + sb + l, p.s_key + sb + l, (se - sb) / npl, npl, 1};
+                sh.heavy = std::min(heavy_nodes, sh.n);
+                sweep(sh, none, scene->light_tabs[l]);
+            }
         }
     };
 
     int tb = 0, te = n, sb = 0, se = 0; // current tree level, previous level's shadows
+    int heavy_tree = 0, heavy_nodes = 0;
     int k = 0;
     for (; k < fp.depth; ++k) {
-        sweep_level(k, tb, te, sb, se);
+        sweep_level(k, tb, te, sb, se, heavy_tree, heavy_nodes);
         launch_spawn(sc, fp, p, tb, te, (k + 1 < fp.depth) ? 1 : 0, by_origin ? 1 : 0, se, st);
         if (te > tb) scene->launches += by_origin ? 4 : 1;
-        CK(cudaMemcpyAsync(ws.h_counters, p.counters, 4 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st), "counters readback");
+        CK(cudaMemcpyAsync(ws.h_counters, p.counters, N_COUNTERS * sizeof(unsigned int), cudaMemcpyDeviceToHost, st), "counters readback");
         CK(cudaStreamSynchronize(st), "wavefront level");
         if (ws.h_counters[3]) return 1; // pool overflow
         lv.tb.push_back(tb); lv.te.push_back(te);
@@ -296,9 +303,13 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         lv.sb.push_back(se); lv.se.push_back(new_se);
         sb = se; se = new_se;
         tb = te; te = new_te;
+        // far nodes come first in the node order, and their children (allocated as spawn runs
+        // through that order) early in the next level: allow for the blocks in flight
+        heavy_nodes = by_origin ? (int)ws.h_counters[4] : 0;
+        heavy_tree = (by_origin && ws.h_counters[5]) ? (int)std::min<long long>(2ll * ws.h_counters[5] + 65536, te - tb) : 0;
         if (tb == te && sb == se) break; // nothing left to cast
     }
-    sweep_level(-1, 0, 0, sb, se); // shadows of the last level
+    sweep_level(-1, 0, 0, sb, se, 0, heavy_nodes); // shadows of the last level
     lv.nodes = ws.h_counters[2];
     CK(sweep_err, "sweep launch");
     CK(cudaGetLastError(), "wavefront launch");
@@ -445,7 +456,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
         if (n > 0) scene->launches += 1;
     }
     cudaEventRecord(ev1, st);
-    CK(cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
+    CK(cudaMemcpyAsync(ws.h_counters + N_COUNTERS, ws.exact_counter, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
     CK(cudaStreamSynchronize(st), "render");
     CK(cudaGetLastError(), "render");
     if (!(pr->flags & RT_FLAG_AUDIT_ALL_PAIRS)) read_sweep_counters(ws, acc);
@@ -570,7 +581,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
         return rc;
     }
     cudaEventRecord(ev1, st);
-    cudaMemcpyAsync(ws.h_counters + 4, ws.exact_counter, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(ws.h_counters + N_COUNTERS, ws.exact_counter, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) {
         rt_forest_destroy(f);

@@ -18,6 +18,8 @@ struct RaySeg {
     int n;
     int stride = 1;
     int preset = 0; // the caller has already set every key to KEY_MISS (required when stride > 1)
+    int heavy = 0;  // the first `heavy` rays are expensive (origins far outside the scene: large filter
+                    // margins); their batches are cut into more table slices so that no work item runs long
 };
 
 // The bound table seen from one point O' (a light, the camera): slot j holds
@@ -71,7 +73,9 @@ struct Pools {
     float4 *s_a, *s_b;
     unsigned long long *s_key;
     int s_cap;
-    // device counters: [0] tree rays allocated, [1] shadow rays allocated, [2] nodes, [3] overflow flag
+    // device counters: [0] tree rays allocated, [1] shadow rays allocated, [2] nodes, [3] overflow flag,
+    // [4] nodes of the level being spawned whose hit point lies outside the node grid's box (they
+    // come first in t_order), [5] child rays those nodes spawned
     unsigned int *counters;
 };
 
@@ -86,6 +90,7 @@ struct FrameParams {
     int forest_shading;
 };
 
+constexpr int N_COUNTERS = 6;
 constexpr int NODE_BIN_BITS = 5, NODE_FAR_BITS = 4; // per axis: hit points inside / outside the shapes' box
 constexpr int NODE_FAR_BINS = 1 << (3 * NODE_FAR_BITS);
 constexpr int NODE_BINS = NODE_FAR_BINS + (1 << (3 * NODE_BIN_BITS)); // + one bin for the rays that missed

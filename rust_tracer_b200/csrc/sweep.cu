@@ -175,7 +175,9 @@ RT_DEV RayCoef ray_coef(const RayRegs &r, float k_seg, float cmax, bool usable) 
         return c;
     }
     c.dx = __fdiv_rn(r.dx, n); c.dy = __fdiv_rn(r.dy, n); c.dz = __fdiv_rn(r.dz, n);
-    c.kb = -fmaf(r.ox, c.dx, fmaf(r.oy, c.dy, r.oz * c.dz));
+    // b = C.dh + kb is the distance from the origin to the centre's foot on the ray; kb carries
+    // 12 u lam (1.5 x the rounding of b) so that the computed b is never below the true one
+    c.kb = fmaf(12.f * U24, lam, -fmaf(r.ox, c.dx, fmaf(r.oy, c.dy, r.oz * c.dz)));
     c.ox2 = 2.f * r.ox; c.oy2 = 2.f * r.oy; c.oz2 = 2.f * r.oz;
     c.seed = fmaf(k_seg * U24, lam * lam, -o2);
     c.seed_g = fmaf(GROUP_MARGIN * k_seg * U24, lam * lam, -o2);
@@ -232,7 +234,8 @@ RT_DEV float2 f2(float x) { return make_float2(x, x); }
 template <int R, int SWEEP_THREADS, bool ORIGIN>
 __global__ void __launch_bounds__(SWEEP_THREADS, 1)
 sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, int slot_end, int n_slices, int slice_slots,
-             int merge, int planes, int item_max, unsigned int *batch_counter, unsigned long long *exact_counter) {
+             int merge, int planes, int item_max, int heavy_batches, int heavy_slices, int heavy_slice_slots,
+             unsigned int *batch_counter, unsigned long long *exact_counter) {
     constexpr int SWEEP_WARPS = SWEEP_THREADS / 32;
     constexpr unsigned int FULL = 0xffffffffu;
     extern __shared__ float4 smem[];
@@ -274,12 +277,25 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
         unsigned int item = 0;
         if (lane == 0) item = atomicAdd(batch_counter, 1u);
         item = __shfl_sync(FULL, item, 0);
-        const unsigned int batch = item / (unsigned int)n_slices;
-        const int slice = (int)(item - batch * (unsigned int)n_slices);
+        // items [0, heavy_batches * heavy_slices): the expensive first batches, cut finer
+        const unsigned int heavy_items = (unsigned int)heavy_batches * (unsigned int)heavy_slices;
+        unsigned int batch;
+        int slice, ss;
+        if (item < heavy_items) {
+            batch = item / (unsigned int)heavy_slices;
+            slice = (int)(item - batch * (unsigned int)heavy_slices);
+            ss = heavy_slice_slots;
+        } else {
+            const unsigned int li = item - heavy_items;
+            batch = li / (unsigned int)n_slices;
+            slice = (int)(li - batch * (unsigned int)n_slices);
+            batch += (unsigned int)heavy_batches;
+            ss = slice_slots;
+        }
         const long long ray0_ll = (long long)batch * (R * 32);
         if (ray0_ll >= total) break;
         const int ray0 = (int)ray0_ll;
-        const int sb = slot_begin + slice * slice_slots, se = min(slot_end, sb + slice_slots);
+        const int sb = slot_begin + slice * ss, se = min(slot_end, sb + ss);
 
         // vmask bits 2r, 2r+1: ray r of this lane exists and has no NaN component (it can be
         // queued); nanmask bit r: it exists and has one
@@ -322,7 +338,8 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                     } else {
                         float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
                         float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2), f2(group ? c[r].seed_g : c[r].seed))));
-                        e[r] = __ffma2_rn(b, b, s);
+                        // a centre behind the origin (b < 0): only s decides, i.e. whether the origin is inside the sphere
+                        e[r] = __ffma2_rn(b, make_float2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f)), s);
                     }
                 }
             };
@@ -383,7 +400,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                                                 oz2 = __shfl_sync(FULL, c[r].oz2, src), seed = __shfl_sync(FULL, c[r].seed, src);
                                     const float b = fmaf(scx, dx, fmaf(scy, dy, fmaf(scz, dz, kb)));
                                     const float sv = fmaf(scx, ox2, fmaf(scy, oy2, fmaf(scz, oz2, seed)));
-                                    ev = fmaf(b, b, sv);
+                                    ev = fmaf(b, fmaxf(b, 0.f), sv);
                                 }
                                 ++evals;
                                 const bool cand = ev >= sw && ev <= clip && (lane < 16 || l1 >= 0);
@@ -534,15 +551,32 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
     const int per = ((sc.n_slots + n_chunks - 1) / n_chunks + SEG_PAD - 1) / SEG_PAD * SEG_PAD;
     const long long batches = (total + 32ll * R - 1) / (32ll * R);
     // Work items = ray batches x table slices.  A launch with few rays is cut into slices of
-    // the table so that every warp of the GPU still gets several items (a ray batch against the
-    // whole m10k table is ~1 ms of one warp: too coarse a grain for a short launch).
-    const long long want_items = 48ll * sm_count * SWEEP_WARPS; // measured: tools/trace_tile.py, RT_B200_SLICES
-    int n_slices = (int)std::min<long long>((want_items + batches - 1) / batches, std::max(1, per / MIN_SLICE_SLOTS));
-    if (const char *e = std::getenv("RT_B200_SLICES")) n_slices = std::max(1, std::min(std::atoi(e), std::max(1, per / SEG_PAD)));
-    n_slices = std::max(n_slices, 1);
-    const int slice_slots = std::max(SEG_PAD, ((per + n_slices - 1) / n_slices + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
-    n_slices = std::max(1, (per + slice_slots - 1) / slice_slots);
-    const int merge = (n_slices > 1 || n_chunks > 1) ? 1 : 0;
+    // the table so that every warp of the GPU still gets several items; the batches of the
+    // first s0.heavy rays (origins far outside the scene: filter margins so wide that they
+    // pass most of the table on to the exact test) are cut as finely as the table allows, since
+    // one of them whole can take longer than the rest of the launch.
+    auto slicing = [&](long long want, long long n_batches, int *slots) {
+        int n = (int)std::min<long long>((want + n_batches - 1) / std::max<long long>(n_batches, 1), std::max(1, per / MIN_SLICE_SLOTS));
+        n = std::max(n, 1);
+        *slots = std::max(SEG_PAD, ((per + n - 1) / n + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
+        return std::max(1, (per + *slots - 1) / *slots);
+    };
+    const long long heavy_batches = std::min<long long>(batches, ((long long)std::max(s0.heavy, 0) + 32ll * R - 1) / (32ll * R));
+    long long want_light = 6ll * sm_count * SWEEP_WARPS, want_heavy = 48ll * sm_count * SWEEP_WARPS; // measured: RT_B200_WANT
+    if (const char *e = std::getenv("RT_B200_WANT")) want_light = std::max(1, std::atoi(e)) * (long long)sm_count * SWEEP_WARPS;
+    int slice_slots = SEG_PAD, heavy_slice_slots = SEG_PAD;
+    int n_slices = slicing(want_light, batches - heavy_batches, &slice_slots);
+    if (const char *e = std::getenv("RT_B200_SLICES")) {
+        n_slices = std::max(1, std::min(std::atoi(e), std::max(1, per / SEG_PAD)));
+        slice_slots = std::max(SEG_PAD, ((per + n_slices - 1) / n_slices + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
+        n_slices = std::max(1, (per + slice_slots - 1) / slice_slots);
+    }
+    int heavy_slices = 1;
+    if (heavy_batches > 0) {
+        heavy_slices = slicing(want_heavy, heavy_batches, &heavy_slice_slots);
+        if (heavy_slices < n_slices) { heavy_slices = n_slices; heavy_slice_slots = slice_slots; }
+    }
+    const int merge = (n_slices > 1 || n_chunks > 1 || (heavy_batches > 0 && heavy_slices > 1)) ? 1 : 0;
     if (merge) { // every item folds its keys in with atomicMin: start from "no hit"
         cudaError_t err = cudaSuccess;
         if (s0.n > 0 && !s0.preset) {
@@ -552,7 +586,7 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
         if (err == cudaSuccess && s1.n > 0) err = cudaMemsetAsync(s1.key, 0xFF, sizeof(unsigned long long) * (size_t)s1.n, stream);
         if (err != cudaSuccess) return err;
     }
-    const long long items = batches * n_slices;
+    const long long items = heavy_batches * heavy_slices + (batches - heavy_batches) * n_slices;
     unsigned int grid = (unsigned int)std::min<long long>((items + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)sm_count);
     for (int c = 0; c < n_chunks; ++c) {
         int b = c * per, e = std::min(sc.n_slots, b + per);
@@ -560,7 +594,8 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
         cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
         sweep_kernel<R, T, ORIGIN><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, n_slices, slice_slots, merge,
-                                                              c == n_chunks - 1 ? 1 : 0, item_max, batch_counters + c, exact_counter);
+                                                              c == n_chunks - 1 ? 1 : 0, item_max, (int)heavy_batches, heavy_slices,
+                                                              heavy_slice_slots, batch_counters + c, exact_counter);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
     }
     *used = n_chunks;

@@ -136,6 +136,10 @@ __global__ void __launch_bounds__(1024) node_scan_kernel(Pools p, int s_begin, i
         __syncthreads();
         unsigned int excl = carry + warp_sum[warp] + x - v;
         if (j < NODE_BINS + 1) p.bins[j] = excl;
+        if (j == NODE_FAR_BINS) { // excl = number of hits outside the box
+            p.counters[4] = excl;
+            p.counters[5] = 0u;
+        }
         if (j == NODE_BINS) { // excl = number of hits
             unsigned long long s_end = (unsigned long long)s_begin + (unsigned long long)excl * (unsigned long long)n_point_lights;
             if (s_end > (unsigned long long)p.s_cap) p.counters[3] = 1u;
@@ -194,10 +198,12 @@ spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn
         }
     }
     if (!spawn_children) return;
+    const bool far_node = ordered && (unsigned int)rank < p.counters[4];
     if (m.reflectivity > F32_EPS) { // render.rs:70
         V3 ro, rd;
         reflect_ray(d, h, ro, rd);
         unsigned int c = atomicAdd(&p.counters[0], 1u);
+        if (far_node) atomicAdd(&p.counters[5], 1u);
         if (c < (unsigned int)p.t_cap) {
             p.t_a[c] = make_float4(ro.x, ro.y, ro.z, rd.x);
             p.t_b[c] = make_float4(rd.y, rd.z, 0.f, 0.f);
@@ -211,6 +217,7 @@ spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn
         V3 ro, rd;
         if (refract_ray(d, h, n1, n2, ro, rd)) {
             unsigned int c = atomicAdd(&p.counters[0], 1u);
+            if (far_node) atomicAdd(&p.counters[5], 1u);
             if (c < (unsigned int)p.t_cap) {
                 p.t_a[c] = make_float4(ro.x, ro.y, ro.z, rd.x);
                 p.t_b[c] = make_float4(rd.y, rd.z, 0.f, 0.f);
