@@ -62,6 +62,7 @@ struct rt_scene {
     int sm_count = 0;
     cudaStream_t stream = nullptr;     // the stream work is launched on
     cudaStream_t own_stream = nullptr; // created with the scene
+    std::vector<cudaStream_t> aux;     // the sweeps of one wavefront level run side by side on these
     unsigned int launches = 0;         // kernels launched by the current call
     rt::Workspace ws;
     // origin tables (kernels.h: OriginTable): one per point light, built with the scene, and

@@ -161,6 +161,20 @@ int Workspace::ensure_misc() {
 
 // ---- the wavefront ------------------------------------------------------------------------
 
+// Make sure the scene has min(want, 8) auxiliary streams; false if they cannot be had.
+static bool scene_aux_streams(rt_scene *scene, int want) {
+    want = std::min(std::max(want, 1), 8);
+    while ((int)scene->aux.size() < want) {
+        cudaStream_t s = nullptr;
+        if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) {
+            cudaGetLastError();
+            return !scene->aux.empty();
+        }
+        scene->aux.push_back(s);
+    }
+    return true;
+}
+
 struct EventPool {
     std::vector<cudaEvent_t> ev;
     size_t used = 0;
@@ -234,23 +248,29 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     launch_raygen(fp, p, sample0, n, st);
     scene->launches += 1;
 
-    auto sweep = [&](RaySeg a, RaySeg b, OriginTable ot) {
+    // `on`: the stream to launch on; `timed`: bracket this sweep with its own pair of events
+    auto sweep_on = [&](RaySeg a, RaySeg b, OriginTable ot, cudaStream_t on, bool timed) {
         if (a.n + b.n == 0) return;
-        cudaEvent_t e0 = events.get(), e1 = events.get();
-        cudaEventRecord(e0, st);
-        if (audit) launch_sweep_all_pairs(sc, a, b, ws.exact_counter, st);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (timed) {
+            e0 = events.get(); e1 = events.get();
+            cudaEventRecord(e0, on);
+        }
+        if (audit) launch_sweep_all_pairs(sc, a, b, ws.exact_counter, on);
         else {
             int used = 0;
             cudaError_t e = launch_sweep(sc, a, b, ot, rpt, scene->sm_count, ws.batch_counters + ws.batch_next,
-                                         BATCH_COUNTERS - ws.batch_next, &used, ws.exact_counter, st);
+                                         BATCH_COUNTERS - ws.batch_next, &used, ws.exact_counter, on);
             ws.batch_next += used;
             scene->launches += used > 0 ? used - 1 : 0;
             if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
         }
-        cudaEventRecord(e1, st);
-        acc.sweep_spans.push_back({e0, e1});
-        acc.sweep_rays.push_back((long long)a.n + b.n);
-        if (trace) { // per-sweep counters: costs a synchronisation per sweep, tracing only
+        if (timed) {
+            cudaEventRecord(e1, on);
+            acc.sweep_spans.push_back({e0, e1});
+            acc.sweep_rays.push_back((long long)a.n + b.n);
+        }
+        if (trace && timed) { // per-sweep counters: costs a synchronisation per sweep, tracing only
             unsigned long long c[3] = {0, 0, 0};
             cudaMemcpyAsync(c, ws.exact_counter, sizeof(c), cudaMemcpyDeviceToHost, st);
             cudaStreamSynchronize(st);
@@ -259,6 +279,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         scene->launches += 1;
         if (audit) acc.exact += (unsigned long long)(a.n + b.n) * (unsigned long long)sc.n_bounded;
     };
+    auto sweep = [&](RaySeg a, RaySeg b, OriginTable ot) { sweep_on(a, b, ot, st, true); };
     auto tree_seg = [&](int b, int e) { return RaySeg{p.t_a + b, p.t_b + b, p.t_key + b, e - b}; };
     auto shadow_seg = [&](int b, int e) { return RaySeg{p.s_a + b, p.s_b + b, p.s_key + b, e - b}; };
     const RaySeg none{nullptr, nullptr, nullptr, 0};
@@ -276,14 +297,46 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         }
         RaySeg tree = tree_seg(tb, te);
         tree.heavy = std::min(heavy_tree, tree.n);
-        sweep(tree, none, level == 0 ? scene->cam : general);
         if (se > sb) {
             cudaError_t e = cudaMemsetAsync(p.s_key + sb, 0xFF, sizeof(unsigned long long) * (size_t)(se - sb), st);
             if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
+        }
+        // The sweeps of one level (the tree rays and each light's shadow rays) do not depend on
+        // each other: launched on separate streams, the next one's CTAs take over the SMs the
+        // previous one's have left, instead of waiting for its last work item.  One timed span
+        // per level then; tracing keeps them serial and timed one by one.
+        const bool fork = !trace && scene_aux_streams(scene, 1 + sc.n_point_lights);
+        const int n_aux = (int)scene->aux.size();
+        cudaEvent_t e0 = nullptr, e1 = nullptr, forked = nullptr;
+        long long rays = 0;
+        if (fork) {
+            e0 = events.get(); e1 = events.get(); forked = events.get();
+            cudaEventRecord(e0, st);
+            cudaEventRecord(forked, st);
+            for (int i = 0; i < n_aux; ++i) cudaStreamWaitEvent(scene->aux[i], forked, 0);
+        }
+        int next_aux = 0;
+        auto stream_for = [&]() { return fork ? scene->aux[next_aux++ % n_aux] : st; };
+        sweep_on(tree, none, level == 0 ? scene->cam : general, stream_for(), !fork);
+        rays += tree.n;
+        if (se > sb) {
             for (int l = 0; l < sc.n_point_lights; ++l) {
                 RaySeg sh{p.s_a + sb + l, p.s_b + sb + l, p.s_key + sb + l, (se - sb) / npl, npl, 1};
                 sh.heavy = std::min(heavy_nodes, sh.n);
-                sweep(sh, none, scene->light_tabs[l]);
+                sweep_on(sh, none, scene->light_tabs[l], stream_for(), !fork);
+                rays += sh.n;
+            }
+        }
+        if (fork) {
+            for (int i = 0; i < std::min(next_aux, n_aux); ++i) {
+                cudaEvent_t done = events.get();
+                cudaEventRecord(done, scene->aux[i]);
+                cudaStreamWaitEvent(st, done, 0);
+            }
+            cudaEventRecord(e1, st);
+            if (rays > 0) {
+                acc.sweep_spans.push_back({e0, e1});
+                acc.sweep_rays.push_back(rays);
             }
         }
     };

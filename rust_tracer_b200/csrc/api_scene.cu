@@ -628,6 +628,7 @@ void rt_scene_destroy(rt_scene *scene) {
     cudaSetDevice(scene->device);
     workspace_give_cached(scene->device, scene->ws);
     for (void *p : scene->allocs) cudaFree(p);
+    for (cudaStream_t a : scene->aux) cudaStreamDestroy(a);
     if (scene->own_stream) cudaStreamDestroy(scene->own_stream);
     delete scene;
 }

@@ -562,7 +562,7 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
         return std::max(1, (per + *slots - 1) / *slots);
     };
     const long long heavy_batches = std::min<long long>(batches, ((long long)std::max(s0.heavy, 0) + 32ll * R - 1) / (32ll * R));
-    long long want_light = 6ll * sm_count * SWEEP_WARPS, want_heavy = 48ll * sm_count * SWEEP_WARPS; // measured: RT_B200_WANT
+    long long want_light = 4ll * sm_count * SWEEP_WARPS, want_heavy = 48ll * sm_count * SWEEP_WARPS; // measured: RT_B200_WANT
     if (const char *e = std::getenv("RT_B200_WANT")) want_light = std::max(1, std::atoi(e)) * (long long)sm_count * SWEEP_WARPS;
     int slice_slots = SEG_PAD, heavy_slice_slots = SEG_PAD;
     int n_slices = slicing(want_light, batches - heavy_batches, &slice_slots);

@@ -219,3 +219,44 @@ def test_origin_tables_with_a_light_inside_a_shape_and_far_lights():
     _assert_same(a, b)
     of, ou, oc = orc.render(desc.desc, abi.default_camera(160, 90), 3)
     assert (a[1] == ou).all() and a[2]["rays"] == oc.rays
+
+
+def test_work_item_shapes_do_not_change_the_image(monkeypatch):
+    """The sweep's scheduling knobs -- table slices per work item (RT_B200_WANT, RT_B200_SLICES),
+    the threshold between sweeping a group ray-by-ray or pair-by-pair (RT_B200_ITEM_MAX) -- and
+    the node order must not change a single key: same image, same ray and node counts, and
+    the same as the all-pairs audit (which uses none of them)."""
+    desc = rt.SceneDesc.synthetic(600, 600, 31, 0.03, 0.1)  # floor plane: hit points far outside the shapes' box
+    w, h, depth = 256, 144, 4
+    ref = None
+    for env in ({}, {"RT_B200_WANT": "1"}, {"RT_B200_WANT": "64"}, {"RT_B200_SLICES": "1"}, {"RT_B200_ITEM_MAX": "0"},
+                {"RT_B200_ITEM_MAX": "32"}, {"RT_B200_RAYS_PER_THREAD": "1"}, {"RT_B200_RAYS_PER_THREAD": "2"}):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        sc = rt.Scene(desc)
+        try:
+            out = sc.render(w, h, depth)
+            if ref is None:
+                ref = out
+                audit = sc.render(w, h, depth, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS)
+                _assert_same(ref, audit)
+        finally:
+            sc.close()
+        for k in env:
+            monkeypatch.delenv(k)
+        _assert_same(ref, out)
+
+
+def test_far_hit_points_take_the_heavy_path():
+    """A camera low over the floor: most primary rays hit the plane far outside the shapes' box,
+    their shadow rays carry wide filter margins (many candidates) and are scheduled first in
+    finer work items.  Result = audit = oracle."""
+    desc = rt.SceneDesc.synthetic(300, 300, 8, 0.04, 0.12)
+    w, h = 192, 108
+    cam = abi.default_camera(w, h)
+    cam.origin[:] = [0.0, -1.9, -8.0]
+    cam.y_min, cam.y_max = -2.2, -1.2
+    a, b = _render_pair(desc, w, h, 3, cam=cam)
+    _assert_same(a, b)
+    of, ou, oc = orc.render(desc.desc, cam, 3)
+    assert (a[1] == ou).all() and a[2]["rays"] == oc.rays and a[2]["nodes"] == oc.nodes
