@@ -67,7 +67,7 @@ struct rt_scene {
     rt::Workspace ws;
     // origin tables (kernels.h: OriginTable): one per point light, built with the scene, and
     // one for the camera origin of the last render.  Empty when the table is too small to pay.
-    std::vector<rt::HostSlot> slots, groups;
+    std::vector<rt::HostSlot> slots, groups, quads;
     std::vector<rt::OriginTable> light_tabs; // by DevLight::point_index
     float4 *cam_tab = nullptr;
     rt::OriginTable cam;                     // bound == cam_tab once built
@@ -75,8 +75,8 @@ struct rt_scene {
 };
 
 namespace rt {
-// Re-centre the scene's bound table and group table on `o` (out = slots then groups, each in
-// the paired layout of DevScene::bound) and fill every field of *tab but `bound` and `group`; toward: the table serves shadow rays travelling towards `o`.
+// Re-centre the scene's bound table and group table on `o` (out = slots, groups, quads, each in
+// the paired layout of DevScene::bound) and fill every field of *tab but the table pointers; toward: the table serves shadow rays travelling towards `o`.
 void build_origin_table(const rt_scene *scene, const float o[3], std::vector<float4> &out, OriginTable *tab, bool toward);
 // Make scene->cam the table of this camera origin (no-op when origin tables are off).
 int prepare_camera_table(rt_scene *scene, const float origin[3]);

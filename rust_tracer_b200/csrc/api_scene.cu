@@ -141,8 +141,9 @@ static Bound bound_from(const double c[3], double rf) {
 // Margins: a member (C, R) at distance a from G passes a ray when dist^2(C, line) <= R^2 + mu;
 // then dist(G, line) <= a + sqrt(R^2 + mu), and (a + sqrt(R^2 + mu))^2 <= (a + R)^2 + (1 + a / R) mu.
 // The group radius therefore counts every member as at least a / 16 wide, and the sweep gives
-// group spheres 17 times the margin mu of a bound (sweep.cu: GROUP_MARGIN).
-static Bound make_group(const Bound *slots, const int *shape, int n) {
+// group spheres 17 times the margin mu of a bound (sweep.cu: GROUP_MARGIN).  Quads are built from
+// their 4 group spheres in the same way with a / 2: 3 times the margin of a group (QUAD_MARGIN).
+static Bound make_group(const Bound *slots, const int *shape, int n, double floor_div) {
     double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
     int m = 0;
     for (int j = 0; j < n; ++j) {
@@ -172,7 +173,7 @@ static Bound make_group(const Bound *slots, const int *shape, int n) {
         if (shape[j] < 0) continue;
         double dx = slots[j].cx - c[0], dy = slots[j].cy - c[1], dz = slots[j].cz - c[2];
         double a = std::sqrt(dx * dx + dy * dy + dz * dz);
-        rg = std::max(rg, a + std::max(slots[j].rf, a / 16.0));
+        rg = std::max(rg, a + std::max(slots[j].rf, a / floor_div));
     }
     return bound_from(c, rg * (1.0 + 1e-9));
 }
@@ -210,9 +211,9 @@ void build_origin_table(const rt_scene *scene, const float o[3], std::vector<flo
         clip = false; // a bound every ray must pass: no far clip in this table
         return S{0.f, 0.f, 0.f, -3.402823466e+38f};
     };
-    // slots, then groups (both paired); rmax covers the groups too
-    const size_t ns = scene->slots.size(), ng = scene->groups.size();
-    out.resize(ns + ng);
+    // slots, then groups, then quads (each paired); rmax (the far clip of slot tests) is the slots' alone
+    const size_t ns = scene->slots.size(), ng = scene->groups.size(), nq = scene->quads.size();
+    out.resize(ns + ng + nq);
     auto fill = [&](const std::vector<HostSlot> &v, float4 *dst) {
         for (size_t j = 0; j + 1 < v.size(); j += 2) {
             S a = one(v[j]), b = one(v[j + 1]);
@@ -221,12 +222,14 @@ void build_origin_table(const rt_scene *scene, const float o[3], std::vector<flo
         }
     };
     fill(scene->slots, out.data());
+    const double rmax_slots = rmax;
     fill(scene->groups, out.data() + ns);
+    fill(scene->quads, out.data() + ns + ng);
     double on = std::sqrt((double)o[0] * o[0] + (double)o[1] * o[1] + (double)o[2] * o[2]);
     double r = (on + (double)scene->dev.cmax) * (1.0 + 1e-6);
     tab->reach = std::isfinite(r) && r < 3e38 ? round_up_f32(r) : 3.0e38f;
     tab->ox = o[0]; tab->oy = o[1]; tab->oz = o[2];
-    tab->rmax = (clip && rmax > 0.0 && rmax < 1e15) ? round_up_f32(rmax * (1.0 + 1e-6)) : 0.f;
+    tab->rmax = (clip && rmax_slots > 0.0 && rmax_slots < 1e15) ? round_up_f32(rmax_slots * (1.0 + 1e-6)) : 0.f;
 }
 
 int prepare_camera_table(rt_scene *scene, const float origin[3]) {
@@ -240,6 +243,7 @@ int prepare_camera_table(rt_scene *scene, const float origin[3]) {
     if ((e = cudaStreamSynchronize(scene->stream)) != cudaSuccess) return cuda_fail(e, "camera table upload");
     t.bound = scene->cam_tab;
     t.group = scene->cam_tab + scene->slots.size();
+    t.quad = t.group + scene->groups.size();
     scene->cam = t;
     std::memcpy(scene->cam_origin, origin, 3 * sizeof(float));
     return RT_OK;
@@ -488,8 +492,18 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     const int n_groups = n_slots / GROUP_SLOTS; // even: SEG_PAD is two groups
     std::vector<Bound> groups(n_groups);
     for (int g = 0; g < n_groups; ++g) {
-        groups[g] = make_group(&slots[(size_t)g * GROUP_SLOTS], &bound_shape[(size_t)g * GROUP_SLOTS], GROUP_SLOTS);
+        groups[g] = make_group(&slots[(size_t)g * GROUP_SLOTS], &bound_shape[(size_t)g * GROUP_SLOTS], GROUP_SLOTS, 16.0);
         cmax = std::max(cmax, groups[g].reach); // a group sphere may reach beyond its members
+    }
+    const int per_quad = QUAD_SLOTS / GROUP_SLOTS, n_quads = n_groups / per_quad; // even: SEG_PAD is two quads
+    std::vector<Bound> quads(n_quads);
+    {
+        std::vector<int> live(n_groups);
+        for (int g = 0; g < n_groups; ++g) live[g] = groups[g].w == 3.402823466e+38f ? -1 : 0; // a group of pads
+        for (int q = 0; q < n_quads; ++q) {
+            quads[q] = make_group(&groups[(size_t)q * per_quad], &live[(size_t)q * per_quad], per_quad, 2.0);
+            cmax = std::max(cmax, quads[q].reach);
+        }
     }
     auto paired = [](const std::vector<Bound> &v) {
         std::vector<float4> out(v.size());
@@ -500,7 +514,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         }
         return out;
     };
-    std::vector<float4> bound = paired(slots), group = paired(groups);
+    std::vector<float4> bound = paired(slots), group = paired(groups), quad = paired(quads);
     std::vector<int2> slot_meta(n_slots);
     std::vector<float4> slot_geom(3 * (size_t)n_slots, make_float4(0.f, 0.f, 0.f, 0.f));
     for (int j = 0; j < n_slots; ++j) {
@@ -554,6 +568,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     d.amb_r = desc->ambient[0]; d.amb_g = desc->ambient[1]; d.amb_b = desc->ambient[2];
     const DevMaterial *dm = nullptr;
     if ((rc = upload(s, bound, &d.bound)) != RT_OK || (rc = upload(s, group, &d.group)) != RT_OK ||
+        (rc = upload(s, quad, &d.quad)) != RT_OK ||
         (rc = upload(s, bound_shape, &d.bound_shape)) != RT_OK || (rc = upload(s, slot_meta, &d.slot_meta)) != RT_OK ||
         (rc = upload(s, slot_geom, &d.slot_geom)) != RT_OK ||
         (rc = upload(s, meta, &d.shape_meta)) != RT_OK || (rc = upload(s, geom, &d.geom)) != RT_OK ||
@@ -576,6 +591,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         };
         for (const Bound &b : slots) s->slots.push_back(host_slot(b));
         for (const Bound &b : groups) s->groups.push_back(host_slot(b));
+        for (const Bound &b : quads) s->quads.push_back(host_slot(b));
         s->light_tabs.resize(n_point);
         std::vector<float4> host;
         for (int l = 0; l < desc->n_lights; ++l) {
@@ -588,9 +604,10 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
                 return rc;
             }
             t.group = t.bound + n_slots;
+            t.quad = t.group + n_groups;
         }
         void *ct = nullptr;
-        if ((e = cudaMalloc(&ct, (size_t)(n_slots + n_groups) * sizeof(float4))) != cudaSuccess) {
+        if ((e = cudaMalloc(&ct, (size_t)(n_slots + n_groups + n_quads) * sizeof(float4))) != cudaSuccess) {
             rt_scene_destroy(s);
             return cuda_fail(e, "cudaMalloc(camera table)");
         }

@@ -15,6 +15,8 @@
 //                                             [GROUP_SLOTS g, GROUP_SLOTS (g + 1)), which are
 //                                             neighbours in space (Morton order within a segment).
 //                                             A warp skips a group none of its rays can touch.
+//   quad[2q], quad[2q+1]    float4 x 2        the same one level up: spheres around QUAD_SLOTS slots
+//                                             (4 consecutive groups), tested first.
 //   bound_shape[j] int32                      shape id of bound slot j, -1 for a pad
 //   slot_meta[j]   int2  (kind, shape id)     and
 //   slot_geom[3*j..] 3 x float4               copies of shape_meta / geom in SLOT order: the exact
@@ -54,7 +56,8 @@ struct DevLight { // 32 bytes
 };
 
 constexpr int GROUP_SLOTS = 16; // bound slots per group
-constexpr int SEG_PAD = 32;     // every segment of the bound table is a multiple of this many slots (a pair of groups)
+constexpr int QUAD_SLOTS = 64;  // bound slots per quad = 4 consecutive groups
+constexpr int SEG_PAD = 128;    // every segment of the bound table is a multiple of this many slots (a pair of quads)
 constexpr int MAX_SEGS = 4;
 
 // Bound slots [begin, end) share one margin factor k: a ray passes slot j iff
@@ -82,6 +85,7 @@ struct DevScene {
     float bin_lo[3], bin_scale[3]; // (hit point - bin_lo) * bin_scale - 1 is in [-1, 1] inside the box of the bounded shapes (wavefront.cu: node cells)
     const float4 *bound;
     const float4 *group;    // n_slots / GROUP_SLOTS group spheres, paired like bound
+    const float4 *quad;     // n_slots / QUAD_SLOTS spheres around 4 consecutive groups each, paired like bound
     const int *bound_shape;
     const int2 *slot_meta;
     const float4 *slot_geom;

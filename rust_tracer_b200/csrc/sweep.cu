@@ -40,6 +40,9 @@ namespace rt {
 constexpr int QCAP = 256;                // queued pairs per warp
 constexpr float U24 = 5.9604645e-08f;    // 2^-24, unit round-off of f32
 constexpr float GROUP_MARGIN = 17.f;     // margin of a group sphere / margin of a bound (make_group: a / rho <= 16)
+constexpr float QUAD_MARGIN = 3.f;       // margin of a quad sphere / margin of a group sphere (a / rho <= 2)
+// seed_q = seed_g + QUAD_SEED (seed_g - seed): (QUAD_MARGIN GROUP_MARGIN - GROUP_MARGIN) / (GROUP_MARGIN - 1)
+constexpr float QUAD_SEED = (QUAD_MARGIN * GROUP_MARGIN - GROUP_MARGIN) / (GROUP_MARGIN - 1.f) * 1.0001f;
 constexpr int MIN_SLICE_SLOTS = 256;     // smallest table slice of a work item
 constexpr int SMEM_LIMIT = 232448;       // 227 KB opt-in dynamic shared memory per CTA on sm_100
 
@@ -242,10 +245,11 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
     __shared__ SweepCtx ctx;
     __shared__ unsigned int n_exact[SWEEP_WARPS];
     __shared__ unsigned long long n_iters[SWEEP_WARPS];
-    const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS;
+    const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS, n_qtab = n_tab / QUAD_SLOTS;
     float4 *tab = smem;                                                         // n_tab slots + one slack pair
-    float4 *gtab = tab + n_tab + 2;                                             // n_gtab groups + one slack pair
-    unsigned long long *best = (unsigned long long *)(gtab + n_gtab + 2);       // SWEEP_THREADS * R
+    float4 *gtab = tab + n_tab + 2;                                             // n_gtab groups
+    float4 *qtab = gtab + n_gtab;                                               // n_qtab quads
+    unsigned long long *best = (unsigned long long *)(qtab + n_qtab);           // SWEEP_THREADS * R
     unsigned int *queue = (unsigned int *)(best + SWEEP_THREADS * R);           // SWEEP_WARPS * QCAP
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -259,10 +263,9 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
         for (int k = tid; k < n_tab; k += SWEEP_THREADS) tab[k] = src[k];
         const float4 *gsrc = (ORIGIN ? ot.group : sc.group) + slot_begin / GROUP_SLOTS;
         for (int k = tid; k < n_gtab; k += SWEEP_THREADS) gtab[k] = gsrc[k];
-        if (tid < 2) { // prefetched past the end, never used
-            tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
-            gtab[n_gtab + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+        const float4 *qsrc = (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS;
+        for (int k = tid; k < n_qtab; k += SWEEP_THREADS) qtab[k] = qsrc[k];
+        if (tid < 2) tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f); // prefetched past the end, never used
     }
     if (tid == 0) {
         ctx.s0 = s0; ctx.s1 = s1;
@@ -272,6 +275,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
     __syncthreads();
     const float4 *tab0 = tab - slot_begin;                 // indexed by absolute slot
     const float4 *gtab0 = gtab - slot_begin / GROUP_SLOTS; // indexed by absolute group
+    const float4 *qtab0 = qtab - slot_begin / QUAD_SLOTS;  // indexed by absolute quad
 
     for (;;) {
         unsigned int item = 0;
@@ -328,30 +332,45 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                 else c[r] = ray_coef(rr, sc.segs.k[g], sc.cmax, usable);
             }
             // e[r] = (filter value of ray r against the two spheres packed in T0, T1)
-            auto pair_e = [&](const float4 &T0, const float4 &T1, float2 (&e)[R], bool group) {
+            // level: 0 bound slots, 1 group spheres, 2 quad spheres (wider margins, see GROUP_MARGIN)
+            auto pair_e = [&](const float4 &T0, const float4 &T1, float2 (&e)[R], int level) {
                 const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     if constexpr (ORIGIN) {
                         float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __fmul2_rn(cz, f2(c[r].dz))));
-                        e[r] = __ffma2_rn(b, b, f2(group ? c[r].mu_g : c[r].mu));
+                        e[r] = __ffma2_rn(b, b, f2(level == 0 ? c[r].mu : (level == 1 ? c[r].mu_g : QUAD_MARGIN * c[r].mu_g)));
                     } else {
                         float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
-                        float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2), f2(group ? c[r].seed_g : c[r].seed))));
+                        float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2),
+                                               f2(level == 0 ? c[r].seed : (level == 1 ? c[r].seed_g : fmaf(QUAD_SEED, c[r].seed_g - c[r].seed, c[r].seed_g))))));
                         // a centre behind the origin (b < 0): only s decides, i.e. whether the origin is inside the sphere
                         e[r] = __ffma2_rn(b, make_float2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f)), s);
                     }
                 }
             };
-            float4 G0 = gtab0[gb >> 4], G1 = gtab0[(gb >> 4) + 1]; // next pair of groups, fetched one step ahead
-            for (int j0 = gb; j0 < ge; j0 += 2 * GROUP_SLOTS) {
+            for (int jq = gb; jq < ge; jq += 2 * QUAD_SLOTS) {
+            // which of the two quads (4 groups each) can any ray of this warp touch?
+            unsigned int quads_hit;
+            {
+                const float4 T0 = qtab0[jq >> 6], T1 = qtab0[(jq >> 6) + 1];
+                float2 e[R];
+                pair_e(T0, T1, e, 2);
+                float m0 = e[0].x, m1 = e[0].y;
+#pragma unroll
+                for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
+                quads_hit = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
+                evals += 2 * R;
+            }
+            for (int gp = 0; gp < 2 * QUAD_SLOTS / (2 * GROUP_SLOTS); ++gp) { // the 4 pairs of groups of the two quads
+                if (!((quads_hit >> (gp >> 1)) & 1u)) continue;
+                const int j0 = jq + gp * 2 * GROUP_SLOTS;
                 // which of the two groups can any ray of this warp touch?
                 unsigned int ball0, ball1, pm = 0;
                 {
-                    const float4 T0 = G0, T1 = G1;
-                    G0 = gtab0[(j0 >> 4) + 2]; G1 = gtab0[(j0 >> 4) + 3]; // past the end: the slack pair
+                    const float4 T0 = gtab0[j0 >> 4], T1 = gtab0[(j0 >> 4) + 1];
                     float2 e[R];
-                    pair_e(T0, T1, e, true);
+                    pair_e(T0, T1, e, 1);
                     float m0 = e[0].x, m1 = e[0].y;
 #pragma unroll
                     for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
@@ -424,7 +443,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                         const float4 T0 = N0, T1 = N1;
                         N0 = tp[2 * i + 2]; N1 = tp[2 * i + 3]; // past the group: the next one's, or the table's slack pair
                         float2 e[R];
-                        pair_e(T0, T1, e, false);
+                        pair_e(T0, T1, e, 0);
                         float m0 = e[0].x, m1 = e[0].y;
 #pragma unroll
                         for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
@@ -457,6 +476,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                     }
                     if (qn >= 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
                 }
+            }
             }
         }
         if (lane == 0) n_iters[warp] += evals;
@@ -521,13 +541,14 @@ sweep_all_pairs_kernel(DevScene sc, RaySeg s0, RaySeg s1, unsigned long long *ex
 }
 
 template <int R, int T> static size_t sweep_smem_fixed() {
-    return 4 * sizeof(float4) + (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int);
+    return 2 * sizeof(float4) + (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int);
 }
 
 // Bound slots one launch can keep in shared memory.
 template <int R, int T> static int sweep_table_cap() {
-    // per slot: its float4 and 1/GROUP_SLOTS of its group's
-    return (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T>()) * GROUP_SLOTS / (sizeof(float4) * (GROUP_SLOTS + 1))) / SEG_PAD * SEG_PAD;
+    // per slot: its float4, 1/GROUP_SLOTS of its group's and 1/QUAD_SLOTS of its quad's
+    return (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T>()) * QUAD_SLOTS / (sizeof(float4) * (QUAD_SLOTS + QUAD_SLOTS / GROUP_SLOTS + 1))) /
+           SEG_PAD * SEG_PAD;
 }
 
 template <int R, int T, bool ORIGIN>
@@ -590,7 +611,7 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
     unsigned int grid = (unsigned int)std::min<long long>((items + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)sm_count);
     for (int c = 0; c < n_chunks; ++c) {
         int b = c * per, e = std::min(sc.n_slots, b + per);
-        const size_t smem = (size_t)((e - b) + (e - b) / GROUP_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T>();
+        const size_t smem = (size_t)((e - b) + (e - b) / GROUP_SLOTS + (e - b) / QUAD_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T>();
         cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
         sweep_kernel<R, T, ORIGIN><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, n_slices, slice_slots, merge,

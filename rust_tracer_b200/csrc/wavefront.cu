@@ -73,7 +73,8 @@ RT_DEV unsigned int spread3_dev(unsigned int x) { // NODE_BIN_BITS <= 10 bits ->
 
 __global__ void __launch_bounds__(256) node_bin_kernel(DevScene sc, Pools p, int begin, int end) {
     int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= end) return;
+    const bool live = i < end;
+    if (!live) i = end - 1; // keep the warp whole for the match below
     unsigned long long key = p.t_key[i];
     unsigned int bin = NODE_BINS; // miss
     if (key != KEY_MISS) {
@@ -103,8 +104,10 @@ __global__ void __launch_bounds__(256) node_bin_kernel(DevScene sc, Pools p, int
             bin = spread3_dev(cell(ux)) | (spread3_dev(cell(uy)) << 1) | (spread3_dev(cell(uz)) << 2);
         }
     }
-    p.t_sbase[i] = (int)bin; // parked here until spawn_kernel overwrites it
-    atomicAdd(&p.bins[bin], 1u);
+    if (live) p.t_sbase[i] = (int)bin; // parked here until spawn_kernel overwrites it
+    // neighbouring rays mostly share a cell: one atomic per distinct cell of the warp
+    const unsigned int same = __match_any_sync(0xffffffffu, live ? bin : 0xffffffffu);
+    if (live && (threadIdx.x & 31) == __ffs(same) - 1) atomicAdd(&p.bins[bin], (unsigned int)__popc(same));
 }
 
 // One block: exclusive scan of bins[0 .. NODE_BINS] in place; counters[1] = end of the level's shadow rays.
@@ -153,9 +156,15 @@ __global__ void __launch_bounds__(1024) node_scan_kernel(Pools p, int s_begin, i
 
 __global__ void __launch_bounds__(256) node_scatter_kernel(Pools p, int begin, int end) {
     int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= end) return;
-    unsigned int pos = atomicAdd(&p.bins[p.t_sbase[i]], 1u);
-    p.t_order[begin + pos] = i;
+    const bool live = i < end;
+    const int lane = threadIdx.x & 31;
+    const unsigned int bin = live ? (unsigned int)p.t_sbase[i] : 0xffffffffu;
+    const unsigned int same = __match_any_sync(0xffffffffu, bin);
+    const int leader = __ffs(same) - 1;
+    unsigned int base = 0;
+    if (live && lane == leader) base = atomicAdd(&p.bins[bin], (unsigned int)__popc(same));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (live) p.t_order[begin + base + __popc(same & ((1u << lane) - 1u))] = i;
 }
 
 __global__ void __launch_bounds__(WF_BLOCK)
