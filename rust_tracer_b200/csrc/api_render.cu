@@ -486,7 +486,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
     cudaEventRecord(ev0, st);
 
     Accum acc;
-    long long band = env_int("RT_B200_BAND_SAMPLES", 1 << 22, 1 << 10, 1 << 28);
+    long long band = env_int("RT_B200_BAND_SAMPLES", 1 << 23, 1 << 10, 1 << 28);
     if (n_samples > 0) {
         long long nb = (n_samples + band - 1) / band;
         band = (n_samples + nb - 1) / nb;

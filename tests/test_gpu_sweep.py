@@ -260,3 +260,24 @@ def test_far_hit_points_take_the_heavy_path():
     _assert_same(a, b)
     of, ou, oc = orc.render(desc.desc, cam, 3)
     assert (a[1] == ou).all() and a[2]["rays"] == oc.rays and a[2]["nodes"] == oc.nodes
+
+
+def test_bands_do_not_change_the_image(monkeypatch):
+    """A frame larger than one band of samples is cast band by band (each with its own ray pools,
+    node order and counters); cutting a small frame into many bands must give the same image,
+    ray and node counts as one band, for 1 and 4 samples per pixel."""
+    desc = rt.SceneDesc.synthetic(300, 300, 77, 0.04, 0.12)
+    w, h, depth = 200, 120, 4
+    sc = rt.Scene(desc)
+    try:
+        one = sc.render(w, h, depth)
+        one4 = sc.render(w, h, depth, spp=4, seed=5)
+        monkeypatch.setenv("RT_B200_BAND_SAMPLES", "3000")
+        many = sc.render(w, h, depth)
+        many4 = sc.render(w, h, depth, spp=4, seed=5)
+        monkeypatch.delenv("RT_B200_BAND_SAMPLES")
+    finally:
+        sc.close()
+    _assert_same(one, many)
+    _assert_same(one4, many4)
+    assert many[2]["kernel_launches"] > 4 * one[2]["kernel_launches"]
