@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 2
+#define RT_B200_ABI_VERSION 3
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -171,6 +171,9 @@ typedef struct rt_stats {
     double   filter_flops;  /* flop the sweeps' bounding-sphere filters executed: 2 x (7 FMA per
                                ray x sphere evaluated, 4 for rays swept against an origin table);
                                spheres = bounds and group spheres, skipped groups not counted */
+    uint64_t tested_pairs;  /* ray x shape pairs resolved ONE BY ONE (bounding-sphere filter of that
+                               shape's own bound, or exact test); the rest of rays x shapes were
+                               dismissed wholesale by a group sphere.  SURVEY 8d credits only these */
 } rt_stats;
 
 typedef struct rt_scene rt_scene;   /* opaque: device-resident scene tables */

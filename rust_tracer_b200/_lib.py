@@ -83,7 +83,7 @@ def lib():
                 "(make -C rust_tracer_b200/csrc). There is no fallback path.")
         handle = C.CDLL(LIB_PATH)
         _declare(handle)
-        if handle.rt_abi_version() != 2:
+        if handle.rt_abi_version() != 3:
             raise ImportError("librt_b200.so ABI version mismatch")
         _lib = handle
     return _lib

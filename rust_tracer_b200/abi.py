@@ -57,7 +57,7 @@ class rt_stats(C.Structure):
                 ("nodes", C.c_uint64), ("sphere_tests", C.c_uint64), ("plane_tests", C.c_uint64),
                 ("triangle_tests", C.c_uint64), ("cube_tests", C.c_uint64), ("exact_tests", C.c_uint64),
                 ("algorithmic_flops", C.c_double), ("sweep_ms", C.c_float), ("shade_ms", C.c_float),
-                ("total_ms", C.c_float), ("kernel_launches", C.c_uint32), ("filter_flops", C.c_double)]
+                ("total_ms", C.c_float), ("kernel_launches", C.c_uint32), ("filter_flops", C.c_double), ("tested_pairs", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -150,10 +150,10 @@ int Workspace::ensure_misc() {
     int rc;
     if (!pools.counters && (rc = dev_alloc(&pools.counters, N_COUNTERS, "counters"))) return rc;
     if (!pools.bins && (rc = dev_alloc(&pools.bins, NODE_BINS + 2, "bins"))) return rc;
-    if (!exact_counter && (rc = dev_alloc(&exact_counter, 3, "exact_counter"))) return rc;
+    if (!exact_counter && (rc = dev_alloc(&exact_counter, N_SWEEP_COUNTERS, "exact_counter"))) return rc;
     if (!batch_counters && (rc = dev_alloc(&batch_counters, BATCH_COUNTERS, "batch_counters"))) return rc;
     if (!h_counters) {
-        cudaError_t e = cudaMallocHost((void **)&h_counters, N_COUNTERS * sizeof(unsigned int) + 3 * sizeof(unsigned long long));
+        cudaError_t e = cudaMallocHost((void **)&h_counters, N_COUNTERS * sizeof(unsigned int) + N_SWEEP_COUNTERS * sizeof(unsigned long long));
         if (e != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
     }
     return RT_OK;
@@ -203,15 +203,19 @@ struct Accum {
     std::vector<long long> sweep_rays; // rays of each span (RT_B200_TRACE)
     std::vector<unsigned long long> sweep_counts; // device counters after each span: exact, general evals, origin evals (trace only)
     double filter_fma = 0.0;           // FMAs executed by the sweeps' filters
+    unsigned long long slot_evals = 0; // (ray, bound slot) pairs the filters evaluated one by one
+    bool audit = false;                // RT_FLAG_AUDIT_ALL_PAIRS: every pair went through the exact test
 };
 
-// exact-test count and filter FMA count of the sweeps, from the device counters read back into
-// ws.h_counters + N_COUNTERS: [0] exact tests, [1] pairs through the general filter, [2] through the origin filter
+// exact-test count and filter counts of the sweeps, from the device counters read back into
+// ws.h_counters + N_COUNTERS: [0] exact tests, [1] spheres evaluated by the general filter, [2] by the
+// origin filter (bounds, group and quad spheres alike), [3] of those, evaluations of bound slots
 static void read_sweep_counters(const Workspace &ws, Accum &acc) {
-    unsigned long long c[3];
+    unsigned long long c[N_SWEEP_COUNTERS];
     std::memcpy(c, ws.h_counters + N_COUNTERS, sizeof(c));
     acc.exact = c[0];
     acc.filter_fma = (double)c[1] * FILTER_FMA_GENERAL + (double)c[2] * FILTER_FMA_ORIGIN;
+    acc.slot_evals = c[3];
 }
 
 static int env_int(const char *name, int dflt, int lo, int hi) {
@@ -271,7 +275,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
             acc.sweep_rays.push_back((long long)a.n + b.n);
         }
         if (trace && timed) { // per-sweep counters: costs a synchronisation per sweep, tracing only
-            unsigned long long c[3] = {0, 0, 0};
+            unsigned long long c[N_SWEEP_COUNTERS] = {};
             cudaMemcpyAsync(c, ws.exact_counter, sizeof(c), cudaMemcpyDeviceToHost, st);
             cudaStreamSynchronize(st);
             acc.sweep_counts.insert(acc.sweep_counts.end(), c, c + 3);
@@ -413,6 +417,11 @@ static void fill_stats(rt_scene *scene, const Accum &acc, unsigned long long pix
                      47.0 * (c[RT_SHAPE_PLANE] - scene->planes_identity) + 14.0 * scene->planes_identity;
     st->algorithmic_flops = (double)rays * per_ray + (double)acc.nodes * (60.0 + 70.0 * scene->dev.n_lights);
     st->filter_flops = 2.0 * acc.filter_fma;
+    // pairs resolved one by one: bound slots the filters evaluated (pads scaled out) + every plane;
+    // the audit sweeps resolve every pair that way
+    const int nb = scene->dev.n_bounded, ns = scene->dev.n_slots;
+    st->tested_pairs = acc.audit ? rays * (unsigned long long)(nb + c[RT_SHAPE_PLANE])
+                             : (unsigned long long)((double)acc.slot_evals * (ns ? (double)nb / ns : 0.0)) + st->plane_tests;
 }
 
 static int check_params(const rt_scene *scene, const rt_camera *cam, const rt_render_params *pr) {
@@ -459,7 +468,7 @@ static int cast_band_sized(rt_scene *scene, Workspace &ws, const FrameParams &fp
         if (rc != RT_OK) return rc;
         rc = cast_band(scene, ws, fp, sample0, n, flags, lv, acc, events);
         if (rc <= 0) return rc;
-        cudaMemsetAsync(ws.exact_counter, 0, 3 * sizeof(unsigned long long), scene->stream); // the band is recast
+        cudaMemsetAsync(ws.exact_counter, 0, N_SWEEP_COUNTERS * sizeof(unsigned long long), scene->stream); // the band is recast
         if (t_cap >= worst) return fail(RT_ERR_INTERNAL, "ray pool overflow at the worst-case size");
         t_cap = std::min(worst, t_cap * 2);
     }
@@ -482,7 +491,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
     EventPool events;
     cudaEvent_t ev0 = events.get(), ev1 = events.get();
     scene->launches = 0;
-    CK(cudaMemsetAsync(ws.exact_counter, 0, 3 * sizeof(unsigned long long), st), "exact counter");
+    CK(cudaMemsetAsync(ws.exact_counter, 0, N_SWEEP_COUNTERS * sizeof(unsigned long long), st), "exact counter");
     cudaEventRecord(ev0, st);
 
     Accum acc;
@@ -509,10 +518,11 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
         if (n > 0) scene->launches += 1;
     }
     cudaEventRecord(ev1, st);
-    CK(cudaMemcpyAsync(ws.h_counters + N_COUNTERS, ws.exact_counter, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
+    CK(cudaMemcpyAsync(ws.h_counters + N_COUNTERS, ws.exact_counter, N_SWEEP_COUNTERS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
     CK(cudaStreamSynchronize(st), "render");
     CK(cudaGetLastError(), "render");
-    if (!(pr->flags & RT_FLAG_AUDIT_ALL_PAIRS)) read_sweep_counters(ws, acc);
+    acc.audit = (pr->flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
+    if (!acc.audit) read_sweep_counters(ws, acc);
     if (stats) {
         fill_stats(scene, acc, (unsigned long long)n_pixels, stats);
         float ms = 0.f, sweep = 0.f;
@@ -625,7 +635,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
     EventPool events;
     cudaEvent_t ev0 = events.get(), ev1 = events.get();
     cudaStream_t st = scene->stream;
-    cudaMemsetAsync(ws.exact_counter, 0, 3 * sizeof(unsigned long long), st);
+    cudaMemsetAsync(ws.exact_counter, 0, N_SWEEP_COUNTERS * sizeof(unsigned long long), st);
     cudaEventRecord(ev0, st);
     Accum acc;
     BandLevels lv;
@@ -634,7 +644,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
         return rc;
     }
     cudaEventRecord(ev1, st);
-    cudaMemcpyAsync(ws.h_counters + N_COUNTERS, ws.exact_counter, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(ws.h_counters + N_COUNTERS, ws.exact_counter, N_SWEEP_COUNTERS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) {
         rt_forest_destroy(f);
@@ -647,7 +657,8 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
         acc.tree_rays = (unsigned long long)f->total_tree_rays;
         acc.shadow_rays = lv.se.empty() ? 0 : (unsigned long long)lv.se.back();
         acc.nodes = lv.nodes;
-        if (!(pr.flags & RT_FLAG_AUDIT_ALL_PAIRS)) read_sweep_counters(ws, acc);
+        acc.audit = (pr.flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
+        if (!acc.audit) read_sweep_counters(ws, acc);
         fill_stats(scene, acc, (unsigned long long)n, stats);
         float ms = 0.f, sweep = 0.f;
         cudaEventElapsedTime(&ms, ev0, ev1);

@@ -42,7 +42,8 @@ struct OriginTable {
 // rays_per_thread: 1, 2 or 4, or 0 to choose by the number of rays.  batch_counters (device,
 // n_counters zeroed words) hand ray batches to the persistent warps, one word per launch;
 // *used receives the number consumed (one per shared-memory chunk of the bound table).
-// exact_counter (device, may be null) accumulates the number of exact pair tests.
+// exact_counter (device, may be null; N_SWEEP_COUNTERS words) accumulates the number of exact pair
+// tests [0] and of filter evaluations [1..3].
 // origin.bound != null: every ray passes through origin's point; s1 must be empty.
 cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable origin, int rays_per_thread, int sm_count,
                          unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
@@ -92,6 +93,7 @@ struct FrameParams {
 };
 
 constexpr int N_COUNTERS = 6;
+constexpr int N_SWEEP_COUNTERS = 4; // launch_sweep's exact_counter: exact tests, general evals, origin evals, slot evals
 constexpr int NODE_BIN_BITS = 5, NODE_FAR_BITS = 4; // per axis: hit points inside / outside the shapes' box
 constexpr int NODE_FAR_BINS = 1 << (3 * NODE_FAR_BITS);
 constexpr int NODE_BINS = NODE_FAR_BINS + (1 << (3 * NODE_BIN_BITS)); // + one bin for the rays that missed

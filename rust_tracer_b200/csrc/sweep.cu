@@ -244,7 +244,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
     extern __shared__ float4 smem[];
     __shared__ SweepCtx ctx;
     __shared__ unsigned int n_exact[SWEEP_WARPS];
-    __shared__ unsigned long long n_iters[SWEEP_WARPS];
+    __shared__ unsigned long long n_iters[SWEEP_WARPS], n_slot[SWEEP_WARPS];
     const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS, n_qtab = n_tab / QUAD_SLOTS;
     float4 *tab = smem;                                                         // n_tab slots + one slack pair
     float4 *gtab = tab + n_tab + 2;                                             // n_gtab groups
@@ -271,7 +271,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
         ctx.s0 = s0; ctx.s1 = s1;
         ctx.slot_meta = sc.slot_meta; ctx.slot_geom = sc.slot_geom; ctx.cube_tris = sc.cube_tris;
     }
-    if (lane == 0) { n_exact[warp] = 0; n_iters[warp] = 0; }
+    if (lane == 0) { n_exact[warp] = 0; n_iters[warp] = 0; n_slot[warp] = 0; }
     __syncthreads();
     const float4 *tab0 = tab - slot_begin;                 // indexed by absolute slot
     const float4 *gtab0 = gtab - slot_begin / GROUP_SLOTS; // indexed by absolute group
@@ -317,7 +317,9 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
         int qn = 0; // queued pairs of this warp (warp-uniform)
 
         // ---- phase 1 + 2 --------------------------------------------------------------
-        unsigned int evals = 0; // filter evaluations of this item, in units of 32 (one per lane)
+        // filter evaluations of this item, in units of 32 (one per lane): against bound slots,
+        // and against group / quad spheres
+        unsigned int evals = 0, evals_hier = 0;
         for (int g = 0; g < sc.segs.n; ++g) {
             const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
             if (gb >= ge) continue;
@@ -360,7 +362,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
 #pragma unroll
                 for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
                 quads_hit = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
-                evals += 2 * R;
+                evals_hier += 2 * R;
             }
             for (int gp = 0; gp < 2 * QUAD_SLOTS / (2 * GROUP_SLOTS); ++gp) { // the 4 pairs of groups of the two quads
                 if (!((quads_hit >> (gp >> 1)) & 1u)) continue;
@@ -376,7 +378,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                     for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
                     ball0 = __ballot_sync(FULL, m0 >= T1.z);
                     ball1 = __ballot_sync(FULL, m1 >= T1.w);
-                    evals += 2 * R;
+                    evals_hier += 2 * R;
                     const int p0 = __popc(ball0), p1 = __popc(ball1);
                     if ((p0 && p0 <= item_max) || (p1 && p1 <= item_max)) { // bit 2r + h of pm: ray r of this lane may touch group h
 #pragma unroll
@@ -479,7 +481,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
             }
             }
         }
-        if (lane == 0) n_iters[warp] += evals;
+        if (lane == 0) { n_iters[warp] += evals + evals_hier; n_slot[warp] += evals; }
         __syncwarp();
         sweep_flush(&ctx, wqueue, wbest, ray0, qn, 1, &n_exact[warp]);
 
@@ -511,6 +513,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
         if (n_exact[warp]) atomicAdd(exact_counter, (unsigned long long)n_exact[warp]);
         // (ray, sphere) pairs the filter evaluated: 2 spheres x 32 R rays per iteration
         if (n_iters[warp]) atomicAdd(exact_counter + (ORIGIN ? 2 : 1), n_iters[warp] * 32ull);
+        if (n_slot[warp]) atomicAdd(exact_counter + 3, n_slot[warp] * 32ull); // of which against bound slots
     }
 }
 

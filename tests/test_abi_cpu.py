@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     handle = rt.lib()
     for name in declared:
         assert hasattr(handle, name), name
-    assert handle.rt_abi_version() == 2
+    assert handle.rt_abi_version() == 3
 
 
 def test_struct_sizes_match_the_header():
@@ -37,7 +37,7 @@ def test_struct_sizes_match_the_header():
     assert C.sizeof(abi.rt_light) == 28
     assert C.sizeof(abi.rt_camera) == 36
     assert C.sizeof(abi.rt_render_params) == 32
-    assert C.sizeof(abi.rt_stats) == 104
+    assert C.sizeof(abi.rt_stats) == 112
 
 
 def _bytes(ptr, n, T):

@@ -281,3 +281,14 @@ def test_bands_do_not_change_the_image(monkeypatch):
     _assert_same(one, many)
     _assert_same(one4, many4)
     assert many[2]["kernel_launches"] > 4 * one[2]["kernel_launches"]
+
+
+def test_tested_pairs_counter():
+    """rt_stats.tested_pairs (credit only the tests actually resolved): every ray x shape
+    pair under the all-pairs audit, a small share of them under the group / quad culling."""
+    desc = rt.SceneDesc.synthetic(600, 600, 3, 0.03, 0.1)
+    a, b = _render_pair(desc, 160, 90, 3)
+    n_shapes = desc.desc.n_shapes
+    assert b[2]["tested_pairs"] == b[2]["rays"] * n_shapes
+    assert 0 < a[2]["tested_pairs"] < 0.5 * a[2]["rays"] * n_shapes
+    assert a[2]["tested_pairs"] >= a[2]["plane_tests"]
