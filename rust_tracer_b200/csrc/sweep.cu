@@ -1,31 +1,37 @@
 // sweep.cu -- the hot kernel: nearest hit of every ray against every shape.
 //
 // Replaces Scene::intersect's linear scan (reference src/scene/mod.rs:98-116, called from
-// src/render.rs:47 and, once per light, src/scene/mod.rs:193).  All-pairs, like an N-body
-// sweep:
-//   phase 1  FILTER   one persistent CTA per SM keeps the whole bounding-sphere table in
-//                     shared memory; each warp fetches batches of 32 R rays, each thread keeps
-//                     R rays in registers and tests them against two bounds at a time with
-//                     packed FFMA2 (fma.rn.f32x2):
-//                     7 FMA per (ray, bound) decide "this ray certainly misses this shape".
-//                     The test is conservative: its margin covers both its own rounding and
-//                     the reference's ("filter margins"), so it only ever rejects
-//                     pairs the exact test would reject too.
-//   phase 2  EXACT    surviving (ray, shape) pairs go to a per-warp queue in shared memory;
+// src/render.rs:47 and, once per light, src/scene/mod.rs:193).  Every (ray, shape) pair is
+// resolved, most of them wholesale:
+//   phase 1  FILTER   one persistent CTA per SM keeps the bounding-sphere table of the shapes
+//                     (slots), of every 16 slots (groups) and of every 64 (quads) in shared
+//                     memory; each warp fetches batches of 32 R rays, each thread keeps the
+//                     filter coefficients of R rays in registers and tests them against two
+//                     spheres at a time with packed FFMA2 (fma.rn.f32x2): quads first, then the
+//                     groups of a quad some ray of the warp may touch, then the slots of such a
+//                     group -- all 32 R rays against each slot pair (brute loop), or, when few
+//                     lanes hold a touching ray, one (ray, group) pair per half warp with
+//                     lane = slot (pair path).  7 FMA per (ray, sphere) decide "this ray
+//                     certainly misses everything in this sphere"; 4 FMA for rays that share a
+//                     point (origin tables, below).  The tests are conservative: their margins
+//                     cover both their own rounding and the reference's ("filter
+//                     margins"), so they only ever reject pairs the exact test would reject too.
+//   phase 2  EXACT    surviving (ray, slot) pairs go to a per-warp queue in shared memory;
 //                     whenever 32 are waiting the warp runs 32 exact tests, one per lane,
 //                     with the reference's own operand order (exact.cuh), and folds the
 //                     result into the ray's 64-bit (t, id) key with an integer atomicMin.
 //   phase 3  PLANES   infinite planes have no bound; every ray tests them exactly.
 // The winner is therefore decided by the exact arithmetic alone, in every case.
 //
-// The filter, for a ray (O, d) and a bound (C, R), with dh = d / |d|, L = C - O:
+// The filter, for a ray (O, d) and a sphere (C, R), with dh = d / |d|, L = C - O:
 //     dist^2(C, line) <= R^2   <=>   (L.dh)^2 - |L|^2 + |C|^2  >=  |C|^2 - R^2 =: W
 // and  (L.dh)^2 - |L|^2 + |C|^2 = b^2 + s  with  b = C.dh - O.dh,  s = C.(2 O) - |O|^2:
-// two 3-FMA chains seeded per ray, one FMA to combine, one compare against the per-bound W.
-// The per-ray seed of s also carries the margin  k 2^-24 (|O| + cmax)^2.
+// two 3-FMA chains seeded per ray, one FMA to combine, one compare against the per-sphere W.
+// The per-ray seed of s also carries the margin  k 2^-24 (|O| + cmax)^2, and b^2 is taken as
+// b max(b, 0): a sphere centred behind the origin passes only if the origin is inside it.
 //
 // Rays that share a point O' -- primary rays (the camera) and the shadow rays of one light --
-// are swept against the table re-centred on O' (kernels.h: OriginTable): with C' = C - O',
+// are swept against the tables re-centred on O' (kernels.h: OriginTable): with C' = C - O',
 //     dist^2(C, line) <= R^2   <=>   (C'.dh)^2  >=  |C'|^2 - R^2 =: W'
 // one 3-FMA chain and one FMA that squares it and adds the per-ray margin: 4 FMA per pair.
 #include <algorithm>
