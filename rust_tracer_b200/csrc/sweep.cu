@@ -446,7 +446,7 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
                     const float4 *tp = tab0 + jg;
                     float4 N0 = tp[0], N1 = tp[1]; // next slot pair, fetched one iteration ahead
                     evals += (GROUP_SLOTS / 2) * 2 * R;
-#pragma unroll 4
+#pragma unroll 2
                     for (int i = 0; i < GROUP_SLOTS / 2; ++i) {
                         const float4 T0 = N0, T1 = N1;
                         N0 = tp[2 * i + 2]; N1 = tp[2 * i + 3]; // past the group: the next one's, or the table's slack pair
