@@ -235,6 +235,10 @@ def run_ours(args, wl):
     barrier()
     clocks = sampler.result()
     dev_ms = sum(a.elapsed_time(b) for a, b in spans)
+    if os.environ.get("RT_B200_BENCH_DEBUG"):  # per-rank split: the library's own device time vs the whole step
+        sys.stderr.write("[bench] rank %d: render %.3f ms/step (sweeps %.3f), step incl. gather %.3f ms\n" % (
+            rank, sum(s["total_ms"] for s in stats_list) / max(1, args.steps),
+            sum(s["sweep_ms"] for s in stats_list) / max(1, args.steps), dev_ms / max(1, args.steps)))
 
     # whole-job numbers: rays of all ranks / max-over-ranks device time
     rays_step = float(sum(s["rays"] for s in stats_list)) / max(1, args.steps)

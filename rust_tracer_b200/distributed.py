@@ -14,12 +14,24 @@ import torch.distributed as dist
 from .api import tile_rows
 
 
+_row_index_cache = {}
+
+
+def _row_index(height, rank, world, rows_per_tile, device):
+    """Device tensor of the rows rank `rank` renders (cached: the gather runs every frame)."""
+    key = (height, rank, world, rows_per_tile, str(device))
+    idx = _row_index_cache.get(key)
+    if idx is None:
+        idx = torch.from_numpy(tile_rows(height, rank, world, rows_per_tile)).to(device, torch.long)
+        _row_index_cache[key] = idx
+    return idx
+
+
 def assemble_rows(tiles, height, width, world, rows_per_tile):
     """tiles[r]: [rows_r, width, 3] uint8 tensor of rank r -> [height, width, 3] image."""
     full = torch.empty((height, width, 3), dtype=tiles[0].dtype, device=tiles[0].device)
     for r in range(world):
-        rows = torch.from_numpy(tile_rows(height, r, world, rows_per_tile)).to(full.device, torch.long)
-        full[rows] = tiles[r]
+        full[_row_index(height, r, world, rows_per_tile, full.device)] = tiles[r]
     return full
 
 
