@@ -180,7 +180,7 @@ def run_ours(args, wl):
     import torch.distributed as dist
 
     import rust_tracer_b200 as rt
-    from rust_tracer_b200.distributed import gather_rows
+    from rust_tracer_b200.distributed import PeerFrame, gather_rows
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -208,12 +208,23 @@ def run_ours(args, wl):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # N > 1: the frame lives on rank 0's GPU, mapped into every rank; the tiles are written straight into
+    # it over NVLink (RT_FLAG_FRAME_ROWS) and the "gather" is a barrier.  NCCL send/recv where mapping fails.
+    frame = PeerFrame.create(h, w, rank, world, local) if world > 1 and not os.environ.get("RT_B200_NCCL_GATHER") else None
+
+    frame_kind = "peer" if frame is not None else "nccl"
+
     def step():
-        """One frame with the scene resident: render this rank's row tiles, gather to rank 0."""
+        """One frame with the scene resident: render this rank's row tiles, collect the frame on rank 0."""
         with torch.cuda.stream(stream):
-            st = scene.render_device(w, h, depth, d_rgb_u8=tile.data_ptr(), spp=spp, seed=1, rank=rank, world=world,
-                                     rows_per_tile=ROWS_PER_TILE)
-            full = gather_rows(tile, h, w, rank, world, ROWS_PER_TILE)
+            if frame is not None:
+                st = scene.render_device(w, h, depth, d_rgb_u8=frame.ptr, spp=spp, seed=1, rank=rank, world=world,
+                                         rows_per_tile=ROWS_PER_TILE, flags=frame.flags)
+                full = frame.collect()
+            else:
+                st = scene.render_device(w, h, depth, d_rgb_u8=tile.data_ptr(), spp=spp, seed=1, rank=rank, world=world,
+                                         rows_per_tile=ROWS_PER_TILE)
+                full = gather_rows(tile, h, w, rank, world, ROWS_PER_TILE)
         return st, full
 
     for _ in range(args.warmup):
@@ -267,10 +278,15 @@ def run_ours(args, wl):
         if world == 1:
             sc.render(w, h, depth, spp=spp, seed=1, want_f32=False, out_u8=pinned.numpy())
         else:
-            t = torch.empty((n_rows, w, 3), dtype=torch.uint8, device=dev)
-            sc.render_device(w, h, depth, d_rgb_u8=t.data_ptr(), spp=spp, seed=1, rank=rank, world=world,
-                             rows_per_tile=ROWS_PER_TILE)
-            full = gather_rows(t, h, w, rank, world, ROWS_PER_TILE)
+            if frame is not None:
+                sc.render_device(w, h, depth, d_rgb_u8=frame.ptr, spp=spp, seed=1, rank=rank, world=world,
+                                 rows_per_tile=ROWS_PER_TILE, flags=frame.flags)
+                full = frame.collect()
+            else:
+                t = torch.empty((n_rows, w, 3), dtype=torch.uint8, device=dev)
+                sc.render_device(w, h, depth, d_rgb_u8=t.data_ptr(), spp=spp, seed=1, rank=rank, world=world,
+                                 rows_per_tile=ROWS_PER_TILE)
+                full = gather_rows(t, h, w, rank, world, ROWS_PER_TILE)
             if rank == 0:
                 pinned.copy_(full)
                 torch.cuda.synchronize()
@@ -287,6 +303,9 @@ def run_ours(args, wl):
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = rays_step * e2e_steps / float(e2e_s.item()) / 1e6
 
+    if frame is not None:
+        barrier()
+        frame.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -350,7 +369,9 @@ def run_ours(args, wl):
         "config": {"workload": args.workload + ": " + wl["desc"], "scene": wl["scene"], "width": w, "height": h,
                    "depth": depth, "spp": spp, "rays_per_frame": rays_step, "rows_per_tile": ROWS_PER_TILE,
                    "l2": "256 MiB buffer written between timed steps; ray pools (>1 GB) exceed L2 anyway",
-                   "partition": "interleaved row tiles, gather to rank 0 inside the step" if world > 1 else "single GPU"},
+                   "partition": ("single GPU" if world == 1 else "interleaved row tiles, " + (
+                       "written straight into rank 0's frame over NVLink (peer-mapped, RT_FLAG_FRAME_ROWS) + barrier"
+                       if frame_kind == "peer" else "NCCL send/recv gather to rank 0") + ", inside the step")},
         "roofline": roofline, "cpu_baseline": cpu,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "what": "rt_scene_create + rt_render into a pinned host RGB8 buffer + rt_scene_destroy"},

@@ -139,7 +139,12 @@ typedef enum rt_render_flags {
      * first; same image by construction, used to audit the filter.                      */
     RT_FLAG_AUDIT_ALL_PAIRS = 1,
     /* evaluate with render_tree.rs's weights instead of render.rs's        */
-    RT_FLAG_FOREST_SHADING = 2
+    RT_FLAG_FOREST_SHADING = 2,
+    /* rt_render_device only: the output buffers are WHOLE frames (y_res x x_res x 3); every
+     * rendered row is stored at its own place instead of compacted.  The buffer may be a
+     * peer-mapped allocation on another GPU (CUDA IPC / peer access): the stores of the last
+     * kernel then are the gather of a multi-GPU frame, over NVLink, with no collective.    */
+    RT_FLAG_FRAME_ROWS = 4
 } rt_render_flags;
 
 typedef struct rt_render_params {
@@ -224,6 +229,22 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *
  * to time the path with inputs resident, and to hand tiles to an NCCL gather.           */
 int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_render_params *params,
                      void *d_rgb_f32, void *d_rgb_u8, rt_stats *stats);
+
+/* ---- multi-GPU frame ------------------------------------------------------ */
+
+/* One whole frame buffer on the GPU that owns the image (rank 0), mapped into every other
+ * rank's process (CUDA IPC, peer access over NVLink): each rank renders its row tiles with
+ * rt_render_device + RT_FLAG_FRAME_ROWS straight into it, so the only exchange step of the
+ * path -- collecting the tiles for the image writer -- is done by the stores of the last
+ * kernel; a barrier afterwards is all the synchronisation needed.
+ *   owner:   rt_frame_alloc, rt_frame_export (64-byte handle, sent to the peers by any means)
+ *   peers:   rt_frame_import on their own device
+ *   both:    rt_frame_release(ptr, imported)                                              */
+#define RT_FRAME_HANDLE_BYTES 64
+int rt_frame_alloc(int32_t device, size_t bytes, void **d_ptr);
+int rt_frame_export(int32_t device, void *d_ptr, uint8_t handle[RT_FRAME_HANDLE_BYTES]);
+int rt_frame_import(int32_t device, const uint8_t handle[RT_FRAME_HANDLE_BYTES], void **d_ptr);
+int rt_frame_release(int32_t device, void *d_ptr, int32_t imported);
 
 /* ---- RayForest renderer -------------------------------------------------------------- */
 

@@ -12,7 +12,8 @@ RT_SHAPE_SPHERE, RT_SHAPE_PLANE, RT_SHAPE_TRIANGLE, RT_SHAPE_CUBE = 0, 1, 2, 3
 RT_COLOR_CONST, RT_COLOR_CHECKERBOARD = 0, 1
 RT_MATERIAL_PHONG, RT_MATERIAL_TEXTURE_PHONG = 0, 1
 RT_LIGHT_POINT, RT_LIGHT_AMBIENT = 0, 1
-RT_FLAG_NONE, RT_FLAG_AUDIT_ALL_PAIRS, RT_FLAG_FOREST_SHADING = 0, 1, 2
+RT_FLAG_NONE, RT_FLAG_AUDIT_ALL_PAIRS, RT_FLAG_FOREST_SHADING, RT_FLAG_FRAME_ROWS = 0, 1, 2, 4
+RT_FRAME_HANDLE_BYTES = 64
 
 
 class rt_shape(C.Structure):

@@ -514,7 +514,8 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
             acc.nodes += lv.nodes;
             if ((rc = shade_band(scene, scene->dev, ws, fp, lv, nullptr)) != RT_OK) return rc;
         }
-        launch_resolve(ws.sample_rgb, s0 / pr->spp, n / pr->spp, pr->spp, out.d_f32, out.d_u8, nullptr, st);
+        launch_resolve(ws.sample_rgb, s0 / pr->spp, n / pr->spp, pr->spp, out.d_f32, out.d_u8, nullptr,
+                       (pr->flags & RT_FLAG_FRAME_ROWS) ? ws.rows : nullptr, cam->x_res, st);
         if (n > 0) scene->launches += 1;
     }
     cudaEventRecord(ev1, st);
@@ -572,6 +573,7 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *
               uint8_t *rgb_u8, rt_stats *stats) {
     int rc = check_params(scene, camera, params);
     if (rc != RT_OK) return rc;
+    if (params->flags & RT_FLAG_FRAME_ROWS) return fail(RT_ERR_INVALID, "RT_FLAG_FRAME_ROWS is for rt_render_device");
     CK(cudaSetDevice(scene->device), "cudaSetDevice");
     Workspace &ws = scene->ws;
     int32_t n_rows = rt_tile_rows_for_rank(camera->y_res, params->rank, params->world, params->tile_rows, nullptr, 0);
@@ -596,6 +598,53 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *
     if ((rc = render_impl(scene, camera, params, out, stats)) != RT_OK) return rc;
     if (rgb_f32 && n_ch) CK(cudaMemcpy(rgb_f32, ws.out_f32, n_ch * sizeof(float), cudaMemcpyDeviceToHost), "D2H rgb_f32");
     if (rgb_u8 && n_ch) CK(cudaMemcpy(rgb_u8, ws.out_u8, n_ch, cudaMemcpyDeviceToHost), "D2H rgb_u8");
+    return RT_OK;
+}
+
+// ---- multi-GPU frame ------------------------------------------------------------------------
+
+int rt_frame_alloc(int32_t device, size_t bytes, void **d_ptr) {
+    if (!d_ptr || bytes == 0) return fail(RT_ERR_INVALID, "null argument");
+    *d_ptr = nullptr;
+    CK(cudaSetDevice(device), "cudaSetDevice");
+    cudaError_t e = cudaMalloc(d_ptr, bytes); // its own allocation: an IPC handle names a whole cudaMalloc block
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(e == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA, "cudaMalloc(frame, %zu bytes): %s", bytes,
+                    cudaGetErrorString(e));
+    }
+    return RT_OK;
+}
+
+int rt_frame_export(int32_t device, void *d_ptr, uint8_t handle[RT_FRAME_HANDLE_BYTES]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_FRAME_HANDLE_BYTES, "handle size");
+    if (!d_ptr || !handle) return fail(RT_ERR_INVALID, "null argument");
+    CK(cudaSetDevice(device), "cudaSetDevice");
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, d_ptr), "cudaIpcGetMemHandle");
+    std::memcpy(handle, &h, sizeof(h));
+    return RT_OK;
+}
+
+int rt_frame_import(int32_t device, const uint8_t handle[RT_FRAME_HANDLE_BYTES], void **d_ptr) {
+    if (!d_ptr || !handle) return fail(RT_ERR_INVALID, "null argument");
+    *d_ptr = nullptr;
+    CK(cudaSetDevice(device), "cudaSetDevice");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    cudaError_t e = cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        *d_ptr = nullptr;
+        return cuda_fail(e, "cudaIpcOpenMemHandle");
+    }
+    return RT_OK;
+}
+
+int rt_frame_release(int32_t device, void *d_ptr, int32_t imported) {
+    if (!d_ptr) return RT_OK;
+    CK(cudaSetDevice(device), "cudaSetDevice");
+    CK(imported ? cudaIpcCloseMemHandle(d_ptr) : cudaFree(d_ptr), "frame release");
     return RT_OK;
 }
 
@@ -743,7 +792,7 @@ static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *i
         CK(cudaMalloc((void **)&d_u8, n_ch), "cudaMalloc(out)");
         if (filtered) CK(cudaMemcpyAsync(d_u8, rgb_u8, n_ch, cudaMemcpyHostToDevice, st), "H2D inout");
     }
-    launch_resolve(ws.sample_rgb, 0, n, 1, d_f32, d_u8, mask, st);
+    launch_resolve(ws.sample_rgb, 0, n, 1, d_f32, d_u8, mask, nullptr, 0, st);
     cudaEventRecord(ev1, st);
     if (d_f32) CK(cudaMemcpyAsync(rgb_f32, d_f32, n_ch * sizeof(float), cudaMemcpyDeviceToHost, st), "D2H");
     if (d_u8) CK(cudaMemcpyAsync(rgb_u8, d_u8, n_ch, cudaMemcpyDeviceToHost, st), "D2H");

@@ -113,9 +113,13 @@ void launch_spawn(const DevScene &sc, const FrameParams &fp, const Pools &p, int
 // sample_rgb[sample - sample0] at level 0.
 void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level,
                   float4 *sample_rgb, const unsigned char *sample_mask, cudaStream_t stream);
-// Average spp samples per pixel (ordered sum * 0.25), write f32 and/or quantised u8.
+// Average spp samples per pixel (ordered sum * 0.25), write f32 and/or quantised u8.  Pixel
+// pixel0 + i of the rendered rows goes to position pixel0 + i of the output, or, with frame_rows
+// (device: the image row of every rendered row), to its own place in a whole width-wide frame --
+// which may be another GPU's memory: the stores then are the multi-GPU gather.
 void launch_resolve(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp, float *rgb_f32,
-                    unsigned char *rgb_u8, const unsigned char *pixel_mask, cudaStream_t stream);
+                    unsigned char *rgb_u8, const unsigned char *pixel_mask, const int *frame_rows, int width,
+                    cudaStream_t stream);
 
 // Forest bookkeeping over tree rays [0, n): sizes[root] += 1 per node (RayTree::size,
 // render_tree.rs:39-48); mask[root] = 1 if a node's Intersection::id is in ids[]

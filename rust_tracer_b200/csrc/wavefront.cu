@@ -329,7 +329,7 @@ shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level
 
 __global__ void __launch_bounds__(256)
 resolve_kernel(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp, float *rgb_f32,
-               unsigned char *rgb_u8, const unsigned char *pixel_mask) {
+               unsigned char *rgb_u8, const unsigned char *pixel_mask, const int *frame_rows, int width) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pixels) return;
     if (pixel_mask && !pixel_mask[i]) return;
@@ -345,7 +345,9 @@ resolve_kernel(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp
         }
         c = cscale(0.25f, sum);
     }
-    long long o = (pixel0 + i) * 3;
+    long long o = pixel0 + i; // pixel number among the rendered rows
+    if (frame_rows) o = (long long)frame_rows[o / width] * width + o % width; // its place in the whole frame
+    o *= 3;
     if (rgb_f32) { rgb_f32[o] = c.x; rgb_f32[o + 1] = c.y; rgb_f32[o + 2] = c.z; }
     if (rgb_u8) { rgb_u8[o] = as_u8(c.x); rgb_u8[o + 1] = as_u8(c.y); rgb_u8[o + 2] = as_u8(c.z); }
 }
@@ -387,10 +389,11 @@ void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int
                                                                           sample_mask);
 }
 void launch_resolve(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp, float *rgb_f32,
-                    unsigned char *rgb_u8, const unsigned char *pixel_mask, cudaStream_t stream) {
+                    unsigned char *rgb_u8, const unsigned char *pixel_mask, const int *frame_rows, int width,
+                    cudaStream_t stream) {
     if (n_pixels > 0)
         resolve_kernel<<<nblk(n_pixels, 256), 256, 0, stream>>>(sample_rgb, pixel0, n_pixels, spp, rgb_f32, rgb_u8,
-                                                                pixel_mask);
+                                                                pixel_mask, frame_rows, width);
 }
 
 void launch_forest_sizes(const Pools &p, int n, int *sizes, cudaStream_t stream) {

@@ -8,10 +8,80 @@ NCCL has no native gather to ragged sizes, so the gather is point-to-point: ever
 NCCL runs as one grouped send/recv over NVLink).  On CPU (gloo) the same code runs the
 world_size-2 tests.
 """
+import ctypes as C
+
 import torch
 import torch.distributed as dist
 
+from . import abi
+from ._lib import check, lib
 from .api import tile_rows
+
+
+class _RawCudaBuffer:
+    """Lets torch view a raw device allocation (rank 0 reads the finished frame as a tensor)."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+class PeerFrame:
+    """The whole RGB8 frame on rank 0's GPU, mapped into every rank (include/rt_b200.h:
+    rt_frame_*): each rank renders its row tiles straight into it with RT_FLAG_FRAME_ROWS --
+    the stores of the resolve kernel travel over NVLink -- and `collect()` is a barrier.
+    Replaces the NCCL send/recv gather below; `PeerFrame.create` returns None where the
+    mapping is refused (no peer access, IPC not permitted), and callers fall back to it."""
+
+    def __init__(self, ptr, height, width, rank, world, local_device, imported):
+        self.ptr, self.height, self.width = ptr, height, width
+        self.rank, self.world, self.local_device, self.imported = rank, world, local_device, imported
+        self.flags = abi.RT_FLAG_FRAME_ROWS
+
+    @classmethod
+    def create(cls, height, width, rank, world, local_device):
+        nbytes = height * width * 3
+        dev = torch.device("cuda", local_device)
+        handle = torch.zeros(abi.RT_FRAME_HANDLE_BYTES, dtype=torch.uint8, device=dev)
+        ptr = C.c_void_p()
+        ok = torch.ones(1, dtype=torch.int32, device=dev)
+        if rank == 0:
+            hbuf = (C.c_uint8 * abi.RT_FRAME_HANDLE_BYTES)()
+            try:
+                check(lib().rt_frame_alloc(local_device, nbytes, C.byref(ptr)))
+                check(lib().rt_frame_export(local_device, ptr, hbuf))
+                handle.copy_(torch.tensor(list(hbuf), dtype=torch.uint8))
+            except RuntimeError:
+                ok.zero_()
+        if world > 1:
+            dist.broadcast(handle, 0)
+        if rank != 0:
+            hbuf = (C.c_uint8 * abi.RT_FRAME_HANDLE_BYTES)(*handle.cpu().tolist())
+            try:
+                check(lib().rt_frame_import(local_device, hbuf, C.byref(ptr)))
+            except RuntimeError:
+                ok.zero_()
+        if world > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks or none
+        frame = cls(ptr.value, height, width, rank, world, local_device, rank != 0) if ptr.value else None
+        if int(ok.item()) == 0:
+            if frame is not None:
+                frame.close()
+            return None
+        return frame
+
+    def collect(self):
+        """After every rank's render call has returned: the frame is complete on rank 0.
+        Returns it there as a [height, width, 3] uint8 tensor (a view, no copy), None elsewhere."""
+        if self.world > 1:
+            dist.barrier()
+        if self.rank != 0:
+            return None
+        return torch.as_tensor(_RawCudaBuffer(self.ptr, (self.height, self.width, 3)), device=torch.device("cuda", self.local_device))
+
+    def close(self):
+        if self.ptr:
+            lib().rt_frame_release(self.local_device, C.c_void_p(self.ptr), 1 if self.imported else 0)
+            self.ptr = None
 
 
 _row_index_cache = {}

@@ -244,3 +244,30 @@ def test_ambient_light_source_is_nan_like_the_reference():
     of, ou, oc = orc.render(desc.desc, abi.default_camera(48, 48), 3)
     assert (np.isnan(f) == np.isnan(of)).all() and np.isnan(of).any()
     assert (u == ou).all() and st["rays"] == oc.rays and st["shadow_rays"] == 0
+
+
+def test_frame_rows_flag_writes_rows_in_place():
+    """RT_FLAG_FRAME_ROWS (rt_render_device): each rank's rows land at their own place of a
+    whole-frame buffer, so two ranks writing into one buffer assemble the frame with no gather
+    (the multi-GPU path maps that buffer across processes: distributed.PeerFrame)."""
+    import torch
+    desc = rt.SceneDesc.builtin("default")
+    w, h, depth = 200, 131, 4  # 131 rows: a ragged last tile
+    sc = rt.Scene(desc)
+    try:
+        ref = torch.zeros((h, w, 3), dtype=torch.uint8, device="cuda")
+        sc.render_device(w, h, depth, d_rgb_u8=ref.data_ptr())
+        full = torch.zeros((h, w, 3), dtype=torch.uint8, device="cuda")
+        ref_f = torch.zeros((h, w, 3), dtype=torch.float32, device="cuda")
+        sc.render_device(w, h, depth, d_rgb_f32=ref_f.data_ptr())
+        full_f = torch.zeros((h, w, 3), dtype=torch.float32, device="cuda")
+        for rank in range(3):
+            sc.render_device(w, h, depth, d_rgb_u8=full.data_ptr(), d_rgb_f32=full_f.data_ptr(), rank=rank, world=3,
+                             rows_per_tile=8, flags=abi.RT_FLAG_FRAME_ROWS)
+        torch.cuda.synchronize()
+        assert bool((full == ref).all())
+        assert torch.equal(full_f, ref_f)
+        with pytest.raises(Exception):
+            sc.render(w, h, depth, flags=abi.RT_FLAG_FRAME_ROWS)  # host-buffer call: compacted rows only
+    finally:
+        sc.close()

@@ -7,7 +7,7 @@ sys.path.insert(0, ROOT)
 import torch
 import torch.distributed as dist
 import rust_tracer_b200 as rt
-from rust_tracer_b200.distributed import gather_rows
+from rust_tracer_b200.distributed import PeerFrame, gather_rows
 
 rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
 torch.cuda.set_device(local)
@@ -21,12 +21,25 @@ for name, w, h, depth, spp in (("default", 1920, 1080, 3, 1), ("m10k", 960, 540,
     tile = torch.empty((n_rows, w, 3), dtype=torch.uint8, device=dev)
     sc.render_device(w, h, depth, d_rgb_u8=tile.data_ptr(), spp=spp, seed=3, rank=rank, world=world, rows_per_tile=8)
     full = gather_rows(tile, h, w, rank, world, 8)
+    # the same through the peer-mapped frame: every rank stores its rows into rank 0's buffer
+    frame = PeerFrame.create(h, w, rank, world, local) if world > 1 else None
+    peer = None
+    if frame is not None:
+        sc.render_device(w, h, depth, d_rgb_u8=frame.ptr, spp=spp, seed=3, rank=rank, world=world, rows_per_tile=8,
+                         flags=frame.flags)
+        peer = frame.collect()
     if rank == 0:
         ref = torch.empty((h, w, 3), dtype=torch.uint8, device=dev)
         sc.render_device(w, h, depth, d_rgb_u8=ref.data_ptr(), spp=spp, seed=3)
         same = bool((full == ref).all())
-        ok &= same
-        print("%s %dx%d d%d spp%d world %d: gathered == single-GPU frame: %s" % (name, w, h, depth, spp, world, same), flush=True)
+        same_peer = bool((peer == ref).all()) if peer is not None else None
+        ok &= same and same_peer is not False
+        print("%s %dx%d d%d spp%d world %d: gathered == single-GPU frame: %s; peer-mapped frame: %s" % (
+            name, w, h, depth, spp, world, same, same_peer), flush=True)
+    if frame is not None:
+        if world > 1:
+            dist.barrier()
+        frame.close()
     sc.close()
 if world > 1:
     dist.barrier()
