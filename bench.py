@@ -209,7 +209,7 @@ def run_ours(args, wl):
         torch.cuda.synchronize()
 
     # N > 1: the frame lives on rank 0's GPU, mapped into every rank; the tiles are written straight into
-    # it over NVLink (RT_FLAG_FRAME_ROWS) and the "gather" is a barrier.  NCCL send/recv where mapping fails.
+    # it over NVLink (RT_FLAG_FRAME_ROWS); completion travels through signal words in the same memory (PeerFrame).  NCCL send/recv where mapping fails.
     frame = PeerFrame.create(h, w, rank, world, local) if world > 1 and not os.environ.get("RT_B200_NCCL_GATHER") else None
 
     frame_kind = "peer" if frame is not None else "nccl"
@@ -218,9 +218,11 @@ def run_ours(args, wl):
         """One frame with the scene resident: render this rank's row tiles, collect the frame on rank 0."""
         with torch.cuda.stream(stream):
             if frame is not None:
+                frame.begin()
                 st = scene.render_device(w, h, depth, d_rgb_u8=frame.ptr, spp=spp, seed=1, rank=rank, world=world,
                                          rows_per_tile=ROWS_PER_TILE, flags=frame.flags)
-                full = frame.collect()
+                full = frame.collect()  # rank 0: returns once every rank's rows are in its frame
+                frame.release()
             else:
                 st = scene.render_device(w, h, depth, d_rgb_u8=tile.data_ptr(), spp=spp, seed=1, rank=rank, world=world,
                                          rows_per_tile=ROWS_PER_TILE)
@@ -279,6 +281,7 @@ def run_ours(args, wl):
             sc.render(w, h, depth, spp=spp, seed=1, want_f32=False, out_u8=pinned.numpy())
         else:
             if frame is not None:
+                frame.begin()
                 sc.render_device(w, h, depth, d_rgb_u8=frame.ptr, spp=spp, seed=1, rank=rank, world=world,
                                  rows_per_tile=ROWS_PER_TILE, flags=frame.flags)
                 full = frame.collect()
@@ -290,6 +293,8 @@ def run_ours(args, wl):
             if rank == 0:
                 pinned.copy_(full)
                 torch.cuda.synchronize()
+            if frame is not None:
+                frame.release()
         sc.close()
 
     e2e_step()  # warm-up
@@ -370,7 +375,7 @@ def run_ours(args, wl):
                    "depth": depth, "spp": spp, "rays_per_frame": rays_step, "rows_per_tile": ROWS_PER_TILE,
                    "l2": "256 MiB buffer written between timed steps; ray pools (>1 GB) exceed L2 anyway",
                    "partition": ("single GPU" if world == 1 else "interleaved row tiles, " + (
-                       "written straight into rank 0's frame over NVLink (peer-mapped, RT_FLAG_FRAME_ROWS) + barrier"
+                       "written straight into rank 0's frame over NVLink (peer-mapped, RT_FLAG_FRAME_ROWS); each rank signals a word in that frame, rank 0 waits for all on the device"
                        if frame_kind == "peer" else "NCCL send/recv gather to rank 0") + ", inside the step")},
         "roofline": roofline, "cpu_baseline": cpu,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -41,7 +41,8 @@ typedef enum rt_status {
     RT_ERR_UNSUPPORTED = -2,  /* e.g. a texture function that is not in rt_colorfn */
     RT_ERR_CUDA = -3,         /* CUDA runtime failure or no device                 */
     RT_ERR_NOMEM = -4,        /* host or device allocation failed                  */
-    RT_ERR_INTERNAL = -5
+    RT_ERR_INTERNAL = -5,
+    RT_ERR_TIMEOUT = -6       /* rt_frame_wait: a peer did not signal in time           */
 } rt_status;
 
 /* ---- scene description (mirrors src/scene/{mod,sphere,plane,triangle,cube,material}.rs; copied at rt_scene_create) ---------- */
@@ -235,16 +236,35 @@ int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_render_p
 /* One whole frame buffer on the GPU that owns the image (rank 0), mapped into every other
  * rank's process (CUDA IPC, peer access over NVLink): each rank renders its row tiles with
  * rt_render_device + RT_FLAG_FRAME_ROWS straight into it, so the only exchange step of the
- * path -- collecting the tiles for the image writer -- is done by the stores of the last
- * kernel; a barrier afterwards is all the synchronisation needed.
+ * path -- collecting the tiles for the image writer (the reference has one RenderBuffer,
+ * src/render.rs:31-38) -- is done by the stores of the last kernel.
  *   owner:   rt_frame_alloc, rt_frame_export (64-byte handle, sent to the peers by any means)
  *   peers:   rt_frame_import on their own device
- *   both:    rt_frame_release(ptr, imported)                                              */
+ *   both:    rt_frame_release(ptr, imported)
+ * Behind the `bytes` of pixels (rounded up to 256) the allocation carries
+ * RT_FRAME_SIGNAL_WORDS 32-bit words, zeroed by rt_frame_alloc, through which the ranks tell
+ * each other how far they are, on the device, in stream order, with no host barrier and no
+ * collective:
+ *   rt_frame_signal  enqueues "word := value" after everything already on `stream` (a
+ *                    system-scope release: the pixels this rank stored are visible to whoever
+ *                    sees the word); returns at once.
+ *   rt_frame_wait    enqueues a one-warp kernel that polls words [first_word, first_word +
+ *                    n_words) until each is >= value (32-bit wrap-around safe), then waits
+ *                    for the stream; RT_ERR_TIMEOUT after timeout_ms (0 or > 60000: 60000),
+ *                    so a dead peer cannot hang the GPU.
+ * Convention used by rust_tracer_b200/distributed.py:PeerFrame -- word r: rank r has finished
+ * frame number `value`; word RT_FRAME_WORD_RELEASED: the owner has consumed it and the
+ * peers may overwrite the pixels.  `bytes` must be the value given to rt_frame_alloc.     */
 #define RT_FRAME_HANDLE_BYTES 64
+#define RT_FRAME_SIGNAL_WORDS 256
+#define RT_FRAME_WORD_RELEASED 255
 int rt_frame_alloc(int32_t device, size_t bytes, void **d_ptr);
 int rt_frame_export(int32_t device, void *d_ptr, uint8_t handle[RT_FRAME_HANDLE_BYTES]);
 int rt_frame_import(int32_t device, const uint8_t handle[RT_FRAME_HANDLE_BYTES], void **d_ptr);
 int rt_frame_release(int32_t device, void *d_ptr, int32_t imported);
+int rt_frame_signal(int32_t device, void *d_ptr, size_t bytes, int32_t word, uint32_t value, void *stream);
+int rt_frame_wait(int32_t device, void *d_ptr, size_t bytes, int32_t first_word, int32_t n_words, uint32_t value,
+                  uint32_t timeout_ms, void *stream);
 
 /* ---- RayForest renderer -------------------------------------------------------------- */
 

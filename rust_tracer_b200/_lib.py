@@ -40,6 +40,8 @@ def _declare(lib):
     lib.rt_frame_export.argtypes = [C.c_int32, vp, P(C.c_uint8)]
     lib.rt_frame_import.argtypes = [C.c_int32, P(C.c_uint8), P(vp)]
     lib.rt_frame_release.argtypes = [C.c_int32, vp, C.c_int32]
+    lib.rt_frame_signal.argtypes = [C.c_int32, vp, C.c_size_t, C.c_int32, C.c_uint32, vp]
+    lib.rt_frame_wait.argtypes = [C.c_int32, vp, C.c_size_t, C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, vp]
     lib.rt_render.argtypes = [vp, P(abi.rt_camera), P(abi.rt_render_params), vp, vp, P(abi.rt_stats)]
     lib.rt_render_device.argtypes = [vp, P(abi.rt_camera), P(abi.rt_render_params), vp, vp, P(abi.rt_stats)]
     lib.rt_forest_build.argtypes = [vp, P(abi.rt_camera), P(abi.rt_render_params), P(vp), P(abi.rt_stats)]
@@ -71,7 +73,7 @@ def _declare(lib):
 EXPORTS = [
     "rt_abi_version", "rt_last_error", "rt_device_count", "rt_camera_default", "rt_tile_rows_for_rank",
     "rt_scene_create", "rt_scene_update_materials", "rt_scene_set_stream", "rt_scene_destroy", "rt_trim", "rt_render", "rt_render_device",
-    "rt_frame_alloc", "rt_frame_export", "rt_frame_import", "rt_frame_release",
+    "rt_frame_alloc", "rt_frame_export", "rt_frame_import", "rt_frame_release", "rt_frame_signal", "rt_frame_wait",
     "rt_forest_build", "rt_forest_eval", "rt_forest_eval_filtered", "rt_forest_get_stats", "rt_forest_size",
     "rt_forest_trees_with", "rt_forest_destroy", "rt_measure_fp32_peak",
     "rt_builtin_scene", "rt_synthetic_scene", "rt_scene_desc_free", "rt_matrix_inverse", "rt_matrix_compose",

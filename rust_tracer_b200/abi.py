@@ -6,7 +6,7 @@ Kept free of any library loading so that both the product binding
 import ctypes as C
 
 RT_OK = 0
-RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NOMEM, RT_ERR_INTERNAL = -1, -2, -3, -4, -5
+RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NOMEM, RT_ERR_INTERNAL, RT_ERR_TIMEOUT = -1, -2, -3, -4, -5, -6
 
 RT_SHAPE_SPHERE, RT_SHAPE_PLANE, RT_SHAPE_TRIANGLE, RT_SHAPE_CUBE = 0, 1, 2, 3
 RT_COLOR_CONST, RT_COLOR_CHECKERBOARD = 0, 1
@@ -14,6 +14,8 @@ RT_MATERIAL_PHONG, RT_MATERIAL_TEXTURE_PHONG = 0, 1
 RT_LIGHT_POINT, RT_LIGHT_AMBIENT = 0, 1
 RT_FLAG_NONE, RT_FLAG_AUDIT_ALL_PAIRS, RT_FLAG_FOREST_SHADING, RT_FLAG_FRAME_ROWS = 0, 1, 2, 4
 RT_FRAME_HANDLE_BYTES = 64
+RT_FRAME_SIGNAL_WORDS = 256
+RT_FRAME_WORD_RELEASED = 255
 
 
 class rt_shape(C.Structure):

@@ -601,53 +601,6 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *
     return RT_OK;
 }
 
-// ---- multi-GPU frame ------------------------------------------------------------------------
-
-int rt_frame_alloc(int32_t device, size_t bytes, void **d_ptr) {
-    if (!d_ptr || bytes == 0) return fail(RT_ERR_INVALID, "null argument");
-    *d_ptr = nullptr;
-    CK(cudaSetDevice(device), "cudaSetDevice");
-    cudaError_t e = cudaMalloc(d_ptr, bytes); // its own allocation: an IPC handle names a whole cudaMalloc block
-    if (e != cudaSuccess) {
-        cudaGetLastError();
-        return fail(e == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA, "cudaMalloc(frame, %zu bytes): %s", bytes,
-                    cudaGetErrorString(e));
-    }
-    return RT_OK;
-}
-
-int rt_frame_export(int32_t device, void *d_ptr, uint8_t handle[RT_FRAME_HANDLE_BYTES]) {
-    static_assert(sizeof(cudaIpcMemHandle_t) == RT_FRAME_HANDLE_BYTES, "handle size");
-    if (!d_ptr || !handle) return fail(RT_ERR_INVALID, "null argument");
-    CK(cudaSetDevice(device), "cudaSetDevice");
-    cudaIpcMemHandle_t h;
-    CK(cudaIpcGetMemHandle(&h, d_ptr), "cudaIpcGetMemHandle");
-    std::memcpy(handle, &h, sizeof(h));
-    return RT_OK;
-}
-
-int rt_frame_import(int32_t device, const uint8_t handle[RT_FRAME_HANDLE_BYTES], void **d_ptr) {
-    if (!d_ptr || !handle) return fail(RT_ERR_INVALID, "null argument");
-    *d_ptr = nullptr;
-    CK(cudaSetDevice(device), "cudaSetDevice");
-    cudaIpcMemHandle_t h;
-    std::memcpy(&h, handle, sizeof(h));
-    cudaError_t e = cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess);
-    if (e != cudaSuccess) {
-        cudaGetLastError();
-        *d_ptr = nullptr;
-        return cuda_fail(e, "cudaIpcOpenMemHandle");
-    }
-    return RT_OK;
-}
-
-int rt_frame_release(int32_t device, void *d_ptr, int32_t imported) {
-    if (!d_ptr) return RT_OK;
-    CK(cudaSetDevice(device), "cudaSetDevice");
-    CK(imported ? cudaIpcCloseMemHandle(d_ptr) : cudaFree(d_ptr), "frame release");
-    return RT_OK;
-}
-
 // ---- RayForest ------------------------------------------------------------------------------
 
 int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_params *params, rt_forest **out,

@@ -1,7 +1,11 @@
-"""Multi-GPU plumbing: one process per GPU (torch.distributed), interleaved row tiles, one
-gather of the quantised RGB8 tiles to rank 0 -- the only exchange step of the path
-(SURVEY 8e).  Rendering itself has no collective: pixels are independent
-(reference src/render.rs:31-38 writes one cell per iteration).
+"""Multi-GPU plumbing: one process per GPU (torch.distributed), interleaved row tiles, and
+getting the quantised RGB8 rows to rank 0 -- the only exchange step of the path.
+Rendering itself has no collective: pixels are independent (reference src/render.rs:31-38
+writes one cell per iteration).
+
+PeerFrame: the frame lives on rank 0's GPU, every rank's resolve kernel stores its rows there
+over NVLink, completion travels through signal words in the same memory.  gather_rows is the
+fallback where peer mapping is not available, and what the CPU (gloo) tests exercise.
 
 NCCL has no native gather to ragged sizes, so the gather is point-to-point: every rank
 != 0 sends its tile buffer, rank 0 receives each into place (batched isend/irecv, which
@@ -28,17 +32,30 @@ class _RawCudaBuffer:
 class PeerFrame:
     """The whole RGB8 frame on rank 0's GPU, mapped into every rank (include/rt_b200.h:
     rt_frame_*): each rank renders its row tiles straight into it with RT_FLAG_FRAME_ROWS --
-    the stores of the resolve kernel travel over NVLink -- and `collect()` is a barrier.
+    the stores of the resolve kernel travel over NVLink -- and tells rank 0 it is done through
+    a signal word behind the pixels, in stream order.  No host barrier, no collective:
+
+        frame.begin()                       # peers: wait until rank 0 has released the previous frame
+        scene.render_device(..., d_rgb_u8=frame.ptr, flags=frame.flags, rank=, world=)
+        full = frame.collect()              # every rank signals; rank 0 waits for all and gets the frame
+        ... rank 0 consumes `full` ...
+        frame.release()                     # rank 0: the peers may overwrite the pixels
+
     Replaces the NCCL send/recv gather below; `PeerFrame.create` returns None where the
     mapping is refused (no peer access, IPC not permitted), and callers fall back to it."""
 
-    def __init__(self, ptr, height, width, rank, world, local_device, imported):
+    def __init__(self, ptr, height, width, rank, world, local_device, imported, timeout_ms=20000):
         self.ptr, self.height, self.width = ptr, height, width
         self.rank, self.world, self.local_device, self.imported = rank, world, local_device, imported
+        self.nbytes = height * width * 3
         self.flags = abi.RT_FLAG_FRAME_ROWS
+        self.epoch = 0          # number of the frame being rendered / last collected
+        self.timeout_ms = timeout_ms
 
     @classmethod
     def create(cls, height, width, rank, world, local_device):
+        if world > abi.RT_FRAME_WORD_RELEASED:
+            return None
         nbytes = height * width * 3
         dev = torch.device("cuda", local_device)
         handle = torch.zeros(abi.RT_FRAME_HANDLE_BYTES, dtype=torch.uint8, device=dev)
@@ -69,16 +86,39 @@ class PeerFrame:
             return None
         return frame
 
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.local_device).cuda_stream)
+
+    def begin(self):
+        """Before rendering the next frame into the buffer.  A peer waits (on the device) until rank 0
+        has released the previous one; rank 0 itself never waits here."""
+        self.epoch += 1
+        if self.rank != 0 and self.epoch > 1:
+            check(lib().rt_frame_wait(self.local_device, C.c_void_p(self.ptr), self.nbytes, abi.RT_FRAME_WORD_RELEASED, 1,
+                                      self.epoch - 1, self.timeout_ms, self._stream()))
+
     def collect(self):
-        """After every rank's render call has returned: the frame is complete on rank 0.
-        Returns it there as a [height, width, 3] uint8 tensor (a view, no copy), None elsewhere."""
-        if self.world > 1:
-            dist.barrier()
+        """After this rank's render call: publish "my rows of frame #epoch are in place".  Rank 0 then
+        waits (on the device) for every rank's word and returns the frame as a [height, width, 3]
+        uint8 tensor (a view, no copy); the other ranks return None without waiting for anyone."""
+        if self.epoch == 0:
+            raise RuntimeError("PeerFrame.collect() without begin()")
+        check(lib().rt_frame_signal(self.local_device, C.c_void_p(self.ptr), self.nbytes, self.rank, self.epoch, self._stream()))
         if self.rank != 0:
             return None
+        check(lib().rt_frame_wait(self.local_device, C.c_void_p(self.ptr), self.nbytes, 0, self.world, self.epoch,
+                                  self.timeout_ms, self._stream()))
         return torch.as_tensor(_RawCudaBuffer(self.ptr, (self.height, self.width, 3)), device=torch.device("cuda", self.local_device))
 
+    def release(self):
+        """Rank 0, once it has consumed the collected frame (ordered after the work already on the
+        current stream, e.g. a copy to the host): the peers may start writing the next one."""
+        if self.rank == 0 and self.epoch > 0:
+            check(lib().rt_frame_signal(self.local_device, C.c_void_p(self.ptr), self.nbytes, abi.RT_FRAME_WORD_RELEASED,
+                                        self.epoch, self._stream()))
+
     def close(self):
+        """Peers unmap, the owner frees; the caller makes sure (a barrier) that the peers are done first."""
         if self.ptr:
             lib().rt_frame_release(self.local_device, C.c_void_p(self.ptr), 1 if self.imported else 0)
             self.ptr = None

@@ -271,3 +271,39 @@ def test_frame_rows_flag_writes_rows_in_place():
             sc.render(w, h, depth, flags=abi.RT_FLAG_FRAME_ROWS)  # host-buffer call: compacted rows only
     finally:
         sc.close()
+
+
+def test_frame_signal_words():
+    """rt_frame_signal / rt_frame_wait: stream-ordered words behind the pixels of a frame; a wait for a
+    value nobody signals ends with RT_ERR_TIMEOUT instead of hanging the GPU."""
+    import ctypes as C
+    import time
+    import torch
+    from rust_tracer_b200._lib import RtError, check, lib
+    L = lib()
+    nbytes = 100 * 30 * 3  # not a multiple of 256: the words start at the next 256-byte boundary
+    ptr = C.c_void_p()
+    check(L.rt_frame_alloc(0, nbytes, C.byref(ptr)))
+    try:
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        check(L.rt_frame_wait(0, ptr, nbytes, 0, abi.RT_FRAME_SIGNAL_WORDS, 0, 100, st))  # zeroed at allocation
+        for word in range(40):  # more words than one warp has lanes
+            check(L.rt_frame_signal(0, ptr, nbytes, word, 7, st))
+        check(L.rt_frame_signal(0, ptr, nbytes, abi.RT_FRAME_WORD_RELEASED, 6, st))
+        check(L.rt_frame_wait(0, ptr, nbytes, 0, 40, 7, 1000, st))
+        check(L.rt_frame_wait(0, ptr, nbytes, abi.RT_FRAME_WORD_RELEASED, 1, 6, 1000, st))
+        t0 = time.perf_counter()
+        with pytest.raises(RtError) as e:
+            check(L.rt_frame_wait(0, ptr, nbytes, 0, 41, 7, 50, st))  # word 40 was never signalled
+        assert e.value.code == abi.RT_ERR_TIMEOUT and time.perf_counter() - t0 < 5.0
+        with pytest.raises(RtError):
+            check(L.rt_frame_wait(0, ptr, nbytes, 250, 10, 1, 50, st))  # range past the last word
+        # the pixels are untouched by the signalling
+        from rust_tracer_b200.distributed import _RawCudaBuffer
+        px = torch.as_tensor(_RawCudaBuffer(ptr.value, (nbytes,)), device="cuda")
+        px.fill_(9)
+        check(L.rt_frame_signal(0, ptr, nbytes, 0, 8, st))
+        check(L.rt_frame_wait(0, ptr, nbytes, 0, 1, 8, 1000, st))
+        assert bool((px == 9).all())
+    finally:
+        L.rt_frame_release(0, ptr, 0)
