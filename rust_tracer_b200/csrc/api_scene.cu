@@ -3,6 +3,7 @@
 // structure-of-arrays device tables of scene_dev.cuh, and builds the conservative
 // bounding spheres the sweep filters with.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -355,6 +356,15 @@ int32_t rt_tile_rows_for_rank(int32_t height, int32_t rank, int32_t world, int32
 
 int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     if (!desc || !out) return fail(RT_ERR_INVALID, "null argument");
+    const bool trace = std::getenv("RT_B200_TRACE") != nullptr; // phase times of the host-side build
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto t_last = now();
+    auto lap = [&](const char *what) {
+        if (!trace) return;
+        auto t = now();
+        std::fprintf(stderr, "[rt_b200] scene create: %-22s %.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t_last).count());
+        t_last = t;
+    };
     *out = nullptr;
     if (desc->n_shapes < 0 || desc->n_materials < 0 || desc->n_lights < 0 || (desc->n_shapes && !desc->shapes) ||
         (desc->n_materials && !desc->materials) || (desc->n_lights && !desc->lights))
@@ -433,6 +443,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     // segments by error class, each padded to SEG_PAD slots; within a class the bounds are put in
     // the leaf order of a median-split tree whose leaves hold exactly GROUP_SLOTS bounds, so that
     // the slots of a group are neighbours in space; slot pairs interleaved for FFMA2
+    lap("shape records, bounds");
     std::stable_sort(bounds.begin(), bounds.end(), [](const B &a, const B &b) {
         bool fa = a.b.w != -3.402823466e+38f, fb = b.b.w != -3.402823466e+38f; // beyond-range bounds last in their class
         return a.cls != b.cls ? a.cls < b.cls : (fa && !fb);
@@ -465,6 +476,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
             work.push_back({lo + left, hi});
         }
     }
+    lap("slot order");
     const int nb = (int)bounds.size();
     SweepSegs segs;
     std::memset(&segs, 0, sizeof(segs));
@@ -505,6 +517,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
             cmax = std::max(cmax, quads[q].reach);
         }
     }
+    lap("groups, quads");
     auto paired = [](const std::vector<Bound> &v) {
         std::vector<float4> out(v.size());
         for (size_t j = 0; j + 1 < v.size(); j += 2) {
@@ -539,6 +552,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     std::vector<float4> ctris;
     cube_tris(ctris);
 
+    lap("slot tables, materials");
     rt_scene *s = new (std::nothrow) rt_scene();
     if (!s) return fail(RT_ERR_NOMEM, "out of host memory");
     s->device = device;
@@ -578,6 +592,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         rt_scene_destroy(s);
         return rc;
     }
+    lap("uploads");
     d.materials = dm;
     s->d_materials = const_cast<DevMaterial *>(dm);
     if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) {
@@ -585,6 +600,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         return cuda_fail(e, "cudaStreamCreate");
     }
     s->own_stream = s->stream;
+    lap("stream");
     if (origin_tables_wanted(n_slots)) {
         auto host_slot = [](const Bound &b) {
             return HostSlot{b.cx, b.cy, b.cz, b.rf, b.w == 3.402823466e+38f ? 1 : (b.w == -3.402823466e+38f ? 2 : 0)};
@@ -614,7 +630,9 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         s->allocs.push_back(ct);
         s->cam_tab = (float4 *)ct;
     }
+    lap("light tables");
     s->ws = workspace_take_cached(device);
+    lap("workspace");
     *out = s;
     return RT_OK;
 }

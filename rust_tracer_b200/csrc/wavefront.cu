@@ -167,74 +167,112 @@ __global__ void __launch_bounds__(256) node_scatter_kernel(Pools p, int begin, i
     if (live) p.t_order[begin + base + __popc(same & ((1u << lane) - 1u))] = i;
 }
 
-__global__ void __launch_bounds__(WF_BLOCK)
+// Child rays of one block are allocated together: its reflected rays first, then its refracted
+// rays.  With the nodes in cell order (node_*_kernel) a run of up to SPAWN_BLOCK consecutive tree
+// rays of the next level then starts at neighbouring points AND leaves the same way -- away from
+// the surface or into it -- which is what the sweep's group culling feeds on.
+constexpr int SPAWN_BLOCK = 512;
+
+__global__ void __launch_bounds__(SPAWN_BLOCK)
 spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn_children, int ordered, int s_begin) {
     const int rank = blockIdx.x * blockDim.x + threadIdx.x; // node number within the level when ordered
-    if (begin + rank >= end) return;
-    const int i = ordered ? p.t_order[begin + rank] : begin + rank;
-    p.t_sbase[i] = -1;
-    p.t_crefl[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    p.t_crefr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    V3 o, d;
-    load_tree_ray(p, i, o, d);
-    Hit h;
-    if (!hit_record(sc, p.t_key[i], o, d, h)) {
-        if (p.t_hitid) p.t_hitid[i] = -1;
-        return;
-    }
-    if (p.t_hitid) p.t_hitid[i] = h.id;
-    atomicAdd(&p.counters[2], 1u);
-    const DevMaterial m = sc.materials[h.material];
-    float n1, n2;
-    refraction_indices(m, h.entering, n1, n2);
-
-    // shadow rays: p = point + 0.0002 * normal (render.rs:147); one per point light
-    if (sc.n_point_lights > 0) {
-        unsigned long long sb = ordered ? (unsigned long long)s_begin + (unsigned long long)rank * (unsigned int)sc.n_point_lights
-                                        : (unsigned long long)atomicAdd(&p.counters[1], (unsigned int)sc.n_point_lights);
-        if (sb + (unsigned int)sc.n_point_lights <= (unsigned long long)p.s_cap) {
-            p.t_sbase[i] = (int)sb;
-            V3 sp = vadd(h.point, vscale(h.normal, 0.0002f));
-            for (int l = 0; l < sc.n_lights; ++l) {
-                DevLight L = sc.lights[l];
-                if (L.kind != 0) continue;
-                V3 ldir = vnorm(vsub(v3(L.px, L.py, L.pz), sp)); // scene/mod.rs:191
-                p.s_a[sb + L.point_index] = make_float4(sp.x, sp.y, sp.z, ldir.x);
-                p.s_b[sb + L.point_index] = make_float4(ldir.y, ldir.z, 0.f, 0.f);
-            }
-        } else {
-            p.counters[3] = 1u;
+    bool refl = false, refr = false, far_node = false;
+    V3 ro0, rd0, ro1, rd1;
+    int i = -1;
+    do {
+        if (begin + rank >= end) break;
+        i = ordered ? p.t_order[begin + rank] : begin + rank;
+        p.t_sbase[i] = -1;
+        p.t_crefl[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        p.t_crefr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        V3 o, d;
+        load_tree_ray(p, i, o, d);
+        Hit h;
+        if (!hit_record(sc, p.t_key[i], o, d, h)) {
+            if (p.t_hitid) p.t_hitid[i] = -1;
+            break;
         }
-    }
+        if (p.t_hitid) p.t_hitid[i] = h.id;
+        atomicAdd(&p.counters[2], 1u);
+        const DevMaterial m = sc.materials[h.material];
+        float n1, n2;
+        refraction_indices(m, h.entering, n1, n2);
+
+        // shadow rays: p = point + 0.0002 * normal (render.rs:147); one per point light
+        if (sc.n_point_lights > 0) {
+            unsigned long long sb = ordered ? (unsigned long long)s_begin + (unsigned long long)rank * (unsigned int)sc.n_point_lights
+                                            : (unsigned long long)atomicAdd(&p.counters[1], (unsigned int)sc.n_point_lights);
+            if (sb + (unsigned int)sc.n_point_lights <= (unsigned long long)p.s_cap) {
+                p.t_sbase[i] = (int)sb;
+                V3 sp = vadd(h.point, vscale(h.normal, 0.0002f));
+                for (int l = 0; l < sc.n_lights; ++l) {
+                    DevLight L = sc.lights[l];
+                    if (L.kind != 0) continue;
+                    V3 ldir = vnorm(vsub(v3(L.px, L.py, L.pz), sp)); // scene/mod.rs:191
+                    p.s_a[sb + L.point_index] = make_float4(sp.x, sp.y, sp.z, ldir.x);
+                    p.s_b[sb + L.point_index] = make_float4(ldir.y, ldir.z, 0.f, 0.f);
+                }
+            } else {
+                p.counters[3] = 1u;
+            }
+        }
+        if (!spawn_children) break;
+        far_node = ordered && (unsigned int)rank < p.counters[4];
+        if (m.reflectivity > F32_EPS) { // render.rs:70
+            reflect_ray(d, h, ro0, rd0);
+            refl = true;
+        }
+        if (m.refraction_index > F32_EPS) // render.rs:86
+            refr = refract_ray(d, h, n1, n2, ro1, rd1);
+    } while (false);
     if (!spawn_children) return;
-    const bool far_node = ordered && (unsigned int)rank < p.counters[4];
-    if (m.reflectivity > F32_EPS) { // render.rs:70
-        V3 ro, rd;
-        reflect_ray(d, h, ro, rd);
-        unsigned int c = atomicAdd(&p.counters[0], 1u);
-        if (far_node) atomicAdd(&p.counters[5], 1u);
+
+    // block-wide allocation: [reflected rays of the block | refracted rays of the block]
+    __shared__ unsigned int warp_refl[SPAWN_BLOCK / 32], warp_refr[SPAWN_BLOCK / 32], warp_far[SPAWN_BLOCK / 32];
+    __shared__ unsigned int block_base, block_refl;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned int m_refl = __ballot_sync(0xffffffffu, refl), m_refr = __ballot_sync(0xffffffffu, refr);
+    const unsigned int m_far = __ballot_sync(0xffffffffu, far_node && refl), m_far2 = __ballot_sync(0xffffffffu, far_node && refr);
+    if (lane == 0) {
+        warp_refl[warp] = __popc(m_refl);
+        warp_refr[warp] = __popc(m_refr);
+        warp_far[warp] = __popc(m_far) + __popc(m_far2);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int n_refl = 0, n_refr = 0, n_far = 0;
+        for (int w = 0; w < SPAWN_BLOCK / 32; ++w) {
+            const unsigned int a = warp_refl[w], b = warp_refr[w];
+            warp_refl[w] = n_refl; // exclusive prefixes
+            warp_refr[w] = n_refr;
+            n_refl += a; n_refr += b; n_far += warp_far[w];
+        }
+        block_refl = n_refl;
+        block_base = (n_refl + n_refr) ? atomicAdd(&p.counters[0], n_refl + n_refr) : 0u;
+        if (n_far) atomicAdd(&p.counters[5], n_far);
+    }
+    __syncthreads();
+    const unsigned int below = (1u << lane) - 1u;
+    if (refl) {
+        const unsigned int c = block_base + warp_refl[warp] + __popc(m_refl & below);
         if (c < (unsigned int)p.t_cap) {
-            p.t_a[c] = make_float4(ro.x, ro.y, ro.z, rd.x);
-            p.t_b[c] = make_float4(rd.y, rd.z, 0.f, 0.f);
+            p.t_a[c] = make_float4(ro0.x, ro0.y, ro0.z, rd0.x);
+            p.t_b[c] = make_float4(rd0.y, rd0.z, 0.f, 0.f);
             p.t_parent[c] = (i << 1) | 0;
             p.t_root[c] = p.t_root[i];
         } else {
             p.counters[3] = 1u;
         }
     }
-    if (m.refraction_index > F32_EPS) { // render.rs:86
-        V3 ro, rd;
-        if (refract_ray(d, h, n1, n2, ro, rd)) {
-            unsigned int c = atomicAdd(&p.counters[0], 1u);
-            if (far_node) atomicAdd(&p.counters[5], 1u);
-            if (c < (unsigned int)p.t_cap) {
-                p.t_a[c] = make_float4(ro.x, ro.y, ro.z, rd.x);
-                p.t_b[c] = make_float4(rd.y, rd.z, 0.f, 0.f);
-                p.t_parent[c] = (i << 1) | 1;
-                p.t_root[c] = p.t_root[i];
-            } else {
-                p.counters[3] = 1u;
-            }
+    if (refr) {
+        const unsigned int c = block_base + block_refl + warp_refr[warp] + __popc(m_refr & below);
+        if (c < (unsigned int)p.t_cap) {
+            p.t_a[c] = make_float4(ro1.x, ro1.y, ro1.z, rd1.x);
+            p.t_b[c] = make_float4(rd1.y, rd1.z, 0.f, 0.f);
+            p.t_parent[c] = (i << 1) | 1;
+            p.t_root[c] = p.t_root[i];
+        } else {
+            p.counters[3] = 1u;
         }
     }
 }
@@ -380,7 +418,7 @@ void launch_spawn(const DevScene &sc, const FrameParams &fp, const Pools &p, int
         node_scan_kernel<<<1, 1024, 0, stream>>>(p, s_begin, sc.n_point_lights);
         node_scatter_kernel<<<nblk(end - begin, 256), 256, 0, stream>>>(p, begin, end);
     }
-    spawn_kernel<<<nblk(end - begin, WF_BLOCK), WF_BLOCK, 0, stream>>>(sc, fp, p, begin, end, spawn_children, ordered, s_begin);
+    spawn_kernel<<<nblk(end - begin, SPAWN_BLOCK), SPAWN_BLOCK, 0, stream>>>(sc, fp, p, begin, end, spawn_children, ordered, s_begin);
 }
 void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level,
                   float4 *sample_rgb, const unsigned char *sample_mask, cudaStream_t stream) {
