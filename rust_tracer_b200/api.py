@@ -123,7 +123,7 @@ class Scene:
         p = _params(depth, spp, seed, rank, world, rows_per_tile, flags)
         n_rows = len(tile_rows(height, rank, world, rows_per_tile))
         f = np.zeros((n_rows, width, 3), dtype=np.float32) if want_f32 else None
-        u = np.zeros((n_rows, width, 3), dtype=np.uint8) if want_u8 else None
+        u = np.zeros((n_rows, width, 3), dtype=np.uint8) if want_u8 and out_u8 is None else None
         if out_u8 is not None:
             if out_u8.dtype != np.uint8 or out_u8.size != n_rows * width * 3 or not out_u8.flags.c_contiguous:
                 raise ValueError("out_u8 must be a contiguous uint8 array of %d x %d x 3" % (n_rows, width))

@@ -26,6 +26,8 @@ struct Workspace {
     int batch_next = 0;
     void *out_f32 = nullptr, *out_u8 = nullptr; // device staging for host-buffer calls
     size_t out_f32_cap = 0, out_u8_cap = 0;
+    void *tables = nullptr; // the device tables of the scene that holds this workspace (api_scene.cu: Arena)
+    size_t tables_cap = 0;
 
     int ensure_pools(long long t_cap, long long s_cap);
     int ensure_samples(long long n);

@@ -3,6 +3,7 @@
 //   sweep(children of level k  +  shadow rays of level k-1)  ->  spawn(level k)
 // then shade from the deepest level up and resolve to RGB.
 #include <algorithm>
+#include <chrono>
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
@@ -13,6 +14,20 @@
 #include "api_internal.h"
 
 namespace rt {
+
+// RT_B200_TRACE: wall-clock laps of the host side of a call
+struct HostLap {
+    const char *call;
+    bool on;
+    std::chrono::steady_clock::time_point t;
+    explicit HostLap(const char *c) : call(c), on(std::getenv("RT_B200_TRACE") != nullptr), t(std::chrono::steady_clock::now()) {}
+    void operator()(const char *what) {
+        if (!on) return;
+        auto n = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[rt_b200] %s: %-20s %.3f ms\n", call, what, std::chrono::duration<double, std::milli>(n - t).count());
+        t = n;
+    }
+};
 
 // ---- workspace --------------------------------------------------------------------------
 
@@ -54,6 +69,7 @@ void Workspace::release() {
     cudaFree(batch_counters); batch_counters = nullptr;
     cudaFree(out_f32); cudaFree(out_u8);
     out_f32 = out_u8 = nullptr; out_f32_cap = out_u8_cap = 0;
+    cudaFree(tables); tables = nullptr; tables_cap = 0;
 }
 
 // ---- per-device cache of one released workspace --------------------------------------------
@@ -478,12 +494,15 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
     int rc = check_params(scene, cam, pr);
     if (rc != RT_OK) return rc;
     CK(cudaSetDevice(scene->device), "cudaSetDevice");
+    HostLap lap("render");
     if ((rc = prepare_camera_table(scene, cam->origin)) != RT_OK) return rc;
+    lap("camera table");
     Workspace &ws = scene->ws;
     if ((rc = ws.ensure_misc()) != RT_OK) return rc;
     cudaStream_t st = scene->stream;
     std::vector<int> rows;
     if ((rc = upload_rows(scene, ws, cam, pr, rows)) != RT_OK) return rc;
+    lap("rows");
     const long long n_pixels = (long long)rows.size() * cam->x_res;
     const long long n_samples = n_pixels * pr->spp;
     FrameParams fp = frame_params(cam, pr, ws.rows, (int)rows.size());
@@ -522,6 +541,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
     CK(cudaMemcpyAsync(ws.h_counters + N_COUNTERS, ws.exact_counter, N_SWEEP_COUNTERS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st), "exact readback");
     CK(cudaStreamSynchronize(st), "render");
     CK(cudaGetLastError(), "render");
+    lap("device work");
     acc.audit = (pr->flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
     if (!acc.audit) read_sweep_counters(ws, acc);
     if (stats) {
@@ -596,8 +616,10 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *
     out.d_f32 = rgb_f32 ? (float *)ws.out_f32 : nullptr;
     out.d_u8 = rgb_u8 ? (unsigned char *)ws.out_u8 : nullptr;
     if ((rc = render_impl(scene, camera, params, out, stats)) != RT_OK) return rc;
+    HostLap lap("render");
     if (rgb_f32 && n_ch) CK(cudaMemcpy(rgb_f32, ws.out_f32, n_ch * sizeof(float), cudaMemcpyDeviceToHost), "D2H rgb_f32");
     if (rgb_u8 && n_ch) CK(cudaMemcpy(rgb_u8, ws.out_u8, n_ch, cudaMemcpyDeviceToHost), "D2H rgb_u8");
+    lap("copy to the host");
     return RT_OK;
 }
 

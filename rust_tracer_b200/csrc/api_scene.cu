@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include "api_internal.h"
@@ -27,6 +28,45 @@ int fail(int code, const char *fmt, ...) {
 
 int cuda_fail(cudaError_t e, const char *what) {
     return fail(RT_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+// ---- host-side data parallelism ----------------------------------------------------------
+// The scene build walks a few thousand to a few hundred thousand records several times
+// (slot order, group spheres, one re-centred table per light and per camera position); with a
+// 50 ms frame behind it that is worth a handful of threads.  RT_B200_HOST_THREADS overrides.
+constexpr int MAX_HOST_CHUNKS = 8;
+
+static int host_threads() {
+    static const int n = [] {
+        int want = 4;
+        if (const char *e = std::getenv("RT_B200_HOST_THREADS")) want = std::atoi(e);
+        const int hw = (int)std::thread::hardware_concurrency();
+        if (hw > 0) want = std::min(want, hw);
+        return std::max(1, std::min(want, MAX_HOST_CHUNKS));
+    }();
+    return n;
+}
+
+// fn(chunk, begin, end) over [0, n) in at most host_threads() chunks of at least min_chunk.
+template <typename F> static void parallel_chunks(size_t n, size_t min_chunk, F &&fn) {
+    size_t nt = std::min<size_t>((size_t)host_threads(), n / std::max<size_t>(min_chunk, 1));
+    if (nt <= 1) {
+        fn(0, (size_t)0, n);
+        return;
+    }
+    const size_t step = (n + nt - 1) / nt;
+    std::vector<std::thread> th;
+    size_t started = 1;
+    try {
+        for (size_t t = 1; t < nt; ++t) {
+            th.emplace_back([&fn, t, step, n] { fn((int)t, std::min(n, t * step), std::min(n, (t + 1) * step)); });
+            ++started;
+        }
+    } catch (...) { // no more threads to be had: the rest runs here
+    }
+    fn(0, (size_t)0, std::min(n, step));
+    for (auto &x : th) x.join();
+    for (size_t t = started; t < nt; ++t) fn((int)t, std::min(n, t * step), std::min(n, (t + 1) * step));
 }
 
 // ---- bounding spheres (host, double precision) ------------------------------------------
@@ -194,9 +234,7 @@ static bool origin_tables_wanted(int n_slots) {
 
 void build_origin_table(const rt_scene *scene, const float o[3], std::vector<float4> &out, OriginTable *tab, bool toward) {
     struct S { float x, y, z, w; };
-    double rmax = 0.0;
-    bool clip = toward;
-    auto one = [&](const HostSlot &h) {
+    auto one = [&](const HostSlot &h, double &rmax, bool &clip) {
         if (h.kind == 1) return S{0.f, 0.f, 0.f, 3.402823466e+38f};
         if (h.kind == 0) {
             double x = (double)h.cx - o[0], y = (double)h.cy - o[1], z = (double)h.cz - o[2];
@@ -215,15 +253,28 @@ void build_origin_table(const rt_scene *scene, const float o[3], std::vector<flo
     // slots, then groups, then quads (each paired); rmax (the far clip of slot tests) is the slots' alone
     const size_t ns = scene->slots.size(), ng = scene->groups.size(), nq = scene->quads.size();
     out.resize(ns + ng + nq);
-    auto fill = [&](const std::vector<HostSlot> &v, float4 *dst) {
-        for (size_t j = 0; j + 1 < v.size(); j += 2) {
-            S a = one(v[j]), b = one(v[j + 1]);
-            dst[j] = make_float4(a.x, b.x, a.y, b.y);
-            dst[j + 1] = make_float4(a.z, b.z, a.w, b.w);
-        }
+    bool clip = toward;
+    auto fill = [&](const std::vector<HostSlot> &v, float4 *dst) { // returns the largest radius
+        double rm[MAX_HOST_CHUNKS] = {0.0};
+        bool cl[MAX_HOST_CHUNKS];
+        for (bool &c : cl) c = true;
+        parallel_chunks(v.size() / 2, 1024, [&](int chunk, size_t begin, size_t end) {
+            double r = 0.0;
+            bool c = true;
+            for (size_t q = begin; q < end; ++q) {
+                const size_t j = 2 * q;
+                S a = one(v[j], r, c), b = one(v[j + 1], r, c);
+                dst[j] = make_float4(a.x, b.x, a.y, b.y);
+                dst[j + 1] = make_float4(a.z, b.z, a.w, b.w);
+            }
+            rm[chunk] = r;
+            cl[chunk] = c;
+        });
+        double r = 0.0;
+        for (int c = 0; c < MAX_HOST_CHUNKS; ++c) { r = std::max(r, rm[c]); clip = clip && cl[c]; }
+        return r;
     };
-    fill(scene->slots, out.data());
-    const double rmax_slots = rmax;
+    const double rmax_slots = fill(scene->slots, out.data());
     fill(scene->groups, out.data() + ns);
     fill(scene->quads, out.data() + ns + ng);
     double on = std::sqrt((double)o[0] * o[0] + (double)o[1] * o[1] + (double)o[2] * o[2]);
@@ -250,18 +301,52 @@ int prepare_camera_table(rt_scene *scene, const float origin[3]) {
     return RT_OK;
 }
 
-template <typename T> static int upload(rt_scene *s, const std::vector<T> &host, const T **dev) {
-    *dev = nullptr;
-    if (host.empty()) return RT_OK;
-    void *d = nullptr;
-    cudaError_t e = cudaMalloc(&d, host.size() * sizeof(T));
-    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(scene table)");
-    s->allocs.push_back(d);
-    e = cudaMemcpy(d, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(scene table)");
-    *dev = (const T *)d;
-    return RT_OK;
-}
+// All device tables of a scene live in ONE allocation, filled by one batch of copies: a scene of
+// 10k shapes has 13 tables + one per light, and a cudaMalloc + blocking cudaMemcpy each would
+// cost more than the copies themselves.
+struct Arena {
+    struct Item { const void *src; size_t bytes, off; const void **dev; };
+    std::vector<Item> items;
+    size_t total = 0;
+    void add_raw(const void *src, size_t bytes, const void **dev) {
+        *dev = nullptr;
+        if (bytes == 0) return;
+        items.push_back({src, bytes, total, dev});
+        total += (bytes + 255) & ~(size_t)255;
+    }
+    template <typename T> void add(const std::vector<T> &host, const T **dev) {
+        add_raw(host.data(), host.size() * sizeof(T), (const void **)dev);
+    }
+    // src == nullptr: space only.  The block belongs to the scene's workspace, which outlives the scene
+    // in the per-device cache: create -> render -> destroy in a loop allocates nothing.
+    int commit(rt_scene *s, cudaStream_t st) {
+        if (total == 0) return RT_OK;
+        Workspace &ws = s->ws;
+        if (ws.tables_cap < total) {
+            cudaFree(ws.tables);
+            ws.tables = nullptr; ws.tables_cap = 0;
+            const size_t cap = total + total / 4;
+            cudaError_t e = cudaMalloc(&ws.tables, cap);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                ws.tables = nullptr;
+                return fail(e == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA, "cudaMalloc(scene tables, %zu bytes): %s", cap,
+                            cudaGetErrorString(e));
+            }
+            ws.tables_cap = cap;
+        }
+        void *d = ws.tables;
+        cudaError_t e;
+        for (const Item &it : items) {
+            *it.dev = (const char *)d + it.off;
+            if (!it.src) continue;
+            e = cudaMemcpyAsync((char *)d + it.off, it.src, it.bytes, cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(scene table)");
+        }
+        if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return cuda_fail(e, "scene table upload");
+        return RT_OK;
+    }
+};
 
 static int convert_colorfn(const rt_colorfn &in, DevColorFn &out) {
     if (in.kind != RT_COLOR_CONST && in.kind != RT_COLOR_CHECKERBOARD)
@@ -458,11 +543,10 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
             while (j < bounds.size() && bounds[j].cls == bounds[i].cls) ++j;
             i = j;
         }
-        while (!work.empty()) {
-            auto [lo, hi] = work.back();
-            work.pop_back();
+        // one median split of [lo, hi) at a whole number of groups; false when it is a single leaf
+        auto split = [&](int lo, int hi, int &mid) {
             const int n = hi - lo;
-            if (n <= GROUP_SLOTS) continue;
+            if (n <= GROUP_SLOTS) return false;
             float mn[3] = {3.4e38f, 3.4e38f, 3.4e38f}, mx[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
             for (int i = lo; i < hi; ++i)
                 for (int ax = 0; ax < 3; ++ax) { mn[ax] = std::min(mn[ax], coord(bounds[i], ax)); mx[ax] = std::max(mx[ax], coord(bounds[i], ax)); }
@@ -472,9 +556,36 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
             const int groups = (n + GROUP_SLOTS - 1) / GROUP_SLOTS, left = (groups / 2) * GROUP_SLOTS;
             std::nth_element(bounds.begin() + lo, bounds.begin() + lo + left, bounds.begin() + hi,
                              [&](const B &a, const B &b) { return coord(a, ax) < coord(b, ax); });
-            work.push_back({lo, lo + left});
-            work.push_back({lo + left, hi});
+            mid = lo + left;
+            return true;
+        };
+        // the top of the tree here, until there is a subtree per host thread; the subtrees (disjoint ranges) in parallel
+        const size_t want = (size_t)host_threads();
+        std::vector<std::pair<int, int>> roots;
+        size_t head = 0;
+        while (head < work.size() && (work.size() - head) + roots.size() < want) { // breadth first: subtrees of like size
+            auto [lo, hi] = work[head++];
+            int mid;
+            if (hi - lo >= 4096 && split(lo, hi, mid)) {
+                work.push_back({lo, mid});
+                work.push_back({mid, hi});
+            } else {
+                roots.push_back({lo, hi});
+            }
         }
+        roots.insert(roots.end(), work.begin() + head, work.end());
+        std::sort(roots.begin(), roots.end(), [](const std::pair<int, int> &a, const std::pair<int, int> &b) { return a.second - a.first > b.second - b.first; });
+        parallel_chunks(roots.size(), 1, [&](int, size_t begin, size_t end) {
+            std::vector<std::pair<int, int>> stack(roots.begin() + begin, roots.begin() + end);
+            while (!stack.empty()) {
+                auto [lo, hi] = stack.back();
+                stack.pop_back();
+                int mid;
+                if (!split(lo, hi, mid)) continue;
+                stack.push_back({lo, mid});
+                stack.push_back({mid, hi});
+            }
+        });
     }
     lap("slot order");
     const int nb = (int)bounds.size();
@@ -503,9 +614,17 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     const int n_slots = (int)slots.size();
     const int n_groups = n_slots / GROUP_SLOTS; // even: SEG_PAD is two groups
     std::vector<Bound> groups(n_groups);
-    for (int g = 0; g < n_groups; ++g) {
-        groups[g] = make_group(&slots[(size_t)g * GROUP_SLOTS], &bound_shape[(size_t)g * GROUP_SLOTS], GROUP_SLOTS, 16.0);
-        cmax = std::max(cmax, groups[g].reach); // a group sphere may reach beyond its members
+    {
+        double reach[MAX_HOST_CHUNKS] = {0.0};
+        parallel_chunks((size_t)n_groups, 64, [&](int chunk, size_t begin, size_t end) {
+            double r = 0.0;
+            for (size_t g = begin; g < end; ++g) {
+                groups[g] = make_group(&slots[g * GROUP_SLOTS], &bound_shape[g * GROUP_SLOTS], GROUP_SLOTS, 16.0);
+                r = std::max(r, groups[g].reach);
+            }
+            reach[chunk] = r;
+        });
+        for (double r : reach) cmax = std::max(cmax, r); // a group sphere may reach beyond its members
     }
     const int per_quad = QUAD_SLOTS / GROUP_SLOTS, n_quads = n_groups / per_quad; // even: SEG_PAD is two quads
     std::vector<Bound> quads(n_quads);
@@ -580,59 +699,54 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
     d.n_lights = desc->n_lights; d.n_point_lights = n_point; d.first_nan_shape = first_nan;
     d.amb_r = desc->ambient[0]; d.amb_g = desc->ambient[1]; d.amb_b = desc->ambient[2];
-    const DevMaterial *dm = nullptr;
-    if ((rc = upload(s, bound, &d.bound)) != RT_OK || (rc = upload(s, group, &d.group)) != RT_OK ||
-        (rc = upload(s, quad, &d.quad)) != RT_OK ||
-        (rc = upload(s, bound_shape, &d.bound_shape)) != RT_OK || (rc = upload(s, slot_meta, &d.slot_meta)) != RT_OK ||
-        (rc = upload(s, slot_geom, &d.slot_geom)) != RT_OK ||
-        (rc = upload(s, meta, &d.shape_meta)) != RT_OK || (rc = upload(s, geom, &d.geom)) != RT_OK ||
-        (rc = upload(s, plane_shape, &d.plane_shape)) != RT_OK || (rc = upload(s, plane_data, &d.plane_data)) != RT_OK ||
-        (rc = upload(s, ctris, &d.cube_tris)) != RT_OK || (rc = upload(s, mats, &dm)) != RT_OK ||
-        (rc = upload(s, lights, &d.lights)) != RT_OK) {
-        rt_scene_destroy(s);
-        return rc;
-    }
-    lap("uploads");
-    d.materials = dm;
-    s->d_materials = const_cast<DevMaterial *>(dm);
     if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         rt_scene_destroy(s);
         return cuda_fail(e, "cudaStreamCreate");
     }
     s->own_stream = s->stream;
     lap("stream");
+    const DevMaterial *dm = nullptr;
+    Arena arena;
+    arena.add(bound, &d.bound); arena.add(group, &d.group); arena.add(quad, &d.quad);
+    arena.add(bound_shape, &d.bound_shape); arena.add(slot_meta, &d.slot_meta); arena.add(slot_geom, &d.slot_geom);
+    arena.add(meta, &d.shape_meta); arena.add(geom, &d.geom);
+    arena.add(plane_shape, &d.plane_shape); arena.add(plane_data, &d.plane_data);
+    arena.add(ctris, &d.cube_tris); arena.add(mats, &dm); arena.add(lights, &d.lights);
+    // the bound table seen from every point light, and room for the one seen from the camera
+    std::vector<std::vector<float4>> light_host(n_point);
+    const float4 *cam_tab = nullptr;
     if (origin_tables_wanted(n_slots)) {
         auto host_slot = [](const Bound &b) {
             return HostSlot{b.cx, b.cy, b.cz, b.rf, b.w == 3.402823466e+38f ? 1 : (b.w == -3.402823466e+38f ? 2 : 0)};
         };
+        s->slots.reserve(slots.size()); s->groups.reserve(groups.size()); s->quads.reserve(quads.size());
         for (const Bound &b : slots) s->slots.push_back(host_slot(b));
         for (const Bound &b : groups) s->groups.push_back(host_slot(b));
         for (const Bound &b : quads) s->quads.push_back(host_slot(b));
         s->light_tabs.resize(n_point);
-        std::vector<float4> host;
         for (int l = 0; l < desc->n_lights; ++l) {
             if (lights[l].point_index < 0) continue;
             const float o[3] = {lights[l].px, lights[l].py, lights[l].pz};
             OriginTable &t = s->light_tabs[lights[l].point_index];
-            build_origin_table(s, o, host, &t, true);
-            if ((rc = upload(s, host, &t.bound)) != RT_OK) {
-                rt_scene_destroy(s);
-                return rc;
-            }
-            t.group = t.bound + n_slots;
-            t.quad = t.group + n_groups;
+            build_origin_table(s, o, light_host[lights[l].point_index], &t, true);
+            arena.add(light_host[lights[l].point_index], &t.bound);
         }
-        void *ct = nullptr;
-        if ((e = cudaMalloc(&ct, (size_t)(n_slots + n_groups + n_quads) * sizeof(float4))) != cudaSuccess) {
-            rt_scene_destroy(s);
-            return cuda_fail(e, "cudaMalloc(camera table)");
-        }
-        s->allocs.push_back(ct);
-        s->cam_tab = (float4 *)ct;
+        arena.add_raw(nullptr, (size_t)(n_slots + n_groups + n_quads) * sizeof(float4), (const void **)&cam_tab);
     }
     lap("light tables");
     s->ws = workspace_take_cached(device);
-    lap("workspace");
+    if ((rc = arena.commit(s, s->stream)) != RT_OK) {
+        rt_scene_destroy(s);
+        return rc;
+    }
+    d.materials = dm;
+    s->d_materials = const_cast<DevMaterial *>(dm);
+    for (OriginTable &t : s->light_tabs) {
+        t.group = t.bound + n_slots;
+        t.quad = t.group + n_groups;
+    }
+    s->cam_tab = const_cast<float4 *>(cam_tab);
+    lap("uploads");
     *out = s;
     return RT_OK;
 }

@@ -10,7 +10,7 @@ for rep in range(3):
     if rep == 2:
         os.environ["RT_B200_TRACE"] = "1"
     t0 = time.perf_counter(); sc = rt.Scene(desc); t1 = time.perf_counter()
-    os.environ.pop("RT_B200_TRACE", None)
     st = sc.render(3840, 2160, 5, want_f32=False, out_u8=buf.numpy())[2]; t2 = time.perf_counter()
+    os.environ.pop("RT_B200_TRACE", None)
     sc.close(); t3 = time.perf_counter()
     print("create %.2f ms  render (host RGB8) %.2f ms (device %.2f)  destroy %.2f ms" % ((t1-t0)*1e3, (t2-t1)*1e3, st["total_ms"], (t3-t2)*1e3))
