@@ -60,6 +60,8 @@ def _declare(lib):
                                       P(P(abi.rt_scene_desc))]
     lib.rt_scene_desc_free.argtypes = [P(abi.rt_scene_desc)]
     lib.rt_scene_desc_free.restype = None
+    lib.rt_scene_desc_save.argtypes = [P(abi.rt_scene_desc), C.c_char_p]
+    lib.rt_scene_desc_load.argtypes = [C.c_char_p, P(P(abi.rt_scene_desc))]
     lib.rt_matrix_inverse.argtypes = [P(C.c_float), P(C.c_float)]
     lib.rt_matrix_compose.argtypes = [C.c_float] * 9 + [P(C.c_float)]
     lib.rt_matrix_compose.restype = None
@@ -76,7 +78,8 @@ EXPORTS = [
     "rt_frame_alloc", "rt_frame_export", "rt_frame_import", "rt_frame_release", "rt_frame_signal", "rt_frame_wait",
     "rt_forest_build", "rt_forest_eval", "rt_forest_eval_filtered", "rt_forest_get_stats", "rt_forest_size",
     "rt_forest_trees_with", "rt_forest_destroy", "rt_measure_fp32_peak",
-    "rt_builtin_scene", "rt_synthetic_scene", "rt_scene_desc_free", "rt_matrix_inverse", "rt_matrix_compose",
+    "rt_builtin_scene", "rt_synthetic_scene", "rt_scene_desc_free", "rt_scene_desc_save", "rt_scene_desc_load",
+    "rt_matrix_inverse", "rt_matrix_compose",
     "rt_plane_axes", "rt_triangle_normal",
 ]
 

@@ -38,6 +38,17 @@ class SceneDesc:
         return cls(p, builtin=True)
 
     @classmethod
+    def load(cls, path):
+        """Read a scene description file (rt_scene_desc_load, include/rt_b200_host.h)."""
+        p = C.POINTER(abi.rt_scene_desc)()
+        check(lib().rt_scene_desc_load(str(path).encode(), C.byref(p)))
+        return cls(p, builtin=True)
+
+    def save(self, path):
+        """Write this description as a scene file (rt_scene_desc_save)."""
+        check(lib().rt_scene_desc_save(self._ptr, str(path).encode()))
+
+    @classmethod
     def from_arrays(cls, shapes, materials, lights, ambient):
         """shapes/materials/lights: ctypes arrays of rt_shape / rt_material / rt_light."""
         d = abi.rt_scene_desc()

@@ -103,12 +103,6 @@ void synthetic_scene(Scene &scene, int n_spheres, int n_triangles, uint64_t seed
     scene.set_ambient(Color(0.1f, 0.1f, 0.1f));
 }
 
-// a heap FlatScene whose first member is reachable from the rt_scene_desc pointer
-struct OwnedDesc {
-    rt_scene_desc desc; // must stay first
-    FlatScene flat;
-};
-
 int export_scene(const Scene &scene, rt_scene_desc **out) {
     OwnedDesc *o = new (std::nothrow) OwnedDesc();
     if (!o) return RT_ERR_NOMEM;

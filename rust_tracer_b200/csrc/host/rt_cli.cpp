@@ -4,8 +4,11 @@
 // the render itself happens in librt_b200.so on the GPU (no CPU fallback).
 //
 //   rt_cli [-w W] [-h H] [-d DEPTH] [--method basic|rayforest] [--stats] [-t] [-i]
-//          [--scene default|s1k|m10k] [--seed N] [--spp 1|4] [--out FILE] [--device N]
+//          [--scene default|s1k|m10k] [--scene-file FILE] [--dump-scene FILE] [--seed N]
+//          [--spp 1|4] [--out FILE] [--device N]
 //          [bench [-n RUNS] [-f]]
+// --scene-file renders a scene description file (include/rt_b200_host.h) instead of a built-in
+// scene; --dump-scene writes the chosen scene as such a file and exits (no GPU needed).
 // --gui needs a display server (src/gui.rs, GTK): unavailable here, it is rejected.
 // The flags after --stats have no counterpart in the reference (its scene is compiled in).
 #include <sys/stat.h>
@@ -89,7 +92,7 @@ struct Config {
     int runs = 10;                             // cli.rs:93
     bool filter_mode = false;
     // extensions
-    std::string scene = "default", out;
+    std::string scene = "default", scene_file, dump_scene, out;
     uint64_t seed = 0;
     int spp = 1, device = 0;
 };
@@ -134,6 +137,8 @@ Config parse_args(int argc, char **argv) {
         else if (a == "--stats") c.print_forest_stats = true;
         else if (a == "-g" || a == "--gui") c.gui = true;
         else if (a == "--scene") c.scene = value(i);
+        else if (a == "--scene-file") c.scene_file = value(i);
+        else if (a == "--dump-scene") c.dump_scene = value(i);
         else if (a == "--seed") c.seed = (uint64_t)parse_int(value(i), "seed");
         else if (a == "--spp") c.spp = (int)parse_int(value(i), "spp");
         else if (a == "--out") c.out = value(i);
@@ -255,7 +260,15 @@ int main(int argc, char **argv) {
 
     std::printf("Create Scene\n");
     rt_scene_desc *desc = nullptr;
-    CHECK(rt_builtin_scene(c.scene.c_str(), 0, &desc));
+    if (!c.scene_file.empty()) CHECK(rt_scene_desc_load(c.scene_file.c_str(), &desc));
+    else if (rt_builtin_scene(c.scene.c_str(), 0, &desc) != RT_OK) die("unknown scene: " + c.scene);
+    if (!c.dump_scene.empty()) { // host only: no device is touched
+        CHECK(rt_scene_desc_save(desc, c.dump_scene.c_str()));
+        std::printf("Wrote scene description: %s (%d shapes, %d materials, %d lights)\n", c.dump_scene.c_str(), desc->n_shapes,
+                    desc->n_materials, desc->n_lights);
+        rt_scene_desc_free(desc);
+        return 0;
+    }
     rt_scene *scene = nullptr;
     CHECK(rt_scene_create(desc, c.device, &scene));
     std::printf("Done Creating Scene\n");

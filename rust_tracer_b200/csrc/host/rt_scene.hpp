@@ -249,6 +249,13 @@ struct FlatScene {
     }
 };
 
+// A heap FlatScene whose first member is reachable from the rt_scene_desc pointer: what
+// rt_builtin_scene / rt_synthetic_scene / rt_scene_desc_load hand out and rt_scene_desc_free takes.
+struct OwnedDesc {
+    rt_scene_desc desc; // must stay first
+    FlatScene flat;
+};
+
 class Scene { // src/scene/mod.rs:22-85
   public:
     void add_shape(std::unique_ptr<Renderable> shape) { // id = index (mod.rs:40-44)

@@ -78,3 +78,17 @@ def test_cli_bench_filter_reports_trees_with_the_blue_sphere():
     assert "Forest Size: 3072" in r.stdout and "Trees Evaluated:" in r.stdout and "Avg Per Op:" in r.stdout
     r = run("-w", "64", "-h", "48", "-d", "4", "bench", "-n", "2")
     assert r.returncode == 0 and r.stdout.count("render_scene:") == 2
+
+
+@pytest.mark.gpu
+def test_cli_renders_a_scene_file(tmp_path):
+    """--scene-file: the committed fixture of the default scene gives the default scene's image."""
+    import orc
+    from rust_tracer_b200 import abi
+    w, h, d = 80, 60, 4
+    out = str(tmp_path / "f.png")
+    r = run("-w", str(w), "-h", str(h), "-d", str(d), "--scene-file", os.path.join(HERE, "golden", "default.rtscene"),
+            "--out", out)
+    assert r.returncode == 0, r.stderr
+    _, ou, _ = orc.render(orc.default_scene().desc, abi.default_camera(w, h), d)
+    assert (read_png_rgb8(out) == ou).all()

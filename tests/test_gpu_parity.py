@@ -307,3 +307,19 @@ def test_frame_signal_words():
         assert bool((px == 9).all())
     finally:
         L.rt_frame_release(0, ptr, 0)
+
+
+def test_scene_loaded_from_a_file_renders_the_same_frame(tmp_path):
+    """Scene description file (rt_scene_desc_save / _load): a scene that went
+    through the file is the same scene to the device, byte for byte, and matches the oracle
+    rendering the loaded description."""
+    desc = rt.SceneDesc.synthetic(120, 120, 11, 0.04, 0.12)
+    path = tmp_path / "s.rtscene"
+    desc.save(path)
+    back = rt.SceneDesc.load(path)
+    f0, u0, st0 = gpu_render(desc, 160, 90, 4)
+    f1, u1, st1 = gpu_render(back, 160, 90, 4)
+    assert (u0 == u1).all() and np.array_equal(f0, f1, equal_nan=True) and st0["rays"] == st1["rays"]
+    _, ou, oc = orc.render(back.desc, abi.default_camera(160, 90), 4)
+    assert_parity(u1, ou, "scene file")
+    assert st1["rays"] == oc.rays
