@@ -308,6 +308,8 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     // (one column of the [node][light] pool) against that light's; the rest as one general sweep.
     const bool by_origin = !audit && !scene->light_tabs.empty() && scene->cam.bound;
     const int npl = std::max(sc.n_point_lights, 1);
+    const bool merge_lights = env_int("RT_B200_MERGE_LIGHTS", 1, 0, 1) != 0;
+    const int heavy_allow = env_int("RT_B200_HEAVY_ALLOW", 65536, 0, 1 << 24);
     // heavy_tree / heavy_nodes: how many of the level's first tree rays / of the previous level's
     // first nodes start far outside the scene (counters[4], [5]); their sweeps get finer work items
     auto sweep_level = [&](int level, int tb, int te, int sb, int se, int heavy_tree, int heavy_nodes) {
@@ -340,9 +342,31 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         sweep_on(tree, none, level == 0 ? scene->cam : general, stream_for(), !fork);
         rays += tree.n;
         if (se > sb) {
-            for (int l = 0; l < sc.n_point_lights; ++l) {
+            auto light_seg = [&](int l) {
                 RaySeg sh{p.s_a + sb + l, p.s_b + sb + l, p.s_key + sb + l, (se - sb) / npl, npl, 1};
                 sh.heavy = std::min(heavy_nodes, sh.n);
+                return sh;
+            };
+            // every light's shadow rays in one launch (a light has 1 / L of the CTAs and L times the
+            // ray batches per warp: small levels need not cut the table into slices to fill the GPU)
+            bool merged = false;
+            if (fork && merge_lights && sc.n_point_lights >= 2) {
+                std::vector<RaySeg> segs;
+                for (int l = 0; l < sc.n_point_lights; ++l) segs.push_back(light_seg(l));
+                int used = 0;
+                cudaError_t e = launch_sweep_jobs(sc, segs.data(), scene->light_tabs.data(), sc.n_point_lights, rpt, scene->sm_count,
+                                                  ws.batch_counters + ws.batch_next, BATCH_COUNTERS - ws.batch_next, &used,
+                                                  ws.exact_counter, stream_for());
+                if (e == cudaSuccess) {
+                    merged = true;
+                    ws.batch_next += used;
+                    scene->launches += 1;
+                    for (const RaySeg &sh : segs) rays += sh.n;
+                } else if (e != cudaErrorNotSupported && sweep_err == cudaSuccess) sweep_err = e;
+                else --next_aux; // nothing was launched on that stream
+            }
+            for (int l = 0; !merged && l < sc.n_point_lights; ++l) {
+                RaySeg sh = light_seg(l);
                 sweep_on(sh, none, scene->light_tabs[l], stream_for(), !fork);
                 rays += sh.n;
             }
@@ -379,7 +403,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         // far nodes come first in the node order, and their children (allocated as spawn runs
         // through that order) early in the next level: allow for the blocks in flight
         heavy_nodes = by_origin ? (int)ws.h_counters[4] : 0;
-        heavy_tree = (by_origin && ws.h_counters[5]) ? (int)std::min<long long>(2ll * ws.h_counters[5] + 65536, te - tb) : 0;
+        heavy_tree = (by_origin && ws.h_counters[5]) ? (int)std::min<long long>(2ll * ws.h_counters[5] + heavy_allow, te - tb) : 0;
         if (tb == te && sb == se) break; // nothing left to cast
     }
     sweep_level(-1, 0, 0, sb, se, 0, heavy_nodes); // shadows of the last level

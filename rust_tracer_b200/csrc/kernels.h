@@ -48,6 +48,14 @@ struct OriginTable {
 cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable origin, int rays_per_thread, int sm_count,
                          unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
                          cudaStream_t stream);
+// Several sweeps against origin tables in ONE launch (the shadow rays of every light of a
+// wavefront level): job j = rays segs[j] (keys preset to KEY_MISS) against tabs[j]; CTA b serves job
+// b % n_jobs.  Consumes n_jobs batch counters.  cudaErrorNotSupported (nothing launched) when the
+// case does not fit -- fewer than 2 or more than 8 jobs, a table too large to stay resident --
+// and the caller falls back to one launch_sweep per job.
+cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int rays_per_thread,
+                              int sm_count, unsigned int *batch_counters, int n_counters, int *used,
+                              unsigned long long *exact_counter, cudaStream_t stream);
 // FMA per (ray, bound) pair of the two filters (for the executed-flop count)
 constexpr int FILTER_FMA_GENERAL = 7, FILTER_FMA_ORIGIN = 4;
 // Same result, every (ray, shape) pair through the exact test in shape order (audit).

@@ -130,6 +130,21 @@ struct SweepCtx {
     const float4 *cube_tris;
 };
 
+// One ray set of a JOBS launch (sweep_kernel) with its origin table, work counter and item shapes.
+struct SweepJob {
+    RaySeg s0;
+    OriginTable ot;
+    unsigned int *batch_counter;
+    int n_slices, slice_slots, merge;
+    int heavy_batches, heavy_slices, heavy_slice_slots;
+    int reg_batches, tail_slices, tail_slice_slots;
+};
+constexpr int MAX_SWEEP_JOBS = 8;
+struct SweepJobs {
+    SweepJob j[MAX_SWEEP_JOBS];
+    int n;
+};
+
 // Run queued pairs 32 at a time, one exact test per lane; a partial batch stays queued unless
 // `all`.  Called by a converged warp.  Returns the number of pairs left in the queue.
 __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueue, unsigned long long *wbest, int ray0,
@@ -236,19 +251,44 @@ RT_DEV float2 f2(float x) { return make_float2(x, x); }
 // memory for the whole launch.  A work item is (batch of 32 R rays) x (slice of the resident
 // slots); each WARP fetches its own items from batch_counter, so no block barrier follows the
 // table load, and small launches still spread over every warp of the GPU (n_slices > 1).
+// Items come in three runs: the batches of the first s0.heavy rays (heavy_slices slices each), the
+// bulk (reg_batches batches, n_slices each), and the last batches of the launch cut finer
+// (tail_slices each) so that the warps run out of work at about the same time.
 // `merge`: keys are folded into global memory with atomicMin (they were initialised to
 // KEY_MISS or hold the result of earlier table chunks) instead of stored; `planes`: this
 // launch also tests the planes (slice 0 does).
 // ORIGIN: the table is `ot` (all rays pass through its point), filter of 4 FMA per pair.
-template <int R, int SWEEP_THREADS, bool ORIGIN>
+//
+// JOBS: one launch sweeps several independent ray sets, each against its own origin table (the
+// shadow rays of every light of one wavefront level): CTA b works on job b % jobs.n only -- its
+// rays, table, work counter and item shapes come from jobs.j[] (copied to shared memory) instead
+// of the parameters of the same name, which are unused.  A level's L small launches, each
+// needing its table cut into slices to occupy every warp of the GPU, become one launch in which
+// a light has 1/L of the CTAs and L times the batches per warp.
+template <int R, int SWEEP_THREADS, bool ORIGIN, bool JOBS>
 __global__ void __launch_bounds__(SWEEP_THREADS, 1)
-sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, int slot_end, int n_slices, int slice_slots,
-             int merge, int planes, int item_max, int heavy_batches, int heavy_slices, int heavy_slice_slots,
-             unsigned int *batch_counter, unsigned long long *exact_counter) {
+sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin, int slot_end, int n_slices_, int slice_slots_,
+             int merge_, int planes, int item_max, int heavy_batches_, int heavy_slices_, int heavy_slice_slots_,
+             int reg_batches_, int tail_slices_, int tail_slice_slots_,
+             unsigned int *batch_counter_, unsigned long long *exact_counter, const __grid_constant__ SweepJobs jobs) {
     constexpr int SWEEP_WARPS = SWEEP_THREADS / 32;
     constexpr unsigned int FULL = 0xffffffffu;
     extern __shared__ float4 smem[];
     __shared__ SweepCtx ctx;
+    __shared__ SweepJob job;
+    if constexpr (JOBS) {
+        if (threadIdx.x == 0) job = jobs.j[blockIdx.x % (unsigned int)jobs.n];
+        __syncthreads();
+    }
+    const RaySeg &s0 = JOBS ? job.s0 : s0_;
+    const OriginTable &ot = JOBS ? job.ot : ot_;
+    const int n_slices = JOBS ? job.n_slices : n_slices_, slice_slots = JOBS ? job.slice_slots : slice_slots_;
+    const int merge = JOBS ? job.merge : merge_;
+    const int heavy_batches = JOBS ? job.heavy_batches : heavy_batches_, heavy_slices = JOBS ? job.heavy_slices : heavy_slices_;
+    const int heavy_slice_slots = JOBS ? job.heavy_slice_slots : heavy_slice_slots_;
+    const int reg_batches = JOBS ? job.reg_batches : reg_batches_, tail_slices = JOBS ? job.tail_slices : tail_slices_;
+    const int tail_slice_slots = JOBS ? job.tail_slice_slots : tail_slice_slots_;
+    unsigned int *const batch_counter = JOBS ? job.batch_counter : batch_counter_;
     __shared__ unsigned int n_exact[SWEEP_WARPS];
     __shared__ unsigned long long n_iters[SWEEP_WARPS], n_slot[SWEEP_WARPS];
     const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS, n_qtab = n_tab / QUAD_SLOTS;
@@ -296,11 +336,19 @@ sweep_kernel(DevScene sc, RaySeg s0, RaySeg s1, OriginTable ot, int slot_begin, 
             slice = (int)(item - batch * (unsigned int)heavy_slices);
             ss = heavy_slice_slots;
         } else {
-            const unsigned int li = item - heavy_items;
-            batch = li / (unsigned int)n_slices;
-            slice = (int)(li - batch * (unsigned int)n_slices);
-            batch += (unsigned int)heavy_batches;
-            ss = slice_slots;
+            const unsigned int li = item - heavy_items, reg_items = (unsigned int)reg_batches * (unsigned int)n_slices;
+            if (li < reg_items) {
+                batch = li / (unsigned int)n_slices;
+                slice = (int)(li - batch * (unsigned int)n_slices);
+                batch += (unsigned int)heavy_batches;
+                ss = slice_slots;
+            } else { // the last batches of the launch, cut finer: the launch ends on short items
+                const unsigned int lt = li - reg_items;
+                batch = lt / (unsigned int)tail_slices;
+                slice = (int)(lt - batch * (unsigned int)tail_slices);
+                batch += (unsigned int)heavy_batches + (unsigned int)reg_batches;
+                ss = tail_slice_slots;
+            }
         }
         const long long ray0_ll = (long long)batch * (R * 32);
         if (ray0_ll >= total) break;
@@ -560,6 +608,83 @@ template <int R, int T> static int sweep_table_cap() {
            SEG_PAD * SEG_PAD;
 }
 
+// How the rays of one sweep are cut into work items (ray batches x table slices), for `warps`
+// persistent warps and a resident table of `per` slots.
+struct ItemPlan {
+    int n_slices = 1, slice_slots = SEG_PAD, merge = 0;
+    long long heavy_batches = 0;
+    int heavy_slices = 1, heavy_slice_slots = SEG_PAD;
+    long long reg_batches = 0; // batches after the heavy ones cut into n_slices; the rest into tail_slices
+    int tail_slices = 1, tail_slice_slots = SEG_PAD;
+    long long items = 0;
+};
+
+static int sweep_env(const char *name, int dflt, int lo, int hi) {
+    const char *e = std::getenv(name);
+    if (!e) return dflt;
+    const int v = std::atoi(e);
+    return v < lo || v > hi ? dflt : v;
+}
+
+template <int R>
+static ItemPlan plan_items(long long total, int heavy, int per, long long warps, int n_chunks) {
+    ItemPlan pl;
+    const long long batches = (total + 32ll * R - 1) / (32ll * R);
+    // Work items = ray batches x table slices.  A launch with few rays is cut into slices of
+    // the table so that every warp of the GPU still gets several items; the batches of the
+    // first `heavy` rays (origins far outside the scene: filter margins so wide that they
+    // pass most of the table on to the exact test) are cut as finely as the table allows, since
+    // one of them whole can take longer than the rest of the launch.
+    auto slicing = [&](long long want, long long n_batches, int *slots) {
+        int n = (int)std::min<long long>((want + n_batches - 1) / std::max<long long>(n_batches, 1), std::max(1, per / MIN_SLICE_SLOTS));
+        n = std::max(n, 1);
+        *slots = std::max(SEG_PAD, ((per + n - 1) / n + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
+        return std::max(1, (per + *slots - 1) / *slots);
+    };
+    pl.heavy_batches = std::min<long long>(batches, ((long long)std::max(heavy, 0) + 32ll * R - 1) / (32ll * R));
+    long long want_light = 4ll * warps, want_heavy = 48ll * warps; // measured: RT_B200_WANT
+    if (const char *e = std::getenv("RT_B200_WANT")) want_light = std::max(1, std::atoi(e)) * warps;
+    pl.n_slices = slicing(want_light, batches - pl.heavy_batches, &pl.slice_slots);
+    if (const char *e = std::getenv("RT_B200_SLICES")) {
+        pl.n_slices = std::max(1, std::min(std::atoi(e), std::max(1, per / SEG_PAD)));
+        pl.slice_slots = std::max(SEG_PAD, ((per + pl.n_slices - 1) / pl.n_slices + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
+        pl.n_slices = std::max(1, (per + pl.slice_slots - 1) / pl.slice_slots);
+    }
+    if (pl.heavy_batches > 0) {
+        pl.heavy_slices = slicing(want_heavy, pl.heavy_batches, &pl.heavy_slice_slots);
+        if (pl.heavy_slices < pl.n_slices) { pl.heavy_slices = pl.n_slices; pl.heavy_slice_slots = pl.slice_slots; }
+    }
+    // A warp's last item ends, on average, half an item before the launch does.  The last
+    // 15 % of the batches (at most 2 per warp) are therefore cut 4 times finer (measured: RT_B200_TAIL_PCT, _MULT).
+    const long long regular = batches - pl.heavy_batches;
+    const int tail_pct = sweep_env("RT_B200_TAIL_PCT", 15, 0, 100), tail_mult = sweep_env("RT_B200_TAIL_MULT", 4, 1, 64);
+    long long tail_batches = std::min<long long>(regular * tail_pct / 100, 2 * warps);
+    pl.tail_slices = pl.n_slices; pl.tail_slice_slots = pl.slice_slots;
+    if (tail_batches > 0 && tail_mult > 1) {
+        const int n = std::min(pl.n_slices * tail_mult, std::max(1, per / MIN_SLICE_SLOTS));
+        pl.tail_slice_slots = std::max(SEG_PAD, ((per + n - 1) / n + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
+        pl.tail_slices = std::max(1, (per + pl.tail_slice_slots - 1) / pl.tail_slice_slots);
+    }
+    if (pl.tail_slices <= pl.n_slices) { tail_batches = 0; pl.tail_slices = pl.n_slices; pl.tail_slice_slots = pl.slice_slots; }
+    pl.reg_batches = regular - tail_batches;
+    pl.merge = (pl.n_slices > 1 || n_chunks > 1 || (pl.heavy_batches > 0 && pl.heavy_slices > 1) || tail_batches > 0) ? 1 : 0;
+    pl.items = pl.heavy_batches * pl.heavy_slices + pl.reg_batches * pl.n_slices + tail_batches * pl.tail_slices;
+    return pl;
+}
+
+// lanes of a warp with a ray touching a group up to which the group is swept (ray, group)
+// pair by pair (lane = slot) rather than all 32 R rays against all its slots: about where the
+// two cost the same
+static int sweep_item_max() {
+    int item_max = 16;
+    if (const char *e = std::getenv("RT_B200_ITEM_MAX")) item_max = std::atoi(e);
+    return item_max;
+}
+
+template <int R, int T> static size_t sweep_smem_bytes(int slots) {
+    return (size_t)(slots + slots / GROUP_SLOTS + slots / QUAD_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T>();
+}
+
 template <int R, int T, bool ORIGIN>
 static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, long long total, int sm_count,
                                   unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
@@ -572,42 +697,10 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
     }
     const int n_chunks = std::max(1, (sc.n_slots + cap - 1) / cap);
     if (n_chunks > n_counters) return cudaErrorInvalidValue;
-    // lanes of a warp with a ray touching a group up to which the group is swept (ray, group)
-    // pair by pair (lane = slot) rather than all 32 R rays against all its slots: about where the
-    // two cost the same
-    int item_max = 16;
-    if (const char *e = std::getenv("RT_B200_ITEM_MAX")) item_max = std::atoi(e);
     // chunks of equal size (rounded to SEG_PAD) rather than cap, cap, ..., rest
     const int per = ((sc.n_slots + n_chunks - 1) / n_chunks + SEG_PAD - 1) / SEG_PAD * SEG_PAD;
-    const long long batches = (total + 32ll * R - 1) / (32ll * R);
-    // Work items = ray batches x table slices.  A launch with few rays is cut into slices of
-    // the table so that every warp of the GPU still gets several items; the batches of the
-    // first s0.heavy rays (origins far outside the scene: filter margins so wide that they
-    // pass most of the table on to the exact test) are cut as finely as the table allows, since
-    // one of them whole can take longer than the rest of the launch.
-    auto slicing = [&](long long want, long long n_batches, int *slots) {
-        int n = (int)std::min<long long>((want + n_batches - 1) / std::max<long long>(n_batches, 1), std::max(1, per / MIN_SLICE_SLOTS));
-        n = std::max(n, 1);
-        *slots = std::max(SEG_PAD, ((per + n - 1) / n + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
-        return std::max(1, (per + *slots - 1) / *slots);
-    };
-    const long long heavy_batches = std::min<long long>(batches, ((long long)std::max(s0.heavy, 0) + 32ll * R - 1) / (32ll * R));
-    long long want_light = 4ll * sm_count * SWEEP_WARPS, want_heavy = 48ll * sm_count * SWEEP_WARPS; // measured: RT_B200_WANT
-    if (const char *e = std::getenv("RT_B200_WANT")) want_light = std::max(1, std::atoi(e)) * (long long)sm_count * SWEEP_WARPS;
-    int slice_slots = SEG_PAD, heavy_slice_slots = SEG_PAD;
-    int n_slices = slicing(want_light, batches - heavy_batches, &slice_slots);
-    if (const char *e = std::getenv("RT_B200_SLICES")) {
-        n_slices = std::max(1, std::min(std::atoi(e), std::max(1, per / SEG_PAD)));
-        slice_slots = std::max(SEG_PAD, ((per + n_slices - 1) / n_slices + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
-        n_slices = std::max(1, (per + slice_slots - 1) / slice_slots);
-    }
-    int heavy_slices = 1;
-    if (heavy_batches > 0) {
-        heavy_slices = slicing(want_heavy, heavy_batches, &heavy_slice_slots);
-        if (heavy_slices < n_slices) { heavy_slices = n_slices; heavy_slice_slots = slice_slots; }
-    }
-    const int merge = (n_slices > 1 || n_chunks > 1 || (heavy_batches > 0 && heavy_slices > 1)) ? 1 : 0;
-    if (merge) { // every item folds its keys in with atomicMin: start from "no hit"
+    const ItemPlan pl = plan_items<R>(total, s0.heavy, per, (long long)sm_count * SWEEP_WARPS, n_chunks);
+    if (pl.merge) { // every item folds its keys in with atomicMin: start from "no hit"
         cudaError_t err = cudaSuccess;
         if (s0.n > 0 && !s0.preset) {
             if (s0.stride != 1) return cudaErrorInvalidValue; // the caller presets the keys of a strided segment
@@ -616,20 +709,78 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
         if (err == cudaSuccess && s1.n > 0) err = cudaMemsetAsync(s1.key, 0xFF, sizeof(unsigned long long) * (size_t)s1.n, stream);
         if (err != cudaSuccess) return err;
     }
-    const long long items = heavy_batches * heavy_slices + (batches - heavy_batches) * n_slices;
-    unsigned int grid = (unsigned int)std::min<long long>((items + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)sm_count);
+    unsigned int grid = (unsigned int)std::min<long long>((pl.items + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)sm_count);
+    static const SweepJobs no_jobs{};
     for (int c = 0; c < n_chunks; ++c) {
         int b = c * per, e = std::min(sc.n_slots, b + per);
-        const size_t smem = (size_t)((e - b) + (e - b) / GROUP_SLOTS + (e - b) / QUAD_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T>();
-        cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        const size_t smem = sweep_smem_bytes<R, T>(e - b);
+        cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
-        sweep_kernel<R, T, ORIGIN><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, n_slices, slice_slots, merge,
-                                                              c == n_chunks - 1 ? 1 : 0, item_max, (int)heavy_batches, heavy_slices,
-                                                              heavy_slice_slots, batch_counters + c, exact_counter);
+        sweep_kernel<R, T, ORIGIN, false><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, pl.n_slices, pl.slice_slots, pl.merge,
+                                                                     c == n_chunks - 1 ? 1 : 0, sweep_item_max(), (int)pl.heavy_batches,
+                                                                     pl.heavy_slices, pl.heavy_slice_slots, (int)pl.reg_batches,
+                                                                     pl.tail_slices, pl.tail_slice_slots, batch_counters + c,
+                                                                     exact_counter, no_jobs);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
     }
     *used = n_chunks;
     return cudaSuccess;
+}
+
+// Rays per thread of a launch: fewer only when even table slicing cannot occupy the warps.
+static int pick_rays_per_thread(int wanted, long long total, int n_slots, int sm_count) {
+    if (wanted > 0) return wanted;
+    const long long want = 2ll * sm_count * 16;
+    const long long max_slices = std::max(1, n_slots / MIN_SLICE_SLOTS);
+    int r = 4;
+    while (r > 1 && ((total + 32ll * r - 1) / (32ll * r)) * max_slices < want) r >>= 1;
+    return r;
+}
+
+template <int R, int T>
+static cudaError_t launch_sweep_jobs_r(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int sm_count,
+                                       unsigned int *batch_counters, unsigned long long *exact_counter, cudaStream_t stream) {
+    constexpr int SWEEP_WARPS = T / 32;
+    SweepJobs jobs{};
+    jobs.n = n_jobs;
+    const unsigned int grid = (unsigned int)sm_count;
+    for (int j = 0; j < n_jobs; ++j) {
+        const long long ctas = (sm_count - j + n_jobs - 1) / n_jobs; // CTAs b with b % n_jobs == j
+        const ItemPlan pl = plan_items<R>(segs[j].n, segs[j].heavy, sc.n_slots, ctas * SWEEP_WARPS, 1);
+        SweepJob &J = jobs.j[j];
+        J.s0 = segs[j]; J.ot = tabs[j]; J.batch_counter = batch_counters + j;
+        J.n_slices = pl.n_slices; J.slice_slots = pl.slice_slots; J.merge = pl.merge;
+        J.heavy_batches = (int)pl.heavy_batches; J.heavy_slices = pl.heavy_slices; J.heavy_slice_slots = pl.heavy_slice_slots;
+        J.reg_batches = (int)pl.reg_batches; J.tail_slices = pl.tail_slices; J.tail_slice_slots = pl.tail_slice_slots;
+    }
+    const size_t smem = sweep_smem_bytes<R, T>(sc.n_slots);
+    cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    const RaySeg none{nullptr, nullptr, nullptr, 0};
+    sweep_kernel<R, T, true, true><<<grid, T, smem, stream>>>(sc, none, none, OriginTable{}, 0, sc.n_slots, 1, SEG_PAD, 0, 1, sweep_item_max(),
+                                                              0, 1, SEG_PAD, 0, 1, SEG_PAD, nullptr, exact_counter, jobs);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int rays_per_thread,
+                              int sm_count, unsigned int *batch_counters, int n_counters, int *used,
+                              unsigned long long *exact_counter, cudaStream_t stream) {
+    *used = 0;
+    if (n_jobs < 2 || n_jobs > MAX_SWEEP_JOBS || n_jobs > n_counters || sm_count < n_jobs) return cudaErrorNotSupported;
+    if (sc.n_slots > sweep_table_cap<4, 512>() || std::getenv("RT_B200_TABLE_CAP")) return cudaErrorNotSupported; // one resident table only
+    long long most = 0;
+    for (int j = 0; j < n_jobs; ++j) {
+        // keys are folded in with atomicMin when a job's items are table slices: the caller presets them
+        if (!tabs[j].bound || segs[j].n <= 0 || !segs[j].preset) return cudaErrorNotSupported;
+        most = std::max<long long>(most, segs[j].n);
+    }
+    const int r = pick_rays_per_thread(rays_per_thread, most, sc.n_slots, std::max(1, sm_count / n_jobs));
+    cudaError_t err;
+    if (r >= 4) err = launch_sweep_jobs_r<4, 512>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream);
+    else if (r >= 2) err = launch_sweep_jobs_r<2, 512>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream);
+    else err = launch_sweep_jobs_r<1, 512>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream);
+    if (err == cudaSuccess) *used = n_jobs;
+    return err;
 }
 
 cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, int rays_per_thread, int sm_count,
@@ -640,13 +791,7 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
     if (total <= 0) return cudaSuccess;
     if (ot.bound && s1.n > 0) return cudaErrorInvalidValue;
     if (sm_count < 1) sm_count = 1;
-    int r = rays_per_thread;
-    if (r <= 0) { // fewer rays per thread only when even table slicing cannot occupy the warps
-        const long long want = 2ll * sm_count * 16;
-        const long long max_slices = std::max(1, sc.n_slots / MIN_SLICE_SLOTS);
-        r = 4;
-        while (r > 1 && ((total + 32ll * r - 1) / (32ll * r)) * max_slices < want) r >>= 1;
-    }
+    const int r = pick_rays_per_thread(rays_per_thread, total, sc.n_slots, sm_count);
 #define RT_SWEEP(R_, T_, O_) \
     launch_sweep_r<R_, T_, O_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
     if (ot.bound) {

@@ -111,33 +111,50 @@ __global__ void __launch_bounds__(256) node_bin_kernel(DevScene sc, Pools p, int
 }
 
 // One block: exclusive scan of bins[0 .. NODE_BINS] in place; counters[1] = end of the level's shadow rays.
+// Warp w owns the SCAN_PER_WARP consecutive bins from w * SCAN_PER_WARP: it loads them in
+// coalesced rounds of 32 (all loads in flight at once), scans round by round with a running
+// carry, and the block meets once to exchange the warps' totals.
+constexpr int SCAN_ROUNDS = (NODE_BINS + 1 + 1023) / 1024; // 32-bin rounds per warp
+constexpr int SCAN_PER_WARP = 32 * SCAN_ROUNDS;
 __global__ void __launch_bounds__(1024) node_scan_kernel(Pools p, int s_begin, int n_point_lights) {
     __shared__ unsigned int warp_sum[32];
-    __shared__ unsigned int carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) carry = 0;
-    __syncthreads();
-    for (int base = 0; base < NODE_BINS + 1; base += 1024) {
-        int j = base + tid;
-        unsigned int v = j < NODE_BINS + 1 ? p.bins[j] : 0u, x = v;
+    const int base = warp * SCAN_PER_WARP + lane;
+    unsigned int v[SCAN_ROUNDS], x[SCAN_ROUNDS];
+#pragma unroll
+    for (int k = 0; k < SCAN_ROUNDS; ++k) {
+        const int j = base + 32 * k;
+        v[k] = j < NODE_BINS + 1 ? p.bins[j] : 0u;
+    }
+    unsigned int carry = 0; // sum of this warp's bins before round k
+#pragma unroll
+    for (int k = 0; k < SCAN_ROUNDS; ++k) {
+        unsigned int t = v[k];
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            unsigned int y = __shfl_up_sync(0xffffffffu, x, o);
-            if (lane >= o) x += y;
+            unsigned int y = __shfl_up_sync(0xffffffffu, t, o);
+            if (lane >= o) t += y;
         }
-        if (lane == 31) warp_sum[warp] = x;
-        __syncthreads();
-        if (warp == 0) {
-            unsigned int w = warp_sum[lane], z = w;
+        x[k] = carry + t - v[k]; // exclusive within the warp's run
+        carry += __shfl_sync(0xffffffffu, t, 31);
+    }
+    if (lane == 0) warp_sum[warp] = carry;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned int w = warp_sum[lane], z = w;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                unsigned int y = __shfl_up_sync(0xffffffffu, z, o);
-                if (lane >= o) z += y;
-            }
-            warp_sum[lane] = z - w; // exclusive
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned int y = __shfl_up_sync(0xffffffffu, z, o);
+            if (lane >= o) z += y;
         }
-        __syncthreads();
-        unsigned int excl = carry + warp_sum[warp] + x - v;
+        warp_sum[lane] = z - w; // exclusive
+    }
+    __syncthreads();
+    const unsigned int before = warp_sum[warp];
+#pragma unroll
+    for (int k = 0; k < SCAN_ROUNDS; ++k) {
+        const int j = base + 32 * k;
+        const unsigned int excl = before + x[k];
         if (j < NODE_BINS + 1) p.bins[j] = excl;
         if (j == NODE_FAR_BINS) { // excl = number of hits outside the box
             p.counters[4] = excl;
@@ -148,9 +165,6 @@ __global__ void __launch_bounds__(1024) node_scan_kernel(Pools p, int s_begin, i
             if (s_end > (unsigned long long)p.s_cap) p.counters[3] = 1u;
             else p.counters[1] = (unsigned int)s_end;
         }
-        __syncthreads();
-        if (tid == 1023) carry = excl + v;
-        __syncthreads();
     }
 }
 
