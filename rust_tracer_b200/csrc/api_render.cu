@@ -339,6 +339,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         }
         int next_aux = 0;
         auto stream_for = [&]() { return fork ? scene->aux[next_aux++ % n_aux] : st; };
+        // tree rays first: measured against shadows first (c4: 51.4 vs 52.0 ms)
         sweep_on(tree, none, level == 0 ? scene->cam : general, stream_for(), !fork);
         rays += tree.n;
         if (se > sb) {

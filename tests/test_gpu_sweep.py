@@ -292,3 +292,55 @@ def test_tested_pairs_counter():
     assert b[2]["tested_pairs"] == b[2]["rays"] * n_shapes
     assert 0 < a[2]["tested_pairs"] < 0.5 * a[2]["rays"] * n_shapes
     assert a[2]["tested_pairs"] >= a[2]["plane_tests"]
+
+
+def test_merged_light_sweeps_and_tail_items_do_not_change_the_image(monkeypatch):
+    """One launch for every light's shadow rays (launch_sweep_jobs: CTA b serves light b % L) against
+    one launch per light (RT_B200_MERGE_LIGHTS=0), and the finer work items at the end of a launch
+    (RT_B200_TAIL_PCT, RT_B200_TAIL_MULT): scheduling only -- same keys, so the same image and counts,
+    and the same as the all-pairs audit.  Also at fewer rays per thread, where the jobs kernel is
+    another instantiation."""
+    desc = rt.SceneDesc.synthetic(500, 500, 77, 0.03, 0.1)
+    w, h, depth = 224, 126, 4
+    ref = None
+    for env in ({}, {"RT_B200_MERGE_LIGHTS": "0"}, {"RT_B200_TAIL_PCT": "0"}, {"RT_B200_TAIL_PCT": "100", "RT_B200_TAIL_MULT": "8"},
+                {"RT_B200_TAIL_PCT": "50", "RT_B200_TAIL_MULT": "64"}, {"RT_B200_RAYS_PER_THREAD": "1"},
+                {"RT_B200_RAYS_PER_THREAD": "2", "RT_B200_WANT": "16"}):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        sc = rt.Scene(desc)
+        try:
+            out = sc.render(w, h, depth)
+            if ref is None:
+                ref = out
+                _assert_same(ref, sc.render(w, h, depth, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS))
+        finally:
+            sc.close()
+        for k in env:
+            monkeypatch.delenv(k)
+        _assert_same(ref, out)
+    assert ref[2]["kernel_launches"] > 0
+
+
+@pytest.mark.parametrize("n_lights", [1, 2, 5, 8, 9])
+def test_any_number_of_point_lights(n_lights):
+    """1 light: nothing to merge; 2..8: one jobs launch per level (8 = MAX_SWEEP_JOBS); 9: more lights
+    than a jobs launch takes, back to one launch per light.  Against the oracle and the audit."""
+    base = rt.SceneDesc.synthetic(150, 150, 5, 0.05, 0.14)
+    d = base.desc
+    lights = (abi.rt_light * n_lights)()
+    rng = np.random.default_rng(n_lights)
+    for i in range(n_lights):
+        lights[i].kind = abi.RT_LIGHT_POINT
+        lights[i].pos[:] = [float(rng.uniform(-5, 5)), float(rng.uniform(2, 8)), float(rng.uniform(-7, 2))]
+        lights[i].color[:] = [float(x) for x in rng.uniform(0.1, 0.5, 3)]
+    shapes = (abi.rt_shape * d.n_shapes)(*[d.shapes[i] for i in range(d.n_shapes)])
+    mats = (abi.rt_material * d.n_materials)(*[d.materials[i] for i in range(d.n_materials)])
+    desc = rt.SceneDesc.from_arrays(shapes, mats, lights, (0.1, 0.1, 0.1))
+    w, h, depth = 128, 72, 4
+    a, b = _render_pair(desc, w, h, depth)
+    _assert_same(a, b)
+    _, ou, oc = orc.render(desc.desc, abi.default_camera(w, h), depth)
+    diff = np.abs(a[1].astype(np.int32) - ou.astype(np.int32)).max(axis=-1)
+    assert float((diff <= 1).mean()) >= 0.999, int(diff.max())
+    assert a[2]["rays"] == oc.rays and a[2]["shadow_rays"] == oc.shadow_rays
