@@ -89,6 +89,8 @@ struct rt_forest {
     rt::Workspace ws;   // owns the pools of the kept ray trees
     rt::FrameParams fp{};
     std::vector<int> tb, te; // tree-ray range of each level
+    std::vector<int> sb, se; // shadow-ray range of each level
+    bool light_major = false; // layout of a level's shadow rays (api_render.cu: BandLevels)
     int total_tree_rays = 0;
     int n_samples = 0;       // = trees = pixels (spp is 1 in forest mode)
     int width = 0, n_rows = 0;

@@ -210,6 +210,7 @@ struct EventPool {
 struct BandLevels {
     std::vector<int> tb, te; // tree-ray range of level k
     std::vector<int> sb, se; // shadow-ray range of level k
+    bool light_major = false; // shadow rays of a level laid out [light][node] (ordered spawn), else [node][light]
     unsigned long long nodes = 0;
 };
 
@@ -259,6 +260,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     const bool audit = (flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
     const bool trace = std::getenv("RT_B200_TRACE") != nullptr;
     lv = BandLevels();
+    lv.light_major = !audit && !scene->light_tabs.empty() && scene->cam.bound; // = by_origin below: spawn runs ordered
 
     unsigned int init[N_COUNTERS] = {(unsigned int)n, 0u, 0u, 0u, 0u, 0u};
     CK(cudaMemcpyAsync(p.counters, init, sizeof(init), cudaMemcpyHostToDevice, st), "counters init");
@@ -344,7 +346,8 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         rays += tree.n;
         if (se > sb) {
             auto light_seg = [&](int l) {
-                RaySeg sh{p.s_a + sb + l, p.s_b + sb + l, p.s_key + sb + l, (se - sb) / npl, npl, 1};
+                const int per_light = (se - sb) / npl; // [light][node]: light l's rays are one contiguous run
+                RaySeg sh{p.s_a + sb + l * per_light, p.s_b + sb + l * per_light, p.s_key + sb + l * per_light, per_light, 1, 1};
                 sh.heavy = std::min(heavy_nodes, sh.n);
                 return sh;
             };
@@ -418,7 +421,9 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
 static int shade_band(rt_scene *scene, const DevScene &sc, Workspace &ws, const FrameParams &fp, const BandLevels &lv,
                       const unsigned char *sample_mask) {
     for (int k = (int)lv.tb.size() - 1; k >= 0; --k) {
-        launch_shade(sc, fp, ws.pools, lv.tb[k], lv.te[k], k, ws.sample_rgb, sample_mask, scene->stream);
+        const int npl = std::max(sc.n_point_lights, 1);
+        launch_shade(sc, fp, ws.pools, lv.tb[k], lv.te[k], k, lv.light_major ? (lv.se[k] - lv.sb[k]) / npl : 1, ws.sample_rgb,
+                     sample_mask, scene->stream);
         if (lv.te[k] > lv.tb[k]) scene->launches += 1;
     }
     CK(cudaGetLastError(), "shade launch");
@@ -701,6 +706,9 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
     }
     f->tb = lv.tb;
     f->te = lv.te;
+    f->sb = lv.sb;
+    f->se = lv.se;
+    f->light_major = lv.light_major;
     f->total_tree_rays = lv.te.empty() ? 0 : lv.te.back();
     if (stats) {
         acc.tree_rays = (unsigned long long)f->total_tree_rays;
@@ -780,6 +788,9 @@ static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *i
     BandLevels lv;
     lv.tb = f->tb;
     lv.te = f->te;
+    lv.sb = f->sb;
+    lv.se = f->se;
+    lv.light_major = f->light_major;
     if ((rc = shade_band(scene, sc, ws, f->fp, lv, mask)) != RT_OK) return rc;
     size_t n_ch = (size_t)n * 3;
     float *d_f32 = nullptr;

@@ -9,8 +9,8 @@ namespace rt {
 
 // A run of n rays: a[i * stride] = (ox, oy, oz, dx), b[i * stride] = (dy, dz, -, -);
 // key[i * stride] receives the nearest hit (exact.cuh: make_key) or KEY_MISS.  stride > 1
-// picks the shadow rays of one light out of the [node][light] shadow pool; only the first
-// segment of a sweep may be strided.
+// picks the rays of one light out of a [node][light] pool (the ordered wavefront lays shadow rays
+// out [light][node] and needs none); only the first segment of a sweep may be strided.
 struct RaySeg {
     const float4 *a;
     const float4 *b;
@@ -80,7 +80,7 @@ struct Pools {
     int *t_order;
     unsigned int *bins;           // NODE_BINS + 2 words
     // shadow rays
-    float4 *s_a, *s_b;
+    float4 *s_a, *s_b;            // per level: [light][node] (ordered spawn) or [node][light]
     unsigned long long *s_key;
     int s_cap;
     // device counters: [0] tree rays allocated, [1] shadow rays allocated, [2] nodes, [3] overflow flag,
@@ -112,14 +112,17 @@ void launch_raygen(const FrameParams &fp, const Pools &p, long long sample0, int
 // spawn_children) its reflect / refract children.
 // ordered: first sort the level's nodes by the cell of their hit point (p.t_order, p.bins), so
 // that consecutive nodes -- and with them consecutive shadow rays of each light and consecutive
-// child rays -- are neighbours in space; node number r of the level then owns shadow rays
-// [s_begin + r L, s_begin + (r + 1) L) and counters[1] = s_begin + hits L.  Not ordered: shadow
-// blocks are handed out by atomicAdd on counters[1] (which must hold s_begin).
+// child rays -- are neighbours in space; the level's shadow rays are then laid out light by
+// light: node number r owns ray s_begin + l hits + r of light l, and counters[1] = s_begin +
+// hits L.  Not ordered: [node][light] blocks are handed out by atomicAdd on counters[1] (which
+// must hold s_begin).
 void launch_spawn(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int spawn_children,
                   int ordered, int s_begin, cudaStream_t stream);
 // Level k, deepest first: colour of every node in [begin, end) -> parent slot, or
 // sample_rgb[sample - sample0] at level 0.
-void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level,
+// light_stride: the shadow ray of point light l of a node is s_key[t_sbase + l * light_stride] -- the
+// level's node count where spawn ran ordered ([light][node] layout), 1 otherwise ([node][light]).
+void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level, int light_stride,
                   float4 *sample_rgb, const unsigned char *sample_mask, cudaStream_t stream);
 // Average spp samples per pixel (ordered sum * 0.25), write f32 and/or quantised u8.  Pixel
 // pixel0 + i of the rendered rows goes to position pixel0 + i of the output, or, with frame_rows

@@ -214,17 +214,29 @@ spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn
 
         // shadow rays: p = point + 0.0002 * normal (render.rs:147); one per point light
         if (sc.n_point_lights > 0) {
-            unsigned long long sb = ordered ? (unsigned long long)s_begin + (unsigned long long)rank * (unsigned int)sc.n_point_lights
-                                            : (unsigned long long)atomicAdd(&p.counters[1], (unsigned int)sc.n_point_lights);
-            if (sb + (unsigned int)sc.n_point_lights <= (unsigned long long)p.s_cap) {
+            // ordered: the level's shadow rays are laid out light by light, [light][node]: node number
+            // `rank` owns ray s_begin + light * hits + rank (hits = the level's nodes, from node_scan_kernel
+            // through counters[1]), so each light's rays are one contiguous, coalesced run for its sweep.
+            // Not ordered: [node][light] blocks handed out by atomicAdd.
+            unsigned long long sb, lstride = 1;
+            bool fits;
+            if (ordered) {
+                fits = p.counters[3] == 0u; // node_scan_kernel checked the level's end against s_cap
+                lstride = (p.counters[1] - (unsigned int)s_begin) / (unsigned int)sc.n_point_lights;
+                sb = (unsigned long long)s_begin + (unsigned long long)rank;
+            } else {
+                sb = (unsigned long long)atomicAdd(&p.counters[1], (unsigned int)sc.n_point_lights);
+                fits = sb + (unsigned int)sc.n_point_lights <= (unsigned long long)p.s_cap;
+            }
+            if (fits) {
                 p.t_sbase[i] = (int)sb;
                 V3 sp = vadd(h.point, vscale(h.normal, 0.0002f));
                 for (int l = 0; l < sc.n_lights; ++l) {
                     DevLight L = sc.lights[l];
                     if (L.kind != 0) continue;
                     V3 ldir = vnorm(vsub(v3(L.px, L.py, L.pz), sp)); // scene/mod.rs:191
-                    p.s_a[sb + L.point_index] = make_float4(sp.x, sp.y, sp.z, ldir.x);
-                    p.s_b[sb + L.point_index] = make_float4(ldir.y, ldir.z, 0.f, 0.f);
+                    p.s_a[sb + L.point_index * lstride] = make_float4(sp.x, sp.y, sp.z, ldir.x);
+                    p.s_b[sb + L.point_index * lstride] = make_float4(ldir.y, ldir.z, 0.f, 0.f);
                 }
             } else {
                 p.counters[3] = 1u;
@@ -292,7 +304,7 @@ spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn
 }
 
 __global__ void __launch_bounds__(WF_BLOCK)
-shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level, float4 *sample_rgb,
+shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level, int light_stride, float4 *sample_rgb,
              const unsigned char *sample_mask) {
     int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
@@ -318,7 +330,7 @@ shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level
             if (L.kind == 0) { // PointLight::get_energy (scene/mod.rs:189-206)
                 V3 lpos = v3(L.px, L.py, L.pz);
                 ldir = vnorm(vsub(lpos, sp));
-                unsigned long long sk = p.s_key[sb + L.point_index];
+                unsigned long long sk = p.s_key[sb + (long long)L.point_index * light_stride];
                 if (sk != KEY_MISS) {
                     V3 hp = ray_at(sp, ldir, key_t(sk));
                     if (vlen2(vsub(hp, sp)) < vlen2(vsub(lpos, sp))) energy = v3(0.f, 0.f, 0.f);
@@ -434,10 +446,10 @@ void launch_spawn(const DevScene &sc, const FrameParams &fp, const Pools &p, int
     }
     spawn_kernel<<<nblk(end - begin, SPAWN_BLOCK), SPAWN_BLOCK, 0, stream>>>(sc, fp, p, begin, end, spawn_children, ordered, s_begin);
 }
-void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level,
+void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int begin, int end, int level, int light_stride,
                   float4 *sample_rgb, const unsigned char *sample_mask, cudaStream_t stream) {
     if (end > begin)
-        shade_kernel<<<nblk(end - begin, WF_BLOCK), WF_BLOCK, 0, stream>>>(sc, fp, p, begin, end, level, sample_rgb,
+        shade_kernel<<<nblk(end - begin, WF_BLOCK), WF_BLOCK, 0, stream>>>(sc, fp, p, begin, end, level, light_stride, sample_rgb,
                                                                           sample_mask);
 }
 void launch_resolve(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp, float *rgb_f32,

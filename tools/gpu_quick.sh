@@ -14,5 +14,10 @@ if [ $rc -eq 0 ]; then
   timeout 150 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
       python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1; echo "ncu list rc=$?"
 fi
+if [ $rc -eq 0 ] && [ "${FULL:-0}" = "1" ]; then
+  # one full capture of the dominant kernel: the level-1 tree sweep (general filter) and the level-0 shadow sweep (all lights, one launch)
+  timeout 240 ncu --set full --clock-control none --import-source on -k regex:sweep_kernel -s 1 -c 2 -f -o gpurun_out/sweep_full \
+      python bench.py --steps 1 --warmup 0 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
+fi
 timeout 60 python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/bench_ref.json 2>&1; echo "bench ref rc=$?"; cat gpurun_out/bench_ref.json
 ls -la gpurun_out
