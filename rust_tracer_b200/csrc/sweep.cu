@@ -418,8 +418,12 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 quads_hit = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
                 evals_hier += 2 * R;
             }
-            for (int gp = 0; gp < 2 * QUAD_SLOTS / (2 * GROUP_SLOTS); ++gp) { // the 4 pairs of groups of the two quads
-                if (!((quads_hit >> (gp >> 1)) & 1u)) continue;
+            // most quad pairs are touched by no ray of the warp: leave before the group loop is set up
+            // (its control flow for skipped quads was 12 % of the instructions executed)
+            if (!quads_hit) continue;
+            constexpr int GP_PER_QUAD = QUAD_SLOTS / (2 * GROUP_SLOTS); // pairs of groups in a quad
+            const int gp_begin = (quads_hit & 1u) ? 0 : GP_PER_QUAD, gp_end = (quads_hit & 2u) ? 2 * GP_PER_QUAD : GP_PER_QUAD;
+            for (int gp = gp_begin; gp < gp_end; ++gp) { // the pairs of groups of the touched quads
                 const int j0 = jq + gp * 2 * GROUP_SLOTS;
                 // which of the two groups can any ray of this warp touch?
                 unsigned int ball0, ball1, pm = 0;
