@@ -34,6 +34,12 @@
 // are swept against the tables re-centred on O' (kernels.h: OriginTable): with C' = C - O',
 //     dist^2(C, line) <= R^2   <=>   (C'.dh)^2  >=  |C'|^2 - R^2 =: W'
 // one 3-FMA chain and one FMA that squares it and adds the per-ray margin: 4 FMA per pair.
+//
+// Scheduling (host side, plan_items / launch_sweep / launch_sweep_jobs): a launch's rays are cut
+// into work items = (batch of 32 R rays) x (slice of the resident table) handed out by an atomic
+// counter -- finer for the first, expensive batches and for the last 15 % of the launch -- and the
+// shadow rays of all lights of a wavefront level go into ONE launch whose CTAs each serve one
+// light's rays and origin table (JOBS).
 #include <algorithm>
 #include <cfloat>
 #include <cstdlib>
