@@ -112,6 +112,21 @@ def oracle_rate(desc, wl, seconds, threads):
     return c.rays / dt / 1e6, sample, int(c.rays), dt
 
 
+def oracle_one_thread(desc, wl):
+    """The oracle on one thread over the middle row of the frame: (Mrays/s, description)."""
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import orc
+    from rust_tracer_b200 import abi
+
+    cam = abi.default_camera(wl["width"], wl["height"])
+    rows = np.array([wl["height"] // 2], dtype=np.int32)
+    t0 = time.perf_counter()
+    _, _, c = orc.render(desc.desc, cam, wl["depth"], rows=rows, spp=wl["spp"], seed=1, threads=1, want_f32=False)
+    dt = max(time.perf_counter() - t0, 1e-6)
+    return c.rays / dt / 1e6, "row %d of the %dx%d frame (%d rays, %.1f s)" % (rows[0], wl["width"], wl["height"], c.rays, dt)
+
+
 _REAL_STDOUT = None
 
 
@@ -366,6 +381,10 @@ def run_ours(args, wl):
         threads = os.cpu_count() or 1
         v, sample, _, _ = oracle_rate(desc, wl, args.cpu_seconds, threads)
         cpu = {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample}
+        # the reference itself is single-threaded (Rc<RefCell<..>> everywhere, src/render.rs:31-38): the same
+        # port on ONE thread, on one row of the frame (SURVEY 8d asks for both figures)
+        v1, sample1 = oracle_one_thread(desc, wl)
+        cpu["one_thread"] = {"value": v1, "unit": "Mrays/s", "cores": 1, "sample": sample1}
 
     emit({
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
