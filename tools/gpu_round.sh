@@ -1,7 +1,8 @@
 #!/bin/bash
 # One gpurun call: GPU tests, smoke, the bench lines, then (each only after its own command
 # exited 0 without ncu) the ncu launch list of the same bench command and one full capture of
-# the dominant kernel.  Outputs land in gpurun_out/.
+# the dominant kernel (launches 1 and 2 of the sweep: the level-1 tree sweep and the level-0 shadow sweep of all lights).
+# Outputs land in gpurun_out/.  tools/gpu_quick.sh is the short version (c4 only; FULL=1 adds the capture).
 set -u
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
@@ -18,7 +19,7 @@ if [ $rc -eq 0 ]; then
   python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/plain_for_ncu.log 2>&1 &&
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
       python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1; echo "ncu list rc=$?"
-  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:sweep_kernel -s 3 -c 2 -f -o gpurun_out/sweep_full \
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:sweep_kernel -s 1 -c 2 -f -o gpurun_out/sweep_full \
       python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 fi
 ls -la gpurun_out
