@@ -229,11 +229,13 @@ def run_ours(args, wl):
 
     frame_kind = "peer" if frame is not None else "nccl"
 
-    def step():
-        """One frame with the scene resident: render this rank's row tiles, collect the frame on rank 0."""
+    def step(begun=False):
+        """One frame with the scene resident: render this rank's row tiles, collect the frame on rank 0.
+        begun: the caller has already called frame.begin() for this frame."""
         with torch.cuda.stream(stream):
             if frame is not None:
-                frame.begin()
+                if not begun:
+                    frame.begin()
                 st = scene.render_device(w, h, depth, d_rgb_u8=frame.ptr, spp=spp, seed=1, rank=rank, world=world,
                                          rows_per_tile=ROWS_PER_TILE, flags=frame.flags)
                 full = frame.collect()  # rank 0: returns once every rank's rows are in its frame
@@ -255,8 +257,16 @@ def run_ours(args, wl):
         flush.zero_()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if frame is not None:
+            # N > 1: a device-side start line.  Without it a peer's span would begin before it may touch the
+            # frame (it first waits for rank 0 to release the previous one) and so include rank 0's L2 flush
+            # and host work BETWEEN steps, which the N = 1 span above excludes too.  With it every rank starts
+            # frame i together, and the longest span over the ranks is the time of the frame.
+            with torch.cuda.stream(stream):
+                frame.begin()
+                frame.align()
         e0.record(stream)
-        st, full = step()
+        st, full = step(begun=frame is not None)
         e1.record(stream)
         spans.append((e0, e1))
         stats_list.append(st)
@@ -395,7 +405,8 @@ def run_ours(args, wl):
                    "l2": "256 MiB buffer written between timed steps; ray pools (>1 GB) exceed L2 anyway",
                    "partition": ("single GPU" if world == 1 else "interleaved row tiles, " + (
                        "written straight into rank 0's frame over NVLink (peer-mapped, RT_FLAG_FRAME_ROWS); each rank signals a word in that frame, rank 0 waits for all on the device"
-                       if frame_kind == "peer" else "NCCL send/recv gather to rank 0") + ", inside the step")},
+                       if frame_kind == "peer" else "NCCL send/recv gather to rank 0") + ", inside the step"
+                       + ("; every timed step starts at a device-side start line over all ranks (PeerFrame.align), outside the span like the L2 flush" if frame_kind == "peer" else ""))},
         "roofline": roofline, "cpu_baseline": cpu,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "what": "rt_scene_create + rt_render into a pinned host RGB8 buffer + rt_scene_destroy"},

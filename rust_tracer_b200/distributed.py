@@ -29,6 +29,13 @@ class _RawCudaBuffer:
         self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
 
 
+# Signal words of a PeerFrame (include/rt_b200.h: RT_FRAME_SIGNAL_WORDS = 256 words behind the pixels):
+# word r = rank r has finished frame #value; word 64 + r = rank r is about to start frame #value (align());
+# word RT_FRAME_WORD_RELEASED = rank 0 has consumed frame #value.
+_WORD_READY0 = 64
+_WORD_READY_MAX_RANKS = 64
+
+
 class PeerFrame:
     """The whole RGB8 frame on rank 0's GPU, mapped into every rank (include/rt_b200.h:
     rt_frame_*): each rank renders its row tiles straight into it with RT_FLAG_FRAME_ROWS --
@@ -36,6 +43,7 @@ class PeerFrame:
     a signal word behind the pixels, in stream order.  No host barrier, no collective:
 
         frame.begin()                       # peers: wait until rank 0 has released the previous frame
+        frame.align()                       # optional (measurements): a device-side start line for all ranks
         scene.render_device(..., d_rgb_u8=frame.ptr, flags=frame.flags, rank=, world=)
         full = frame.collect()              # every rank signals; rank 0 waits for all and gets the frame
         ... rank 0 consumes `full` ...
@@ -54,7 +62,7 @@ class PeerFrame:
 
     @classmethod
     def create(cls, height, width, rank, world, local_device):
-        if world > abi.RT_FRAME_WORD_RELEASED:
+        if world > _WORD_READY0:  # the "finished" words must stay below the "ready" words
             return None
         nbytes = height * width * 3
         dev = torch.device("cuda", local_device)
@@ -96,6 +104,18 @@ class PeerFrame:
         if self.rank != 0 and self.epoch > 1:
             check(lib().rt_frame_wait(self.local_device, C.c_void_p(self.ptr), self.nbytes, abi.RT_FRAME_WORD_RELEASED, 1,
                                       self.epoch - 1, self.timeout_ms, self._stream()))
+
+    def align(self):
+        """Every rank, after begin(): publish "I am about to start frame #epoch" and wait (on the device;
+        the call returns when the wait is over) until every rank has.  A start line for measurements:
+        after it the ranks' render calls begin within a launch latency of each other, so the longest
+        (start -> done) span over the ranks IS the frame time.  Not needed for correctness."""
+        if self.world > _WORD_READY_MAX_RANKS:
+            raise RuntimeError("PeerFrame.align() supports at most %d ranks" % _WORD_READY_MAX_RANKS)
+        check(lib().rt_frame_signal(self.local_device, C.c_void_p(self.ptr), self.nbytes, _WORD_READY0 + self.rank, self.epoch,
+                                    self._stream()))
+        check(lib().rt_frame_wait(self.local_device, C.c_void_p(self.ptr), self.nbytes, _WORD_READY0, self.world, self.epoch,
+                                  self.timeout_ms, self._stream()))
 
     def collect(self):
         """After this rank's render call: publish "my rows of frame #epoch are in place".  Rank 0 then

@@ -66,3 +66,61 @@ def test_gather_layout_single_process():
     tiles = [torch.from_numpy(full[rt.tile_rows(h, r, world, rpt)]) for r in range(world)]
     out = distributed.assemble_rows(tiles, h, w, world, rpt)
     assert (out.numpy() == full).all()
+
+
+def test_peer_frame_protocol_against_a_recording_library(monkeypatch):
+    """PeerFrame's signal-word protocol (begin / align / collect / release) with the C library replaced
+    by a recorder that keeps the 256 words of one shared frame: two ranks step through three frames
+    in an interleaving a real run can produce; every wait must already be satisfied when it is
+    issued in that order (no deadlock), and the words used are the documented ones."""
+    from rust_tracer_b200 import abi, distributed as D
+
+    words = [0] * abi.RT_FRAME_SIGNAL_WORDS
+    log = []
+
+    class Lib:
+        def rt_frame_signal(self, dev, ptr, nbytes, word, value, stream):
+            assert 0 <= word < abi.RT_FRAME_SIGNAL_WORDS
+            words[word] = value
+            log.append(("signal", dev, word, value))
+            return 0
+
+        def rt_frame_wait(self, dev, ptr, nbytes, first, n, value, timeout_ms, stream):
+            assert first >= 0 and n >= 1 and first + n <= abi.RT_FRAME_SIGNAL_WORDS
+            pending = [first + i for i in range(n) if words[first + i] < value]
+            log.append(("wait", dev, first, n, value, tuple(pending)))
+            return 0
+
+        def rt_frame_release(self, *a):
+            return 0
+
+    monkeypatch.setattr(D, "lib", lambda: Lib())
+    monkeypatch.setattr(D.PeerFrame, "_stream", lambda self: None)
+    h, w, world = 16, 8, 2
+    r0 = D.PeerFrame(0x1000, h, w, 0, world, 0, imported=False)
+    r1 = D.PeerFrame(0x1000, h, w, 1, world, 1, imported=True)
+
+    def pending_of_last_wait():
+        return [e for e in log if e[0] == "wait"][-1][5]
+
+    for frame_no in (1, 2, 3):
+        r0.begin()                      # rank 0 never waits here
+        r1.begin()                      # frame 1: nothing to wait for; later: rank 0 released frame_no - 1 below
+        if frame_no > 1:
+            assert pending_of_last_wait() == ()
+        # start line: both publish "ready", then both wait -- a real run may order the two signals either way
+        for f in (r0, r1):
+            D.check(D.lib().rt_frame_signal(f.local_device, None, f.nbytes, D._WORD_READY0 + f.rank, f.epoch, None))
+        r0.align()
+        assert pending_of_last_wait() == ()
+        r1.align()
+        assert pending_of_last_wait() == ()
+        assert r1.collect() is None     # a peer signals "done" and does not wait
+        monkeypatch.setattr(D.torch, "as_tensor", lambda *a, **k: "frame")
+        assert r0.collect() == "frame"  # rank 0 signals, then waits for both "done" words
+        assert pending_of_last_wait() == ()
+        r0.release()
+        assert words[abi.RT_FRAME_WORD_RELEASED] == frame_no
+        assert words[0] == words[1] == frame_no and words[D._WORD_READY0] == words[D._WORD_READY0 + 1] == frame_no
+    # the three word ranges do not overlap for any supported world size
+    assert D._WORD_READY0 + D._WORD_READY_MAX_RANKS <= abi.RT_FRAME_WORD_RELEASED
