@@ -69,11 +69,15 @@ impl FlatScene {
     }
 
     unsafe fn from_owned_desc(p: *mut sys::rt_scene_desc) -> FlatScene {
+        // an empty array may come with a null pointer, which from_raw_parts does not accept
+        unsafe fn copy<T: Copy>(ptr: *const T, n: i32) -> Vec<T> {
+            if ptr.is_null() || n <= 0 { Vec::new() } else { std::slice::from_raw_parts(ptr, n as usize).to_vec() }
+        }
         let d = &*p;
         let flat = FlatScene {
-            shapes: std::slice::from_raw_parts(d.shapes, d.n_shapes as usize).to_vec(),
-            materials: std::slice::from_raw_parts(d.materials, d.n_materials as usize).to_vec(),
-            lights: std::slice::from_raw_parts(d.lights, d.n_lights as usize).to_vec(),
+            shapes: copy(d.shapes, d.n_shapes),
+            materials: copy(d.materials, d.n_materials),
+            lights: copy(d.lights, d.n_lights),
             ambient: d.ambient,
         };
         sys::rt_scene_desc_free(p);
