@@ -107,6 +107,128 @@ def ray_at(ray, t):  # `t * ray` = origin + direction * t (ray.rs:50-52, 63-77)
     return vadd(ray[0], vscale(ray[1], t))
 
 
+# ---- src/math/matrix.rs: construction (4x4 lists of f32) and the Gauss-Jordan inverse -----------------
+
+for _name in ("sinf", "cosf"):
+    _fn = getattr(_libm, _name)
+    _fn.restype = C.c_float
+    _fn.argtypes = [C.c_float]
+
+
+def _rows(*rows):
+    return [[F(x) for x in r] for r in rows]
+
+
+def m_identity():
+    return _rows((1, 0, 0, 0), (0, 1, 0, 0), (0, 0, 1, 0), (0, 0, 0, 1))
+
+
+def m_scale(x, y, z):  # matrix.rs:144-153
+    return _rows((x, 0, 0, 0), (0, y, 0, 0), (0, 0, z, 0), (0, 0, 0, 1))
+
+
+def m_translate(x, y, z):  # matrix.rs:155-164
+    return _rows((1, 0, 0, x), (0, 1, 0, y), (0, 0, 1, z), (0, 0, 0, 1))
+
+
+def _rads(angle):  # angle / 180.0 * pi
+    return F(angle) / F(180.0) * PI
+
+
+def m_rotate_x(angle):  # matrix.rs:166-178
+    r = _rads(angle)
+    c, s = F(_libm.cosf(float(r))), F(_libm.sinf(float(r)))
+    return _rows((1, 0, 0, 0), (0, c, -s, 0), (0, s, c, 0), (0, 0, 0, 1))
+
+
+def m_rotate_z(angle):  # matrix.rs:194-206
+    r = _rads(angle)
+    c, s = F(_libm.cosf(float(r))), F(_libm.sinf(float(r)))
+    return _rows((c, -s, 0, 0), (s, c, 0, 0), (0, 0, 1, 0), (0, 0, 0, 1))
+
+
+def m_mul(a, b):  # matrix.rs:57-75: sum starts at 0., += s[row][i] * a[i][col]
+    out = []
+    for row in range(4):
+        r = []
+        for col in range(4):
+            acc = ZERO
+            for i in range(4):
+                acc = acc + a[row][i] * b[i][col]
+            r.append(acc)
+        out.append(r)
+    return out
+
+
+def m_inverse(m):  # matrix.rs:88-142 (panics "Singular Matrix" -> ValueError here)
+    m = [list(r) for r in m]
+    inv = m_identity()
+    for col in range(4):
+        if abs(m[col][col]) < EPS:
+            big = col
+            for row in range(4):
+                if abs(m[row][col]) > abs(m[big][col]):
+                    big = row
+            if big == col:
+                raise ValueError("Singular Matrix")
+            for j in range(4):
+                m[big][j], m[col][j] = m[col][j], m[big][j]
+                inv[big][j], inv[col][j] = inv[col][j], inv[big][j]
+        for row in range(4):
+            if row != col:
+                coeff = m[row][col] / m[col][col]
+                if abs(coeff) >= EPS:
+                    for j in range(4):
+                        m[row][j] = m[row][j] - coeff * m[col][j]
+                        inv[row][j] = inv[row][j] - coeff * inv[col][j]
+                    m[row][col] = ZERO
+    for row in range(4):
+        for col in range(4):
+            inv[row][col] = inv[row][col] / m[row][row]
+    return inv
+
+
+def m_flat(m):
+    return [x for r in m for x in r]
+
+
+def plane_axes(normal):  # Plane::new, plane.rs:22-30
+    w = (ZERO, ONE, ZERO) if np.sqrt(len2(cross(normal, (ONE, ZERO, ZERO)))) <= EPS else (ONE, ZERO, ZERO)
+    u = norm(cross(normal, w))
+    return u, norm(cross(normal, u))
+
+
+def default_scene_values():
+    """src/my_scene.rs:45-120 read a third time: [(kind, transform | None, p12 | None, material)], lights, ambient.
+    material = (kind, ambient fn, diffuse fn, specular fn, power, reflectivity, refraction index),
+    fn = (0, rgb) constant | (1, rgb) checkerboard."""
+    W, K = (ONE, ONE, ONE), (ZERO, ZERO, ZERO)
+    dim_white = (F(0.1) * ONE, F(0.1) * ONE, F(0.1) * ONE)  # fn dim_white: 0.1 * WHITE
+    const = lambda c: (0, tuple(F(x) for x in c))
+    phong = lambda a, d, sp, pw, rf, ri: (0, const(a), const(d), const(sp), F(pw), F(rf), F(ri))
+    tex = (1, (0, dim_white), (1, W), (0, dim_white), F(60.0), F(0.0), F(0.0))
+    t1 = m_mul(m_mul(m_translate(-1.0, 0.0, 0.0), m_rotate_z(75.0)), m_scale(1.0, 0.25, 1.0))
+    t2 = m_translate(1.0, -1.0, 0.0)
+    t3 = m_mul(m_translate(0.0, -0.5, -3.0), m_scale(0.6, 0.6, 0.6))
+    t6 = m_mul(m_translate(-1.0, -1.0, -4.0), m_rotate_x(-45.0))
+
+    def plane(origin, normal):
+        o, n = tuple(F(x) for x in origin), tuple(F(x) for x in normal)
+        u, v = plane_axes(n)
+        return list(o) + list(n) + list(u) + list(v)
+
+    shapes = [
+        (0, t1, None, phong((0.1, 0.1, 0.1), (1, 0, 0), W, 60.0, 0.5, 0.0)),
+        (0, t2, None, phong(K, (0, 0, 1), (0, 0, 0.1), 600.0, 0.4, 0.0)),
+        (0, t3, None, phong(K, W, W, 60.0, 0.7, 1.333)),
+        (1, None, plane((0, -2, 2), (0, 0, -1)), tex),
+        (1, None, plane((0, -2, 0), (0, 1, 0)), tex),
+        (3, t6, None, phong(K, W, W, 60.0, 0.0, 1.333)),
+    ]
+    lights = [((4, 4, 0), (1, 0, 0)), ((-1, 2, -4), (0, 1, 0)), ((0, 8, -4), (0, 0, 1))]
+    return shapes, lights, (F(0.1), F(0.1), F(0.1))
+
+
 # ---- scene loading ----------------------------------------------------------------------------------
 
 def _f(seq):

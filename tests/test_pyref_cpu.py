@@ -103,3 +103,59 @@ def test_forest_golden_fixture_is_what_the_second_restatement_renders():
     owner = mk()
     f, u8, cnt, _ = pyref.render_forest(owner.desc, abi.default_camera(w, h), depth)
     assert np.array_equal(f, g["rgb_f32"], equal_nan=True) and (u8 == g["rgb_u8"]).all()
+
+
+def test_default_scene_description_bit_for_bit(default_desc):
+    """The host builder's flat description of src/my_scene.rs (transforms through Matrix::translate /
+    rotate / scale / mat_mul, inverses through the reference's Gauss-Jordan, plane texture axes, every
+    material and light constant) against the values pyref derives from the Rust source on its own."""
+    shapes, lights, ambient = pyref.default_scene_values()
+    d = default_desc.desc
+    assert (d.n_shapes, d.n_materials, d.n_lights) == (len(shapes), len(shapes), len(lights))
+    bits = lambda xs: [np.float32(x).view(np.uint32) for x in xs]
+    ident = pyref.m_flat(pyref.m_identity())
+    for i, (kind, transform, p12, mat) in enumerate(shapes):
+        s = d.shapes[i]
+        assert s.kind == kind and s.material == i
+        t = pyref.m_flat(transform) if transform is not None else ident
+        inv = pyref.m_flat(pyref.m_inverse(transform)) if transform is not None else ident
+        assert bits(s.transform) == bits(t), i
+        assert bits(s.inv_transform) == bits(inv), i
+        if p12 is not None:
+            assert bits(s.p) == bits(p12), i
+        m = d.materials[i]
+        mk, amb, dif, spec, power, refl, ridx = mat
+        assert m.kind == mk
+        for got, want in ((m.ambient, amb), (m.diffuse, dif), (m.specular, spec)):
+            assert got.kind == want[0] and bits(got.rgb) == bits(want[1]), i
+        assert bits([m.power, m.reflectivity, m.refraction_index]) == bits([power, refl, ridx])
+    for i, (pos, col) in enumerate(lights):
+        assert d.lights[i].kind == abi.RT_LIGHT_POINT
+        assert bits(d.lights[i].pos) == bits(pos) and bits(d.lights[i].color) == bits(col)
+    assert bits(d.ambient) == bits(ambient)
+
+
+def test_matrix_inverse_bit_for_bit_on_random_transforms():
+    """Gauss-Jordan of src/math/matrix.rs:88-142 (pivot swap, EPSILON-skipped rows, final division) in
+    pyref against the host library's rt_matrix_inverse, on T.Rz.Rx.S compositions and on matrices that
+    need the row swap."""
+    import ctypes as C
+    L = rt.lib()
+    rng = np.random.default_rng(17)
+    cases = []
+    for _ in range(40):
+        t, a, sc = rng.uniform(-3, 3, 3), rng.uniform(-180, 180, 2), rng.uniform(0.2, 2.5, 3)
+        cases.append(pyref.m_mul(pyref.m_mul(pyref.m_mul(pyref.m_translate(*t), pyref.m_rotate_z(a[0])), pyref.m_rotate_x(a[1])),
+                                 pyref.m_scale(*sc)))
+    cases.append(pyref._rows((0, 1, 0, 2), (1, 0, 0, -1), (0, 0, 2, 0.5), (0, 0, 0, 1)))  # zero pivot: rows swap
+    cases.append(pyref._rows((0, 0, 1, 0), (0, 1, 0, 0), (1, 0, 0, 0), (0, 0, 0, 1)))
+    for m in cases:
+        flat = (C.c_float * 16)(*[float(x) for x in pyref.m_flat(m)])
+        out = (C.c_float * 16)()
+        assert L.rt_matrix_inverse(flat, out) == 0
+        want = pyref.m_flat(pyref.m_inverse(m))
+        assert [np.float32(x).view(np.uint32) for x in out] == [np.float32(x).view(np.uint32) for x in want]
+    singular = (C.c_float * 16)(*([0.0] * 16))
+    assert L.rt_matrix_inverse(singular, out) == abi.RT_ERR_INVALID
+    with pytest.raises(ValueError):
+        pyref.m_inverse(pyref._rows(*([(0, 0, 0, 0)] * 4)))
