@@ -9,7 +9,9 @@
 // Parity status: the reference is Rust and cannot be built here (no rustc/cargo), and it
 // ships no golden images; this restatement is pinned against every known-answer unit test
 // the reference holds for this path (tests/test_oracle_kat.py lists them with file:line).
-// Whole-image parity is therefore "pinned by KATs + line-by-line review", see DESIGN.md.
+// Whole-image parity is therefore "pinned by KATs + line-by-line review"; a second,
+// independent restatement of the same Rust (tests/pyref.py, scalar numpy.float32) agrees with this
+// one bit for bit on whole frames, counts and the default scene's description (tests/test_pyref_cpu.py).
 #pragma once
 #include <cmath>
 #include <cstdint>
