@@ -159,3 +159,33 @@ def test_matrix_inverse_bit_for_bit_on_random_transforms():
     assert L.rt_matrix_inverse(singular, out) == abi.RT_ERR_INVALID
     with pytest.raises(ValueError):
         pyref.m_inverse(pyref._rows(*([(0, 0, 0, 0)] * 4)))
+
+
+def test_the_references_own_bench_scene():
+    """`render_128x128` (src/render.rs:233-249), the one render workload the reference defines besides
+    my_scene.rs: one sphere under scale(1, 2.25, 1), Phong(WHITE, RED, WHITE, 60, reflectivity 1, index 0),
+    no lights, ambient BLACK (Scene::new), 128x128, depth 5.  Nothing emits light, so the frame is black;
+    what the bench measures is the rays: primary + reflection rays off the sphere."""
+    import ctypes as C
+    shapes, mats, lights = (abi.rt_shape * 1)(), (abi.rt_material * 1)(), (abi.rt_light * 0)()
+    t = pyref.m_scale(1.0, 2.25, 1.0)
+    shapes[0].kind, shapes[0].material = abi.RT_SHAPE_SPHERE, 0
+    shapes[0].transform[:] = [float(x) for x in pyref.m_flat(t)]
+    shapes[0].inv_transform[:] = [float(x) for x in pyref.m_flat(pyref.m_inverse(t))]
+    m = mats[0]
+    m.kind = abi.RT_MATERIAL_PHONG
+    for fn, rgb in ((m.ambient, (1, 1, 1)), (m.diffuse, (1, 0, 0)), (m.specular, (1, 1, 1))):
+        fn.kind = abi.RT_COLOR_CONST
+        fn.rgb[:] = rgb
+    m.power, m.reflectivity, m.refraction_index = 60.0, 1.0, 0.0
+    desc = rt.SceneDesc.from_arrays(shapes, mats, lights, (0.0, 0.0, 0.0))
+    cam = abi.default_camera(128, 128)
+    of, ou, oc = orc.render(desc.desc, cam, 5)
+    assert (of == 0).all() and (ou == 0).all()
+    hits = int(oc.nodes)
+    assert oc.shadow_rays == 0 and oc.rays == 128 * 128 + hits  # every node reflects once (reflectivity 1), none refracts
+    assert 0 < hits < 128 * 128
+    small = abi.default_camera(32, 32)  # the second restatement on a thumbnail of the same scene
+    f, u8, cnt = pyref.render(desc.desc, small, 5)
+    sf, su, sc = orc.render(desc.desc, small, 5)
+    assert np.array_equal(f, sf) and cnt["rays"] == sc.rays and cnt["nodes"] == sc.nodes
