@@ -124,3 +124,75 @@ def test_peer_frame_protocol_against_a_recording_library(monkeypatch):
         assert words[0] == words[1] == frame_no and words[D._WORD_READY0] == words[D._WORD_READY0 + 1] == frame_no
     # the three word ranges do not overlap for any supported world size
     assert D._WORD_READY0 + D._WORD_READY_MAX_RANKS <= abi.RT_FRAME_WORD_RELEASED
+
+
+def test_peer_frame_protocol_does_not_deadlock_under_concurrency(monkeypatch):
+    """The same protocol with REAL blocking: four "ranks" run bench.py's timed-step sequence
+    (begin, align, render, collect, release) concurrently in threads against one shared word array whose
+    waits block until satisfied (or fail after 5 s).  Random delays shuffle the interleavings; every
+    rank must get through every frame, and rank 0 must never collect a frame a peer has not signalled."""
+    import random
+    import threading
+    import time
+    from rust_tracer_b200 import abi, distributed as D
+
+    world, frames = 4, 25
+    words = [0] * abi.RT_FRAME_SIGNAL_WORDS
+    cond = threading.Condition()
+    rendered = [0] * world          # frames each rank has "rendered"
+    errors = []
+
+    class Lib:
+        def rt_frame_signal(self, dev, ptr, nbytes, word, value, stream):
+            with cond:
+                words[word] = value
+                cond.notify_all()
+            return 0
+
+        def rt_frame_wait(self, dev, ptr, nbytes, first, n, value, timeout_ms, stream):
+            deadline = time.monotonic() + 5.0
+            with cond:
+                while any(words[first + i] < value for i in range(n)):
+                    left = deadline - time.monotonic()
+                    if left <= 0:
+                        errors.append("timeout waiting for words [%d, %d) >= %d: %s" % (first, first + n, value, words[first:first + n]))
+                        return abi.RT_ERR_TIMEOUT
+                    cond.wait(left)
+            return 0
+
+        def rt_last_error(self):
+            return b"timeout"
+
+    the_lib = Lib()
+    monkeypatch.setattr(D, "lib", lambda: the_lib)
+    monkeypatch.setattr(D, "check", lambda rc: (_ for _ in ()).throw(RuntimeError("rc %d" % rc)) if rc < 0 else rc)
+    monkeypatch.setattr(D.PeerFrame, "_stream", lambda self: None)
+    monkeypatch.setattr(D.torch, "as_tensor", lambda *a, **k: "frame")
+
+    def rank_main(rank):
+        rng = random.Random(rank)
+        f = D.PeerFrame(0x1000, 8, 8, rank, world, rank, imported=rank != 0)
+        try:
+            for i in range(1, frames + 1):
+                time.sleep(rng.random() * 0.002)        # L2 flush, host work between steps
+                f.begin()
+                if rank != 0 and i > 1:                 # a peer may not touch the pixels before rank 0 has consumed frame i - 1
+                    assert words[abi.RT_FRAME_WORD_RELEASED] >= i - 1
+                f.align()
+                time.sleep(rng.random() * 0.003)        # the render call
+                rendered[rank] = i
+                full = f.collect()
+                if rank == 0:
+                    assert full == "frame"
+                    assert all(r >= i for r in rendered), (i, list(rendered))  # every rank's rows of frame i are in
+                f.release()
+        except Exception as e:  # noqa: BLE001
+            errors.append("rank %d: %r" % (rank, e))
+
+    threads = [threading.Thread(target=rank_main, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(30)
+    assert not errors, errors
+    assert rendered == [frames] * world and words[abi.RT_FRAME_WORD_RELEASED] == frames
