@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 3
+#define RT_B200_ABI_VERSION 4
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -180,6 +180,18 @@ typedef struct rt_stats {
     uint64_t tested_pairs;  /* ray x shape pairs resolved ONE BY ONE (bounding-sphere filter of that
                                shape's own bound, or exact test); the rest of rays x shapes were
                                dismissed wholesale by a group sphere.  SURVEY 8d credits only these */
+    /* The same, split so that a reader can price each pair for what was done to it (SURVEY 8d:
+     * "culling must be subtracted"): a pair whose own bounding sphere was evaluated and rejected cost
+     * 4 or 7 FMA, not an intersection test; only exact tests are intersections the reference's way. */
+    uint64_t bound_evals_sphere;   /* ray x sphere pairs whose own bounding sphere the filter evaluated */
+    uint64_t bound_evals_triangle; /* ray x triangle pairs, likewise                                  */
+    uint64_t bound_evals_cube;     /* ray x cube pairs, likewise                                      */
+    uint64_t hier_evals;           /* ray x (group sphere | quad sphere) evaluations                  */
+    uint64_t exact_sphere_tests;   /* exact_tests by kind of shape; the planes' are plane_tests       */
+    uint64_t exact_triangle_tests;
+    uint64_t exact_cube_tests;
+    double   exact_flops;          /* exact tests x their SURVEY 8d price (54 / 30 / 393, planes 47 | 14) */
+    double   executed_flops;       /* filter_flops + exact_flops: what the sweeps' FP32 pipe was asked to do */
 } rt_stats;
 
 typedef struct rt_scene rt_scene;   /* opaque: device-resident scene tables */
@@ -204,12 +216,16 @@ int32_t rt_tile_rows_for_rank(int32_t height, int32_t rank, int32_t world, int32
  * the description into structure-of-arrays device tables on CUDA device `device`.       */
 int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out);
 /* Material::set_diffuse + friends after upload (src/gui.rs:221-235): replaces the whole
- * material table, geometry untouched.  n must equal the scene's n_materials.            */
+ * material table, geometry untouched.  n must equal the scene's n_materials.  While a forest
+ * built from the scene is alive, reflectivity and refraction_index must stay as they are (they
+ * decided which rays the forest holds): RT_ERR_UNSUPPORTED otherwise.                   */
 int rt_scene_update_materials(rt_scene *scene, const rt_material *materials, int32_t n);
 /* Launch this scene's kernels and copies on `stream` (a cudaStream_t created by the caller
  * on the scene's device, e.g. a torch stream's handle) so that the caller's own events
  * bracket the work; NULL restores the scene's private stream.  Calls stay synchronous.   */
 int rt_scene_set_stream(rt_scene *scene, void *stream);
+/* Forests built from the scene keep using its tables: if any is alive, the scene is freed when the
+ * last of them is destroyed (either order of the two destroy calls is fine).                  */
 void rt_scene_destroy(rt_scene *scene);
 /* Destroyed scenes and forests leave their ray pools (device memory) cached, one set per
  * device, for the next scene; rt_trim frees the cache of `device` (-1: every device).     */
@@ -265,6 +281,35 @@ int rt_frame_release(int32_t device, void *d_ptr, int32_t imported);
 int rt_frame_signal(int32_t device, void *d_ptr, size_t bytes, int32_t word, uint32_t value, void *stream);
 int rt_frame_wait(int32_t device, void *d_ptr, size_t bytes, int32_t first_word, int32_t n_words, uint32_t value,
                   uint32_t timeout_ms, void *stream);
+
+/* ---- one host call, several GPUs (SURVEY 8b "Threading", 8e) ---------------------------- */
+
+/* The reference renders a frame with ONE blocking call from one thread, render::render(&camera,
+ * &scene, &mut buffer, depth) (src/render.rs:31-38; caller src/main.rs:244-261).  rt_multi is the
+ * same call for a host that owns several GPUs: the scene tables are built once on the host and
+ * uploaded to every listed device; each render call splits the frame into interleaved tiles of
+ * params->tile_rows rows (tile k goes to device k % n: pixels are independent, no collective),
+ * drives every device from its own worker thread inside the library and returns when the whole
+ * image is in place.  params->rank / world must be 0 / 1.  stats are summed over the devices,
+ * the times are those of the slowest one.                                                      */
+typedef struct rt_multi rt_multi; /* opaque: one scene resident on n devices */
+int rt_multi_create(const rt_scene_desc *desc, const int32_t *devices, int32_t n_devices, rt_multi **out);
+int32_t rt_multi_device_count(const rt_multi *multi);
+int rt_multi_update_materials(rt_multi *multi, const rt_material *materials, int32_t n);
+/* Whole-frame HOST buffers (either may be NULL), y_res x x_res x 3: every device copies its own
+ * rows to their place in the image over its own PCIe link, all devices in parallel.          */
+int rt_multi_render(rt_multi *multi, const rt_camera *camera, const rt_render_params *params, float *rgb_f32,
+                    uint8_t *rgb_u8, rt_stats *stats);
+/* Whole-frame DEVICE buffers on the FIRST listed device: every device's last kernel stores its rows
+ * there over NVLink / NVSwitch peer access (RT_FLAG_FRAME_ROWS): the gather is those stores.
+ * RT_ERR_UNSUPPORTED when a device has no peer access to the first one.                       */
+int rt_multi_render_device(rt_multi *multi, const rt_camera *camera, const rt_render_params *params, void *d_rgb_f32,
+                           void *d_rgb_u8, rt_stats *stats);
+void rt_multi_destroy(rt_multi *multi);
+/* rt_multi_create + rt_multi_render + rt_multi_destroy: the reference's call as it stands, a scene
+ * description in, an image out (what rust/reference_patch/gpu.rs binds for `--gpus N`).        */
+int rt_render_multi(const rt_scene_desc *desc, const int32_t *devices, int32_t n_devices, const rt_camera *camera,
+                    const rt_render_params *params, float *rgb_f32, uint8_t *rgb_u8, rt_stats *stats);
 
 /* ---- RayForest renderer -------------------------------------------------------------- */
 

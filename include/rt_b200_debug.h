@@ -1,0 +1,36 @@
+/*
+ * rt_b200_debug.h -- test and measurement hooks of librt_b200.so.  NOT part of the drop-in ABI
+ * (include/rt_b200.h): a host binding has no reason to call these, and the Rust `-sys` crate
+ * does not declare them.
+ *
+ * The library never reads the environment.  Its scheduling constants (work items per warp,
+ * rays per thread, table chunking, ...; rust_tracer_b200/csrc/tuning.h) are compile-time
+ * defaults that the GPU tests override through rt_debug_set to drive every code path of the
+ * sweep (several table chunks, pair path on / off, one launch per light, ...) and the tools
+ * under tools/ to A/B them.  No knob can change a result: the correctness margins of the bound
+ * filter are constants of the library and cannot be set from here.
+ */
+#ifndef RT_B200_DEBUG_H
+#define RT_B200_DEBUG_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* name: a field of rt::Tuning ("rays_per_thread", "want_light", "want_heavy", "slices",
+ * "tail_pct", "tail_mult", "item_max", "table_cap", "merge_lights", "heavy_allow",
+ * "band_samples", "origin_tables", "origin_min_slots", "host_threads", "shadow_anyhit",
+ * "trace").  Process-wide; takes effect at the next call (scene knobs: at the next
+ * rt_scene_create).  RT_ERR_INVALID for an unknown name or a value out of range.          */
+int rt_debug_set(const char *name, int64_t value);
+/* Current value, or INT64_MIN for an unknown name. */
+int64_t rt_debug_get(const char *name);
+/* Back to the compile-time defaults. */
+void rt_debug_reset(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_DEBUG_H */

@@ -16,7 +16,7 @@
 //! gains one method, `flatten`, written below next to the fields it reads.
 
 use crate::math::Matrix;
-use crate::render::RenderBuffer;
+use crate::render::{Camera, RenderBuffer};
 use crate::scene::{Color, ColorFun, Scene};
 use rt_b200::{rt_colorfn, rt_light, rt_material, rt_shape, FlatScene};
 use std::collections::HashSet;
@@ -147,12 +147,34 @@ fn store(img: &rt_b200::Image, buffer: &mut RenderBuffer) {
     }
 }
 
-/// Replaces the body of `render::render` (src/render.rs:31-38) for `--method basic`.
+/// The reference's `Camera` (src/render.rs:155-163, every field public) as the ABI's `rt_camera`.
+pub fn flatten_camera(camera: &Camera) -> rt_b200::rt_camera {
+    rt_b200::rt_camera {
+        origin: [camera.origin.x(), camera.origin.y(), camera.origin.z()],
+        x_min: camera.x_min,
+        x_max: camera.x_max,
+        y_min: camera.y_min,
+        y_max: camera.y_max,
+        x_res: camera.x_res as i32,
+        y_res: camera.y_res as i32,
+    }
+}
+
+/// Replaces the body of `render::render(camera, scene, buffer, depth)` (src/render.rs:31-38) for
+/// `--method basic`, same arguments.  Renders on every GPU of the box (`--gpus N` of the patched
+/// CLI narrows that; one device = the single-GPU path of the library).
 /// Panics on failure like the reference does on its own errors (src/cli.rs:123).
-pub fn render(scene: &Scene, buffer: &mut RenderBuffer, depth: usize) {
+pub fn render(camera: &Camera, scene: &Scene, buffer: &mut RenderBuffer, depth: usize) {
+    let n = rt_b200::device_count().unwrap_or_else(|e| panic!("{}", e));
+    let devices: Vec<i32> = (0..n as i32).collect();
+    render_on(&devices, camera, scene, buffer, depth)
+}
+
+/// `render` on the listed CUDA devices: one blocking call, the library drives them all.
+pub fn render_on(devices: &[i32], camera: &Camera, scene: &Scene, buffer: &mut RenderBuffer, depth: usize) {
     let flat = flatten(scene);
-    let mut gpu = rt_b200::Scene::new(&flat, 0).unwrap_or_else(|e| panic!("{}", e));
-    let (img, _stats) = gpu.render(buffer.w, buffer.h, depth).unwrap_or_else(|e| panic!("{}", e));
+    let cam = flatten_camera(camera);
+    let (img, _stats) = rt_b200::render_multi(&flat, devices, &cam, depth).unwrap_or_else(|e| panic!("{}", e));
     store(&img, buffer);
 }
 

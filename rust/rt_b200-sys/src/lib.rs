@@ -8,7 +8,7 @@
 
 use std::os::raw::{c_char, c_int, c_void};
 
-pub const RT_B200_ABI_VERSION: c_int = 3;
+pub const RT_B200_ABI_VERSION: c_int = 4;
 
 // rt_status
 pub const RT_OK: c_int = 0;
@@ -135,6 +135,15 @@ pub struct rt_stats {
     pub kernel_launches: u32,
     pub filter_flops: f64,
     pub tested_pairs: u64,
+    pub bound_evals_sphere: u64,
+    pub bound_evals_triangle: u64,
+    pub bound_evals_cube: u64,
+    pub hier_evals: u64,
+    pub exact_sphere_tests: u64,
+    pub exact_triangle_tests: u64,
+    pub exact_cube_tests: u64,
+    pub exact_flops: f64,
+    pub executed_flops: f64,
 }
 
 #[repr(C)]
@@ -153,6 +162,12 @@ pub struct rt_forest_stats {
 /// Opaque: device-resident scene tables.
 #[repr(C)]
 pub struct rt_scene {
+    _private: [u8; 0],
+}
+
+/// Opaque: one scene resident on several devices, rendered by one call.
+#[repr(C)]
+pub struct rt_multi {
     _private: [u8; 0],
 }
 
@@ -192,6 +207,38 @@ extern "C" {
         params: *const rt_render_params,
         d_rgb_f32: *mut c_void,
         d_rgb_u8: *mut c_void,
+        stats: *mut rt_stats,
+    ) -> c_int;
+
+    // ---- one host call, several GPUs
+    pub fn rt_multi_create(desc: *const rt_scene_desc, devices: *const i32, n_devices: i32, out: *mut *mut rt_multi) -> c_int;
+    pub fn rt_multi_device_count(multi: *const rt_multi) -> i32;
+    pub fn rt_multi_update_materials(multi: *mut rt_multi, materials: *const rt_material, n: i32) -> c_int;
+    pub fn rt_multi_render(
+        multi: *mut rt_multi,
+        camera: *const rt_camera,
+        params: *const rt_render_params,
+        rgb_f32: *mut f32,
+        rgb_u8: *mut u8,
+        stats: *mut rt_stats,
+    ) -> c_int;
+    pub fn rt_multi_render_device(
+        multi: *mut rt_multi,
+        camera: *const rt_camera,
+        params: *const rt_render_params,
+        d_rgb_f32: *mut c_void,
+        d_rgb_u8: *mut c_void,
+        stats: *mut rt_stats,
+    ) -> c_int;
+    pub fn rt_multi_destroy(multi: *mut rt_multi);
+    pub fn rt_render_multi(
+        desc: *const rt_scene_desc,
+        devices: *const i32,
+        n_devices: i32,
+        camera: *const rt_camera,
+        params: *const rt_render_params,
+        rgb_f32: *mut f32,
+        rgb_u8: *mut u8,
         stats: *mut rt_stats,
     ) -> c_int;
 

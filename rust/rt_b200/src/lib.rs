@@ -164,13 +164,19 @@ impl Scene {
         check(unsafe { sys::rt_scene_update_materials(self.handle, materials.as_ptr(), materials.len() as i32) })
     }
 
-    /// `render::render(&camera, &scene, &mut buffer, depth)` (src/render.rs:31-38).
+    /// `render::render(&camera, &scene, &mut buffer, depth)` (src/render.rs:31-38) with
+    /// `Camera::new(width, height)`.
     pub fn render(&mut self, width: usize, height: usize, depth: usize) -> Result<(Image, rt_stats)> {
-        let cam = camera(width, height);
+        self.render_with(&camera(width, height), depth)
+    }
+
+    /// The same with the caller's camera: every field of the reference's `Camera` is public
+    /// (src/render.rs:155-163) and `rt_camera` carries them all.
+    pub fn render_with(&mut self, cam: &rt_camera, depth: usize) -> Result<(Image, rt_stats)> {
         let p = params(depth, sys::RT_FLAG_NONE);
-        let mut img = Image::new(width, height);
+        let mut img = Image::new(cam.x_res as usize, cam.y_res as usize);
         let mut stats = rt_stats::default();
-        check(unsafe { sys::rt_render(self.handle, &cam, &p, img.rgb.as_mut_ptr(), ptr::null_mut(), &mut stats) })?;
+        check(unsafe { sys::rt_render(self.handle, cam, &p, img.rgb.as_mut_ptr(), ptr::null_mut(), &mut stats) })?;
         Ok((img, stats))
     }
 
@@ -199,7 +205,66 @@ impl Drop for Scene {
     }
 }
 
-/// Device-resident ray forest (`rt_forest`).  Must be dropped before the `Scene` it was built from.
+/// One scene resident on several GPUs (`rt_multi`): the reference's single blocking
+/// `render::render` call (src/render.rs:31-38) for a host that owns 1-8 devices.  The library
+/// drives every device from its own worker thread; the frame is split into interleaved row tiles.
+pub struct MultiScene {
+    handle: *mut sys::rt_multi,
+}
+
+impl MultiScene {
+    pub fn new(flat: &FlatScene, devices: &[i32]) -> Result<MultiScene> {
+        let desc = flat.as_desc();
+        let mut handle = ptr::null_mut();
+        check(unsafe { sys::rt_multi_create(&desc, devices.as_ptr(), devices.len() as i32, &mut handle) })?;
+        Ok(MultiScene { handle })
+    }
+
+    pub fn devices(&self) -> usize {
+        unsafe { sys::rt_multi_device_count(self.handle) as usize }
+    }
+
+    pub fn update_materials(&mut self, materials: &[rt_material]) -> Result<()> {
+        check(unsafe { sys::rt_multi_update_materials(self.handle, materials.as_ptr(), materials.len() as i32) })
+    }
+
+    /// `render::render(&camera, &scene, &mut buffer, depth)` on all devices of the scene.
+    pub fn render_with(&mut self, cam: &rt_camera, depth: usize) -> Result<(Image, rt_stats)> {
+        let p = params(depth, sys::RT_FLAG_NONE);
+        let mut img = Image::new(cam.x_res as usize, cam.y_res as usize);
+        let mut stats = rt_stats::default();
+        check(unsafe { sys::rt_multi_render(self.handle, cam, &p, img.rgb.as_mut_ptr(), ptr::null_mut(), &mut stats) })?;
+        Ok((img, stats))
+    }
+}
+
+impl Drop for MultiScene {
+    fn drop(&mut self) {
+        unsafe { sys::rt_multi_destroy(self.handle) }
+    }
+}
+
+/// One-shot `rt_render_multi`: scene description in, image out, on the listed devices.
+pub fn render_multi(flat: &FlatScene, devices: &[i32], cam: &rt_camera, depth: usize) -> Result<(Image, rt_stats)> {
+    let desc = flat.as_desc();
+    let p = params(depth, sys::RT_FLAG_NONE);
+    let mut img = Image::new(cam.x_res as usize, cam.y_res as usize);
+    let mut stats = rt_stats::default();
+    check(unsafe {
+        sys::rt_render_multi(&desc, devices.as_ptr(), devices.len() as i32, cam, &p, img.rgb.as_mut_ptr(), ptr::null_mut(), &mut stats)
+    })?;
+    Ok((img, stats))
+}
+
+/// Number of CUDA devices the library sees (`rt_device_count`).
+pub fn device_count() -> Result<usize> {
+    let n = unsafe { sys::rt_device_count() };
+    check(n.min(0))?;
+    Ok(n as usize)
+}
+
+/// Device-resident ray forest (`rt_forest`).  May be dropped before or after the `Scene` it was built
+/// from: the library keeps the scene's tables alive until its last forest is gone.
 pub struct Forest {
     handle: *mut sys::rt_forest,
     pub width: usize,

@@ -5,5 +5,5 @@ into librt_b200.so), the C++ host mirror of the reference's scene API (csrc/host
 this thin ctypes binding.  There is no CPU implementation in this package.
 """
 from . import abi  # noqa: F401
-from .api import Forest, Scene, SceneDesc, camera, measure_fp32_peak, tile_rows, trim  # noqa: F401
+from .api import Forest, MultiScene, Scene, SceneDesc, camera, device_count, measure_fp32_peak, render_multi, tile_rows, trim, tuned  # noqa: F401
 from ._lib import RtError, lib  # noqa: F401

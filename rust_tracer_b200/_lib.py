@@ -44,6 +44,16 @@ def _declare(lib):
     lib.rt_frame_wait.argtypes = [C.c_int32, vp, C.c_size_t, C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, vp]
     lib.rt_render.argtypes = [vp, P(abi.rt_camera), P(abi.rt_render_params), vp, vp, P(abi.rt_stats)]
     lib.rt_render_device.argtypes = [vp, P(abi.rt_camera), P(abi.rt_render_params), vp, vp, P(abi.rt_stats)]
+    lib.rt_multi_create.argtypes = [P(abi.rt_scene_desc), P(C.c_int32), C.c_int32, P(vp)]
+    lib.rt_multi_device_count.argtypes = [vp]
+    lib.rt_multi_device_count.restype = C.c_int32
+    lib.rt_multi_update_materials.argtypes = [vp, P(abi.rt_material), C.c_int32]
+    lib.rt_multi_render.argtypes = [vp, P(abi.rt_camera), P(abi.rt_render_params), vp, vp, P(abi.rt_stats)]
+    lib.rt_multi_render_device.argtypes = [vp, P(abi.rt_camera), P(abi.rt_render_params), vp, vp, P(abi.rt_stats)]
+    lib.rt_multi_destroy.argtypes = [vp]
+    lib.rt_multi_destroy.restype = None
+    lib.rt_render_multi.argtypes = [P(abi.rt_scene_desc), P(C.c_int32), C.c_int32, P(abi.rt_camera), P(abi.rt_render_params),
+                                    vp, vp, P(abi.rt_stats)]
     lib.rt_forest_build.argtypes = [vp, P(abi.rt_camera), P(abi.rt_render_params), P(vp), P(abi.rt_stats)]
     lib.rt_forest_eval.argtypes = [vp, P(C.c_float), vp, vp, P(abi.rt_stats)]
     lib.rt_forest_eval_filtered.argtypes = [vp, P(C.c_float), P(C.c_int32), C.c_int32, vp, vp, P(C.c_uint64),
@@ -54,6 +64,11 @@ def _declare(lib):
     lib.rt_forest_destroy.argtypes = [vp]
     lib.rt_forest_destroy.restype = None
     lib.rt_measure_fp32_peak.argtypes = [C.c_int32, P(C.c_double), P(C.c_int32), P(C.c_int32)]
+    # debug hooks (include/rt_b200_debug.h)
+    lib.rt_debug_set.argtypes = [C.c_char_p, C.c_int64]
+    lib.rt_debug_get.argtypes = [C.c_char_p]
+    lib.rt_debug_get.restype = C.c_int64
+    lib.rt_debug_reset.restype = None
     # host helpers
     lib.rt_builtin_scene.argtypes = [C.c_char_p, C.c_uint64, P(P(abi.rt_scene_desc))]
     lib.rt_synthetic_scene.argtypes = [C.c_int32, C.c_int32, C.c_uint64, C.c_float, C.c_float,
@@ -75,6 +90,8 @@ def _declare(lib):
 EXPORTS = [
     "rt_abi_version", "rt_last_error", "rt_device_count", "rt_camera_default", "rt_tile_rows_for_rank",
     "rt_scene_create", "rt_scene_update_materials", "rt_scene_set_stream", "rt_scene_destroy", "rt_trim", "rt_render", "rt_render_device",
+    "rt_multi_create", "rt_multi_device_count", "rt_multi_update_materials", "rt_multi_render", "rt_multi_render_device",
+    "rt_multi_destroy", "rt_render_multi",
     "rt_frame_alloc", "rt_frame_export", "rt_frame_import", "rt_frame_release", "rt_frame_signal", "rt_frame_wait",
     "rt_forest_build", "rt_forest_eval", "rt_forest_eval_filtered", "rt_forest_get_stats", "rt_forest_size",
     "rt_forest_trees_with", "rt_forest_destroy", "rt_measure_fp32_peak",
@@ -82,6 +99,10 @@ EXPORTS = [
     "rt_matrix_inverse", "rt_matrix_compose",
     "rt_plane_axes", "rt_triangle_normal",
 ]
+
+
+# include/rt_b200_debug.h: test and measurement hooks, not part of the drop-in ABI
+DEBUG_EXPORTS = ["rt_debug_set", "rt_debug_get", "rt_debug_reset"]
 
 
 def lib():
@@ -93,7 +114,7 @@ def lib():
                 "(make -C rust_tracer_b200/csrc). There is no fallback path.")
         handle = C.CDLL(LIB_PATH)
         _declare(handle)
-        if handle.rt_abi_version() != 3:
+        if handle.rt_abi_version() != 4:
             raise ImportError("librt_b200.so ABI version mismatch")
         _lib = handle
     return _lib

@@ -60,7 +60,10 @@ class rt_stats(C.Structure):
                 ("nodes", C.c_uint64), ("sphere_tests", C.c_uint64), ("plane_tests", C.c_uint64),
                 ("triangle_tests", C.c_uint64), ("cube_tests", C.c_uint64), ("exact_tests", C.c_uint64),
                 ("algorithmic_flops", C.c_double), ("sweep_ms", C.c_float), ("shade_ms", C.c_float),
-                ("total_ms", C.c_float), ("kernel_launches", C.c_uint32), ("filter_flops", C.c_double), ("tested_pairs", C.c_uint64)]
+                ("total_ms", C.c_float), ("kernel_launches", C.c_uint32), ("filter_flops", C.c_double), ("tested_pairs", C.c_uint64),
+                ("bound_evals_sphere", C.c_uint64), ("bound_evals_triangle", C.c_uint64), ("bound_evals_cube", C.c_uint64),
+                ("hier_evals", C.c_uint64), ("exact_sphere_tests", C.c_uint64), ("exact_triangle_tests", C.c_uint64),
+                ("exact_cube_tests", C.c_uint64), ("exact_flops", C.c_double), ("executed_flops", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

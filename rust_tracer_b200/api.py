@@ -174,6 +174,72 @@ class Scene:
             pass
 
 
+class MultiScene:
+    """One scene resident on several GPUs, rendered by one call (rt_multi: the reference's single
+    blocking render::render, src/render.rs:31, for a host with 1-8 GPUs)."""
+
+    def __init__(self, desc, devices):
+        self._h = C.c_void_p()
+        self.desc = desc
+        self.devices = list(devices)
+        arr = (C.c_int32 * len(self.devices))(*self.devices)
+        check(lib().rt_multi_create(C.byref(desc.desc), arr, len(self.devices), C.byref(self._h)))
+
+    def update_materials(self, materials):
+        check(lib().rt_multi_update_materials(self._h, materials, len(materials)))
+
+    def render(self, width, height, depth, spp=1, seed=0, rows_per_tile=8, flags=0, want_f32=True, want_u8=True,
+               out_u8=None, cam=None):
+        """Whole frame into host arrays; returns (rgb_f32 | None, rgb_u8 | None, stats dict)."""
+        cam = cam if cam is not None else camera(width, height)
+        p = _params(depth, spp, seed, 0, 1, rows_per_tile, flags)
+        f = np.zeros((height, width, 3), dtype=np.float32) if want_f32 else None
+        u = np.zeros((height, width, 3), dtype=np.uint8) if want_u8 and out_u8 is None else None
+        if out_u8 is not None:
+            if out_u8.dtype != np.uint8 or out_u8.size != height * width * 3 or not out_u8.flags.c_contiguous:
+                raise ValueError("out_u8 must be a contiguous uint8 array of %d x %d x 3" % (height, width))
+            u, want_u8 = out_u8, True
+        st = abi.rt_stats()
+        check(lib().rt_multi_render(self._h, C.byref(cam), C.byref(p), f.ctypes.data if want_f32 else None,
+                                    u.ctypes.data if want_u8 else None, C.byref(st)))
+        return f, u, st.as_dict()
+
+    def render_device(self, width, height, depth, d_rgb_f32=0, d_rgb_u8=0, spp=1, seed=0, rows_per_tile=8, flags=0):
+        """Whole frame into device buffers on the first device (raw pointers), gathered by peer stores."""
+        cam = camera(width, height)
+        p = _params(depth, spp, seed, 0, 1, rows_per_tile, flags)
+        st = abi.rt_stats()
+        check(lib().rt_multi_render_device(self._h, C.byref(cam), C.byref(p), C.c_void_p(d_rgb_f32 or None),
+                                           C.c_void_p(d_rgb_u8 or None), C.byref(st)))
+        return st.as_dict()
+
+    def close(self):
+        if self._h:
+            lib().rt_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def render_multi(desc, devices, width, height, depth, spp=1, seed=0, rows_per_tile=8, out_u8=None):
+    """rt_render_multi: scene description in, RGB8 image out, on the listed devices."""
+    cam = camera(width, height)
+    p = _params(depth, spp, seed, 0, 1, rows_per_tile, 0)
+    u = out_u8 if out_u8 is not None else np.zeros((height, width, 3), dtype=np.uint8)
+    arr = (C.c_int32 * len(devices))(*devices)
+    st = abi.rt_stats()
+    check(lib().rt_render_multi(C.byref(desc.desc), arr, len(devices), C.byref(cam), C.byref(p), None, u.ctypes.data, C.byref(st)))
+    return u, st.as_dict()
+
+
+def device_count():
+    return check(lib().rt_device_count())
+
+
 class Forest:
     """Device-resident ray forest (rt_forest)."""
 
@@ -230,6 +296,29 @@ class Forest:
             self.close()
         except Exception:
             pass
+
+
+class tuned:
+    """Test / tool hook (include/rt_b200_debug.h): override scheduling constants of the library for the
+    duration of a `with` block, e.g. `with rt.tuned(table_cap=128): ...`.  Never changes a result."""
+
+    def __init__(self, **knobs):
+        self.knobs = knobs
+        self.saved = {}
+
+    def __enter__(self):
+        for k, v in self.knobs.items():
+            old = lib().rt_debug_get(k.encode())
+            if old == -(1 << 63):
+                raise KeyError(k)
+            self.saved[k] = old
+            check(lib().rt_debug_set(k.encode(), int(v)))
+        return self
+
+    def __exit__(self, *exc):
+        for k, v in self.saved.items():
+            lib().rt_debug_set(k.encode(), int(v))
+        return False
 
 
 def trim(device=-1):

@@ -6,7 +6,6 @@
 #include <chrono>
 #include <climits>
 #include <cstdio>
-#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -15,12 +14,12 @@
 
 namespace rt {
 
-// RT_B200_TRACE: wall-clock laps of the host side of a call
+// tuning().trace: wall-clock laps of the host side of a call
 struct HostLap {
     const char *call;
     bool on;
     std::chrono::steady_clock::time_point t;
-    explicit HostLap(const char *c) : call(c), on(std::getenv("RT_B200_TRACE") != nullptr), t(std::chrono::steady_clock::now()) {}
+    explicit HostLap(const char *c) : call(c), on(tuning().trace != 0), t(std::chrono::steady_clock::now()) {}
     void operator()(const char *what) {
         if (!on) return;
         auto n = std::chrono::steady_clock::now();
@@ -31,7 +30,7 @@ struct HostLap {
 
 // ---- workspace --------------------------------------------------------------------------
 
-constexpr int BATCH_COUNTERS = 8192; // one per sweep launch of a band: (depth + 1 <= 31) x (1 + lights) x table chunks
+constexpr int BATCH_COUNTERS_MIN = 1024; // one work counter per sweep launch of a band: (depth + 1) x (1 + lights) x table chunks
 
 template <typename T> static int dev_alloc(T **p, size_t n, const char *what) {
     *p = nullptr;
@@ -66,7 +65,7 @@ void Workspace::release() {
     if (h_counters) cudaFreeHost(h_counters);
     h_counters = nullptr;
     cudaFree(exact_counter); exact_counter = nullptr;
-    cudaFree(batch_counters); batch_counters = nullptr;
+    cudaFree(batch_counters); batch_counters = nullptr; batch_cap = 0;
     cudaFree(out_f32); cudaFree(out_u8);
     out_f32 = out_u8 = nullptr; out_f32_cap = out_u8_cap = 0;
     cudaFree(tables); tables = nullptr; tables_cap = 0;
@@ -162,12 +161,21 @@ int Workspace::ensure_mask(long long n) {
     return rc;
 }
 
+int Workspace::ensure_batch_counters(int n) {
+    n = std::max(n, BATCH_COUNTERS_MIN);
+    if (batch_counters && batch_cap >= n) return RT_OK;
+    cudaFree(batch_counters);
+    batch_counters = nullptr; batch_cap = 0;
+    int rc = dev_alloc(&batch_counters, (size_t)n, "batch_counters");
+    if (rc == RT_OK) batch_cap = n;
+    return rc;
+}
+
 int Workspace::ensure_misc() {
     int rc;
     if (!pools.counters && (rc = dev_alloc(&pools.counters, N_COUNTERS, "counters"))) return rc;
     if (!pools.bins && (rc = dev_alloc(&pools.bins, NODE_BINS + 2, "bins"))) return rc;
     if (!exact_counter && (rc = dev_alloc(&exact_counter, N_SWEEP_COUNTERS, "exact_counter"))) return rc;
-    if (!batch_counters && (rc = dev_alloc(&batch_counters, BATCH_COUNTERS, "batch_counters"))) return rc;
     if (!h_counters) {
         cudaError_t e = cudaMallocHost((void **)&h_counters, N_COUNTERS * sizeof(unsigned int) + N_SWEEP_COUNTERS * sizeof(unsigned long long));
         if (e != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
@@ -220,27 +228,25 @@ struct Accum {
     std::vector<long long> sweep_rays; // rays of each span (RT_B200_TRACE)
     std::vector<unsigned long long> sweep_counts; // device counters after each span: exact, general evals, origin evals (trace only)
     double filter_fma = 0.0;           // FMAs executed by the sweeps' filters
-    unsigned long long slot_evals = 0; // (ray, bound slot) pairs the filters evaluated one by one
+    unsigned long long slot_evals[MAX_SEGS] = {0, 0, 0, 0}; // (ray, bound slot) pairs the filters evaluated one by one, per table segment
+    unsigned long long all_evals = 0;  // spheres of every level (slots, groups, quads) the filters evaluated
+    unsigned long long exact_sphere = 0, exact_triangle = 0; // exact tests by kind (the rest of `exact` are cubes)
     bool audit = false;                // RT_FLAG_AUDIT_ALL_PAIRS: every pair went through the exact test
 };
 
 // exact-test count and filter counts of the sweeps, from the device counters read back into
 // ws.h_counters + N_COUNTERS: [0] exact tests, [1] spheres evaluated by the general filter, [2] by the
-// origin filter (bounds, group and quad spheres alike), [3] of those, evaluations of bound slots
+// origin filter (bounds, group and quad spheres alike), [3 + g] of those, evaluations of bound slots of
+// segment g, [7], [8] exact tests of spheres / triangles
 static void read_sweep_counters(const Workspace &ws, Accum &acc) {
     unsigned long long c[N_SWEEP_COUNTERS];
     std::memcpy(c, ws.h_counters + N_COUNTERS, sizeof(c));
     acc.exact = c[0];
     acc.filter_fma = (double)c[1] * FILTER_FMA_GENERAL + (double)c[2] * FILTER_FMA_ORIGIN;
-    acc.slot_evals = c[3];
-}
-
-static int env_int(const char *name, int dflt, int lo, int hi) {
-    const char *e = std::getenv(name);
-    if (!e) return dflt;
-    long v = std::atol(e);
-    if (v < lo || v > hi) return dflt;
-    return (int)v;
+    acc.all_evals = c[1] + c[2];
+    for (int g = 0; g < MAX_SEGS; ++g) acc.slot_evals[g] = c[3 + g];
+    acc.exact_sphere = c[3 + MAX_SEGS];
+    acc.exact_triangle = c[4 + MAX_SEGS];
 }
 
 #define CK(call, what)                                        \
@@ -256,15 +262,20 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     const DevScene &sc = scene->dev;
     cudaStream_t st = scene->stream;
     Pools &p = ws.pools;
-    const int rpt = env_int("RT_B200_RAYS_PER_THREAD", 0, 0, 4);
     const bool audit = (flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
-    const bool trace = std::getenv("RT_B200_TRACE") != nullptr;
+    const bool trace = tuning().trace != 0;
     lv = BandLevels();
     lv.light_major = !audit && !scene->light_tabs.empty() && scene->cam.bound; // = by_origin below: spawn runs ordered
 
     unsigned int init[N_COUNTERS] = {(unsigned int)n, 0u, 0u, 0u, 0u, 0u};
     CK(cudaMemcpyAsync(p.counters, init, sizeof(init), cudaMemcpyHostToDevice, st), "counters init");
-    CK(cudaMemsetAsync(ws.batch_counters, 0, BATCH_COUNTERS * sizeof(unsigned int), st), "batch counters");
+    { // a counter per sweep launch: every level sweeps its tree rays and each light's shadow rays, chunk by chunk
+        const long long need = (long long)(fp.depth + 2) * (1 + std::max(sc.n_point_lights, 0)) * sweep_table_chunks(sc);
+        if (need > (1 << 24)) return fail(RT_ERR_UNSUPPORTED, "depth %d x %d lights x %d table chunks: too many sweep launches per band", fp.depth, sc.n_point_lights, sweep_table_chunks(sc));
+        int rc = ws.ensure_batch_counters((int)need);
+        if (rc != RT_OK) return rc;
+    }
+    CK(cudaMemsetAsync(ws.batch_counters, 0, (size_t)ws.batch_cap * sizeof(unsigned int), st), "batch counters");
     ws.batch_next = 0;
     cudaError_t sweep_err = cudaSuccess;
     launch_raygen(fp, p, sample0, n, st);
@@ -281,8 +292,8 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         if (audit) launch_sweep_all_pairs(sc, a, b, ws.exact_counter, on);
         else {
             int used = 0;
-            cudaError_t e = launch_sweep(sc, a, b, ot, rpt, scene->sm_count, ws.batch_counters + ws.batch_next,
-                                         BATCH_COUNTERS - ws.batch_next, &used, ws.exact_counter, on);
+            cudaError_t e = launch_sweep(sc, a, b, ot, scene->sm_count, ws.batch_counters + ws.batch_next,
+                                         ws.batch_cap - ws.batch_next, &used, ws.exact_counter, on);
             ws.batch_next += used;
             scene->launches += used > 0 ? used - 1 : 0;
             if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
@@ -310,8 +321,8 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     // (one column of the [node][light] pool) against that light's; the rest as one general sweep.
     const bool by_origin = !audit && !scene->light_tabs.empty() && scene->cam.bound;
     const int npl = std::max(sc.n_point_lights, 1);
-    const bool merge_lights = env_int("RT_B200_MERGE_LIGHTS", 1, 0, 1) != 0;
-    const int heavy_allow = env_int("RT_B200_HEAVY_ALLOW", 65536, 0, 1 << 24);
+    const bool merge_lights = tuning().merge_lights != 0;
+    const int heavy_allow = tuning().heavy_allow;
     // heavy_tree / heavy_nodes: how many of the level's first tree rays / of the previous level's
     // first nodes start far outside the scene (counters[4], [5]); their sweeps get finer work items
     auto sweep_level = [&](int level, int tb, int te, int sb, int se, int heavy_tree, int heavy_nodes) {
@@ -358,8 +369,8 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
                 std::vector<RaySeg> segs;
                 for (int l = 0; l < sc.n_point_lights; ++l) segs.push_back(light_seg(l));
                 int used = 0;
-                cudaError_t e = launch_sweep_jobs(sc, segs.data(), scene->light_tabs.data(), sc.n_point_lights, rpt, scene->sm_count,
-                                                  ws.batch_counters + ws.batch_next, BATCH_COUNTERS - ws.batch_next, &used,
+                cudaError_t e = launch_sweep_jobs(sc, segs.data(), scene->light_tabs.data(), sc.n_point_lights, scene->sm_count,
+                                                  ws.batch_counters + ws.batch_next, ws.batch_cap - ws.batch_next, &used,
                                                   ws.exact_counter, stream_for());
                 if (e == cudaSuccess) {
                     merged = true;
@@ -439,14 +450,10 @@ static long long worst_case_tree_rays(long long n, int depth) {
 }
 
 
-struct Outputs {
-    float *d_f32 = nullptr;        // device, may be null
-    unsigned char *d_u8 = nullptr; // device, may be null
-};
-
 static void fill_stats(rt_scene *scene, const Accum &acc, unsigned long long pixels, rt_stats *st) {
     std::memset(st, 0, sizeof(*st));
-    const int *c = scene->counts;
+    const HostScene &hs = *scene->host;
+    const int *c = hs.counts;
     unsigned long long rays = acc.tree_rays + acc.shadow_rays;
     st->pixels = pixels;
     st->rays = rays;
@@ -456,21 +463,44 @@ static void fill_stats(rt_scene *scene, const Accum &acc, unsigned long long pix
     st->plane_tests = rays * (unsigned long long)c[RT_SHAPE_PLANE];
     st->triangle_tests = rays * (unsigned long long)c[RT_SHAPE_TRIANGLE];
     st->cube_tests = rays * (unsigned long long)c[RT_SHAPE_CUBE];
-    st->exact_tests = acc.exact + st->plane_tests;
     // sphere 54, triangle 30, plane 47 (14 when inv is the identity), cube 33 + 12*30,
     // node 60 + 70 L
-    double per_ray = 54.0 * c[RT_SHAPE_SPHERE] + 30.0 * c[RT_SHAPE_TRIANGLE] + 393.0 * c[RT_SHAPE_CUBE] +
-                     47.0 * (c[RT_SHAPE_PLANE] - scene->planes_identity) + 14.0 * scene->planes_identity;
+    const double plane_flop = 47.0 * (c[RT_SHAPE_PLANE] - hs.planes_identity) + 14.0 * hs.planes_identity;
+    double per_ray = 54.0 * c[RT_SHAPE_SPHERE] + 30.0 * c[RT_SHAPE_TRIANGLE] + 393.0 * c[RT_SHAPE_CUBE] + plane_flop;
     st->algorithmic_flops = (double)rays * per_ray + (double)acc.nodes * (60.0 + 70.0 * scene->dev.n_lights);
     st->filter_flops = 2.0 * acc.filter_fma;
-    // pairs resolved one by one: bound slots the filters evaluated (pads scaled out) + every plane;
-    // the audit sweeps resolve every pair that way
-    const int nb = scene->dev.n_bounded, ns = scene->dev.n_slots;
-    st->tested_pairs = acc.audit ? rays * (unsigned long long)(nb + c[RT_SHAPE_PLANE])
-                             : (unsigned long long)((double)acc.slot_evals * (ns ? (double)nb / ns : 0.0)) + st->plane_tests;
+    if (acc.audit) { // every pair through the exact test, no filter
+        st->exact_sphere_tests = st->sphere_tests;
+        st->exact_triangle_tests = st->triangle_tests;
+        st->exact_cube_tests = st->cube_tests;
+        st->exact_tests = rays * (unsigned long long)scene->dev.n_shapes;
+        st->tested_pairs = st->exact_tests;
+    } else {
+        // pairs whose own bound the filter evaluated, by kind: the segment's evaluations with its pads scaled out
+        unsigned long long slot_pairs = 0, slot_all = 0;
+        for (int g = 0; g < scene->dev.segs.n; ++g) {
+            const int slots = scene->dev.segs.end[g] - scene->dev.segs.begin[g];
+            const unsigned long long real = slots ? (unsigned long long)((double)acc.slot_evals[g] * hs.seg_real[g] / slots) : 0ull;
+            if (hs.seg_kind[g] == RT_SHAPE_SPHERE) st->bound_evals_sphere += real;
+            else if (hs.seg_kind[g] == RT_SHAPE_TRIANGLE) st->bound_evals_triangle += real;
+            else st->bound_evals_cube += real;
+            slot_pairs += real;
+            slot_all += acc.slot_evals[g];
+        }
+        st->hier_evals = acc.all_evals - slot_all;
+        st->exact_sphere_tests = acc.exact_sphere;
+        st->exact_triangle_tests = acc.exact_triangle;
+        st->exact_cube_tests = acc.exact - acc.exact_sphere - acc.exact_triangle;
+        st->exact_tests = acc.exact + st->plane_tests;
+        // pairs resolved one by one: a bound-slot evaluation or an exact test (every plane)
+        st->tested_pairs = slot_pairs + st->plane_tests;
+    }
+    st->exact_flops = 54.0 * (double)st->exact_sphere_tests + 30.0 * (double)st->exact_triangle_tests +
+                      393.0 * (double)st->exact_cube_tests + (double)rays * plane_flop;
+    st->executed_flops = st->filter_flops + st->exact_flops;
 }
 
-static int check_params(const rt_scene *scene, const rt_camera *cam, const rt_render_params *pr) {
+int check_params(const rt_scene *scene, const rt_camera *cam, const rt_render_params *pr) {
     if (!scene || !cam || !pr) return fail(RT_ERR_INVALID, "null argument");
     if (cam->x_res <= 0 || cam->y_res <= 0) return fail(RT_ERR_INVALID, "resolution %dx%d", cam->x_res, cam->y_res);
     if (pr->depth < 0 || pr->depth > 30) return fail(RT_ERR_INVALID, "depth %d not in 0..30", pr->depth);
@@ -509,18 +539,41 @@ static int cast_band_sized(rt_scene *scene, Workspace &ws, const FrameParams &fp
     const long long worst = worst_case_tree_rays(n, std::max(fp.depth, 1));
     const int npl = std::max(scene->dev.n_point_lights, 0);
     long long t_cap = std::max<long long>(ws.pools.t_cap, std::min<long long>(worst, std::max<long long>((long long)n * 3, 1 << 16)));
+    const size_t spans0 = acc.sweep_spans.size(), counts0 = acc.sweep_counts.size();
     for (;;) {
         int rc = ws.ensure_pools(t_cap, t_cap * npl);
         if (rc != RT_OK) return rc;
         rc = cast_band(scene, ws, fp, sample0, n, flags, lv, acc, events);
         if (rc <= 0) return rc;
-        cudaMemsetAsync(ws.exact_counter, 0, N_SWEEP_COUNTERS * sizeof(unsigned long long), scene->stream); // the band is recast
+        cudaMemsetAsync(ws.exact_counter, 0, N_SWEEP_COUNTERS * sizeof(unsigned long long), scene->stream); // the band is recast:
+        acc.sweep_spans.resize(spans0); acc.sweep_rays.resize(spans0); acc.sweep_counts.resize(counts0); // its aborted sweeps do not count
         if (t_cap >= worst) return fail(RT_ERR_INTERNAL, "ray pool overflow at the worst-case size");
         t_cap = std::min(worst, t_cap * 2);
     }
 }
 
-static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_params *pr, Outputs out, rt_stats *stats) {
+// Device staging buffers of n_ch channels for a host-buffer call (kept with the workspace).
+int ensure_staging(rt_scene *scene, size_t n_ch, bool want_f32, bool want_u8) {
+    Workspace &ws = scene->ws;
+    int rc;
+    if (want_f32 && ws.out_f32_cap < n_ch * sizeof(float)) {
+        cudaFree(ws.out_f32);
+        ws.out_f32 = nullptr; ws.out_f32_cap = 0;
+        float *p;
+        if ((rc = dev_alloc(&p, n_ch, "out_f32")) != RT_OK) return rc;
+        ws.out_f32 = p; ws.out_f32_cap = n_ch * sizeof(float);
+    }
+    if (want_u8 && ws.out_u8_cap < n_ch) {
+        cudaFree(ws.out_u8);
+        ws.out_u8 = nullptr; ws.out_u8_cap = 0;
+        unsigned char *p;
+        if ((rc = dev_alloc(&p, n_ch, "out_u8")) != RT_OK) return rc;
+        ws.out_u8 = p; ws.out_u8_cap = n_ch;
+    }
+    return RT_OK;
+}
+
+int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_params *pr, Outputs out, rt_stats *stats) {
     int rc = check_params(scene, cam, pr);
     if (rc != RT_OK) return rc;
     CK(cudaSetDevice(scene->device), "cudaSetDevice");
@@ -544,7 +597,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
     cudaEventRecord(ev0, st);
 
     Accum acc;
-    long long band = env_int("RT_B200_BAND_SAMPLES", 1 << 23, 1 << 10, 1 << 28);
+    long long band = tuning().band_samples;
     if (n_samples > 0) {
         long long nb = (n_samples + band - 1) / band;
         band = (n_samples + nb - 1) / nb;
@@ -578,7 +631,7 @@ static int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_pa
         fill_stats(scene, acc, (unsigned long long)n_pixels, stats);
         float ms = 0.f, sweep = 0.f;
         cudaEventElapsedTime(&ms, ev0, ev1);
-        const bool trace = std::getenv("RT_B200_TRACE") != nullptr;
+        const bool trace = tuning().trace != 0;
         for (size_t i = 0; i < acc.sweep_spans.size(); ++i) {
             float t = 0.f;
             cudaEventElapsedTime(&t, acc.sweep_spans[i].first, acc.sweep_spans[i].second);
@@ -628,20 +681,7 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *
     Workspace &ws = scene->ws;
     int32_t n_rows = rt_tile_rows_for_rank(camera->y_res, params->rank, params->world, params->tile_rows, nullptr, 0);
     size_t n_ch = (size_t)n_rows * (size_t)camera->x_res * 3;
-    if (rgb_f32 && ws.out_f32_cap < n_ch * sizeof(float)) {
-        cudaFree(ws.out_f32);
-        ws.out_f32 = nullptr; ws.out_f32_cap = 0;
-        float *p;
-        if ((rc = dev_alloc(&p, n_ch, "out_f32")) != RT_OK) return rc;
-        ws.out_f32 = p; ws.out_f32_cap = n_ch * sizeof(float);
-    }
-    if (rgb_u8 && ws.out_u8_cap < n_ch) {
-        cudaFree(ws.out_u8);
-        ws.out_u8 = nullptr; ws.out_u8_cap = 0;
-        unsigned char *p;
-        if ((rc = dev_alloc(&p, n_ch, "out_u8")) != RT_OK) return rc;
-        ws.out_u8 = p; ws.out_u8_cap = n_ch;
-    }
+    if ((rc = ensure_staging(scene, n_ch, rgb_f32 != nullptr, rgb_u8 != nullptr)) != RT_OK) return rc;
     Outputs out;
     out.d_f32 = rgb_f32 ? (float *)ws.out_f32 : nullptr;
     out.d_u8 = rgb_u8 ? (unsigned char *)ws.out_u8 : nullptr;
@@ -668,6 +708,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
     rt_forest *f = new (std::nothrow) rt_forest();
     if (!f) return fail(RT_ERR_NOMEM, "out of host memory");
     f->scene = scene;
+    scene->forests += 1; // the forest uses the scene's tables and stream until it is destroyed
     f->ws = workspace_take_cached(scene->device);
     Workspace &ws = f->ws;
     std::vector<int> rows;
@@ -732,9 +773,12 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
 
 void rt_forest_destroy(rt_forest *forest) {
     if (!forest) return;
-    if (forest->scene) {
-        cudaSetDevice(forest->scene->device);
-        workspace_give_cached(forest->scene->device, forest->ws);
+    rt_scene *scene = forest->scene;
+    if (scene) {
+        cudaSetDevice(scene->device);
+        workspace_give_cached(scene->device, forest->ws);
+        scene->forests -= 1;
+        if (scene->forests == 0 && scene->destroy_pending) scene_free(scene); // rt_scene_destroy came first
     } else {
         forest->ws.release();
     }
@@ -774,7 +818,13 @@ static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *i
     cudaEventRecord(ev0, st);
     const unsigned char *mask = nullptr;
     uint64_t evaluated = (uint64_t)n;
-    int *d_ids = nullptr;
+    struct Temps { // freed on every way out
+        int *d_ids = nullptr;
+        float *d_f32 = nullptr;
+        unsigned char *d_u8 = nullptr;
+        ~Temps() { cudaFree(d_ids); cudaFree(d_f32); cudaFree(d_u8); }
+    } tmp;
+    int *&d_ids = tmp.d_ids;
     if (filtered) {
         if ((rc = ws.ensure_mask(n)) != RT_OK) return rc;
         CK(cudaMemsetAsync(ws.mask, 0, (size_t)std::max(n, 1), st), "mask clear");
@@ -793,8 +843,8 @@ static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *i
     lv.light_major = f->light_major;
     if ((rc = shade_band(scene, sc, ws, f->fp, lv, mask)) != RT_OK) return rc;
     size_t n_ch = (size_t)n * 3;
-    float *d_f32 = nullptr;
-    unsigned char *d_u8 = nullptr;
+    float *&d_f32 = tmp.d_f32;
+    unsigned char *&d_u8 = tmp.d_u8;
     if (rgb_f32 && n_ch) {
         CK(cudaMalloc((void **)&d_f32, n_ch * sizeof(float)), "cudaMalloc(out)");
         if (filtered) CK(cudaMemcpyAsync(d_f32, rgb_f32, n_ch * sizeof(float), cudaMemcpyHostToDevice, st), "H2D inout");
@@ -813,7 +863,6 @@ static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *i
         CK(cudaMemcpyAsync(hmask.data(), ws.mask, (size_t)n, cudaMemcpyDeviceToHost, st), "D2H mask");
     }
     CK(cudaStreamSynchronize(st), "forest eval");
-    cudaFree(d_f32); cudaFree(d_u8); cudaFree(d_ids);
     CK(cudaGetLastError(), "forest eval");
     if (filtered) {
         evaluated = 0;

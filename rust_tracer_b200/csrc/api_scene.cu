@@ -13,10 +13,16 @@
 #include <vector>
 
 #include "api_internal.h"
+#include "../../include/rt_b200_debug.h"
 
 namespace rt {
 
 static thread_local char g_err[512] = "";
+
+Tuning &tuning() {
+    static Tuning t;
+    return t;
+}
 
 int fail(int code, const char *fmt, ...) {
     va_list ap;
@@ -33,18 +39,14 @@ int cuda_fail(cudaError_t e, const char *what) {
 // ---- host-side data parallelism ----------------------------------------------------------
 // The scene build walks a few thousand to a few hundred thousand records several times
 // (slot order, group spheres, one re-centred table per light and per camera position); with a
-// 50 ms frame behind it that is worth a handful of threads.  RT_B200_HOST_THREADS overrides.
+// 50 ms frame behind it that is worth a handful of threads (tuning.h: host_threads).
 constexpr int MAX_HOST_CHUNKS = 8;
 
 static int host_threads() {
-    static const int n = [] {
-        int want = 4;
-        if (const char *e = std::getenv("RT_B200_HOST_THREADS")) want = std::atoi(e);
-        const int hw = (int)std::thread::hardware_concurrency();
-        if (hw > 0) want = std::min(want, hw);
-        return std::max(1, std::min(want, MAX_HOST_CHUNKS));
-    }();
-    return n;
+    static const int hw = (int)std::thread::hardware_concurrency();
+    int want = tuning().host_threads;
+    if (hw > 0) want = std::min(want, hw);
+    return std::max(1, std::min(want, MAX_HOST_CHUNKS));
 }
 
 // fn(chunk, begin, end) over [0, n) in at most host_threads() chunks of at least min_chunk.
@@ -128,14 +130,9 @@ static float round_up_f32(double x) {
     return f;
 }
 
-static float tri_bound_scale() {
-    const char *e = std::getenv("RT_B200_TRI_BOUND_SCALE");
-    if (e) {
-        double v = std::atof(e);
-        if (v >= 1.0 && v <= 64.0) return (float)v;
-    }
-    return 1.5f;
-}
+// Radius of a triangle's (and a cube's) bound over its circumradius about the centroid: a
+// correctness margin ("filter margins"), a constant of the library.
+constexpr double TRI_BOUND_SCALE = 1.5;
 
 static float round_down_f32(double x) {
     float f = (float)x;
@@ -225,14 +222,10 @@ static float seg_margin(double aniso) { return round_up_f32(1.5 * (57.0 + 15.0 *
 // Its share for the reference's exact test alone (origin tables, sweep.cu: ray_coef_origin).
 static float seg_margin_exact(double aniso) { return round_up_f32(1.5 * (25.0 + 15.0 * aniso * aniso)); }
 
-static bool origin_tables_wanted(int n_slots) {
-    if (const char *e = std::getenv("RT_B200_NO_ORIGIN")) if (std::atoi(e)) return false;
-    int min_slots = 256; // below this a sweep is launch-bound and one general launch per level is cheaper
-    if (const char *e = std::getenv("RT_B200_ORIGIN_MIN_SLOTS")) min_slots = std::atoi(e);
-    return n_slots >= min_slots;
-}
+// Below origin_min_slots a sweep is launch-bound and one general launch per level is cheaper.
+static bool origin_tables_wanted(int n_slots) { return tuning().origin_tables != 0 && n_slots >= tuning().origin_min_slots; }
 
-void build_origin_table(const rt_scene *scene, const float o[3], std::vector<float4> &out, OriginTable *tab, bool toward) {
+void build_origin_table(const HostScene &hs, const float o[3], std::vector<float4> &out, OriginTable *tab, bool toward) {
     struct S { float x, y, z, w; };
     auto one = [&](const HostSlot &h, double &rmax, bool &clip) {
         if (h.kind == 1) return S{0.f, 0.f, 0.f, 3.402823466e+38f};
@@ -251,7 +244,7 @@ void build_origin_table(const rt_scene *scene, const float o[3], std::vector<flo
         return S{0.f, 0.f, 0.f, -3.402823466e+38f};
     };
     // slots, then groups, then quads (each paired); rmax (the far clip of slot tests) is the slots' alone
-    const size_t ns = scene->slots.size(), ng = scene->groups.size(), nq = scene->quads.size();
+    const size_t ns = hs.slots.size(), ng = hs.groups.size(), nq = hs.quads.size();
     out.resize(ns + ng + nq);
     bool clip = toward;
     auto fill = [&](const std::vector<HostSlot> &v, float4 *dst) { // returns the largest radius
@@ -274,28 +267,38 @@ void build_origin_table(const rt_scene *scene, const float o[3], std::vector<flo
         for (int c = 0; c < MAX_HOST_CHUNKS; ++c) { r = std::max(r, rm[c]); clip = clip && cl[c]; }
         return r;
     };
-    const double rmax_slots = fill(scene->slots, out.data());
-    fill(scene->groups, out.data() + ns);
-    fill(scene->quads, out.data() + ns + ng);
+    const double rmax_slots = fill(hs.slots, out.data());
+    fill(hs.groups, out.data() + ns);
+    fill(hs.quads, out.data() + ns + ng);
     double on = std::sqrt((double)o[0] * o[0] + (double)o[1] * o[1] + (double)o[2] * o[2]);
-    double r = (on + (double)scene->dev.cmax) * (1.0 + 1e-6);
+    double r = (on + (double)hs.dev.cmax) * (1.0 + 1e-6);
     tab->reach = std::isfinite(r) && r < 3e38 ? round_up_f32(r) : 3.0e38f;
     tab->ox = o[0]; tab->oy = o[1]; tab->oz = o[2];
     tab->rmax = (clip && rmax_slots > 0.0 && rmax_slots < 1e15) ? round_up_f32(rmax_slots * (1.0 + 1e-6)) : 0.f;
+    tab->shadow = toward ? 1 : 0;
 }
 
 int prepare_camera_table(rt_scene *scene, const float origin[3]) {
     if (!scene->cam_tab) return RT_OK; // origin tables are off for this scene
     if (scene->cam.bound && std::memcmp(scene->cam_origin, origin, 3 * sizeof(float)) == 0) return RT_OK;
-    std::vector<float4> host;
+    const HostScene &hs = *scene->host;
     OriginTable t;
-    build_origin_table(scene, origin, host, &t, false);
-    cudaError_t e = cudaMemcpyAsync(scene->cam_tab, host.data(), host.size() * sizeof(float4), cudaMemcpyHostToDevice, scene->stream);
+    cudaError_t e;
+    { // the devices of a multi-GPU scene share the host copy: the first one to ask builds it
+        std::lock_guard<std::mutex> lock(hs.cam_mu);
+        if (!hs.cam_valid || std::memcmp(hs.cam_origin, origin, 3 * sizeof(float)) != 0) {
+            build_origin_table(hs, origin, hs.cam_host, &hs.cam_tab, false);
+            std::memcpy(hs.cam_origin, origin, 3 * sizeof(float));
+            hs.cam_valid = true;
+        }
+        t = hs.cam_tab;
+        e = cudaMemcpyAsync(scene->cam_tab, hs.cam_host.data(), hs.cam_host.size() * sizeof(float4), cudaMemcpyHostToDevice, scene->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(scene->stream); // cam_host may be rebuilt once the lock is gone
+    }
     if (e != cudaSuccess) return cuda_fail(e, "camera table upload");
-    if ((e = cudaStreamSynchronize(scene->stream)) != cudaSuccess) return cuda_fail(e, "camera table upload");
     t.bound = scene->cam_tab;
-    t.group = scene->cam_tab + scene->slots.size();
-    t.quad = t.group + scene->groups.size();
+    t.group = scene->cam_tab + hs.slots.size();
+    t.quad = t.group + hs.groups.size();
     scene->cam = t;
     std::memcpy(scene->cam_origin, origin, 3 * sizeof(float));
     return RT_OK;
@@ -405,72 +408,37 @@ static void cube_tris(std::vector<float4> &out) {
     }
 }
 
-} // namespace rt
+// ---- scene build (host only) -----------------------------------------------------------------
 
-using namespace rt;
-
-extern "C" {
-
-int rt_abi_version(void) { return RT_B200_ABI_VERSION; }
-const char *rt_last_error(void) { return g_err; }
-
-int rt_device_count(void) {
-    int n = 0;
-    cudaError_t e = cudaGetDeviceCount(&n);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
-    return n;
-}
-
-void rt_camera_default(int32_t x_res, int32_t y_res, rt_camera *out) {
-    out->origin[0] = 0.f; out->origin[1] = 0.f; out->origin[2] = -8.f;
-    out->x_min = -3.f; out->x_max = 3.f; out->y_min = -3.f; out->y_max = 3.f;
-    out->x_res = x_res; out->y_res = y_res;
-}
-
-int32_t rt_tile_rows_for_rank(int32_t height, int32_t rank, int32_t world, int32_t tile_rows, int32_t *rows,
-                              int32_t cap) {
-    if (height < 0 || world < 1 || rank < 0 || rank >= world || tile_rows < 1) return fail(RT_ERR_INVALID, "bad tiling");
-    int32_t n = 0;
-    for (int32_t v = 0; v < height; ++v)
-        if ((v / tile_rows) % world == rank) {
-            if (rows && n < cap) rows[n] = v;
-            ++n;
-        }
-    return n;
-}
-
-int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
-    if (!desc || !out) return fail(RT_ERR_INVALID, "null argument");
-    const bool trace = std::getenv("RT_B200_TRACE") != nullptr; // phase times of the host-side build
+int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
+    const bool trace = tuning().trace != 0; // phase times of the host-side build
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto t_last = now();
     auto lap = [&](const char *what) {
         if (!trace) return;
         auto t = now();
-        std::fprintf(stderr, "[rt_b200] scene create: %-22s %.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t_last).count());
+        std::fprintf(stderr, "[rt_b200] scene build: %-22s %.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t_last).count());
         t_last = t;
     };
-    *out = nullptr;
     if (desc->n_shapes < 0 || desc->n_materials < 0 || desc->n_lights < 0 || (desc->n_shapes && !desc->shapes) ||
         (desc->n_materials && !desc->materials) || (desc->n_lights && !desc->lights))
         return fail(RT_ERR_INVALID, "malformed scene description");
     if (desc->n_shapes >= (1 << 24)) return fail(RT_ERR_UNSUPPORTED, "more than 2^24 shapes");
-    int ndev = 0;
-    cudaError_t e = cudaGetDeviceCount(&ndev);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount (no CPU fallback exists)");
-    if (device < 0 || device >= ndev) return fail(RT_ERR_CUDA, "CUDA device %d not present (%d devices)", device, ndev);
-    if ((e = cudaSetDevice(device)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
 
     const int n = desc->n_shapes;
-    std::vector<int4> meta(n);
-    std::vector<float4> geom(3 * (size_t)n);
-    std::vector<int> plane_shape;
-    std::vector<float4> plane_data;
-    // error class of a bound: 0 similarity-transformed spheres, 1 triangles, 2 the rest
+    std::vector<int4> &meta = hs.meta;
+    std::vector<float4> &geom = hs.geom;
+    meta.resize(n);
+    geom.resize(3 * (size_t)n);
+    std::vector<int> &plane_shape = hs.plane_shape;
+    std::vector<float4> &plane_data = hs.plane_data;
+    // error class of a bound = segment of the table: 0 similarity-transformed spheres, 1 triangles,
+    // 2 other spheres, 3 cubes (one kind of shape per segment: the sweeps count their filter
+    // evaluations per segment, rt_stats.bound_evals_*)
     struct B { Bound b; int shape; int cls; double aniso; };
+    static const int cls_kind[MAX_SEGS] = {RT_SHAPE_SPHERE, RT_SHAPE_TRIANGLE, RT_SHAPE_SPHERE, RT_SHAPE_CUBE};
     std::vector<B> bounds;
-    const float tri_scale = tri_bound_scale();
-    int counts[4] = {0, 0, 0, 0}, planes_identity = 0, first_nan = -1;
+    int *counts = hs.counts, planes_identity = 0, first_nan = -1;
 
     for (int i = 0; i < n; ++i) {
         const rt_shape &s = desc->shapes[i];
@@ -490,7 +458,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
             if (!world_extent(iv, c, stretch, aniso)) return fail(RT_ERR_INVALID, "shape %d: singular inverse transform", i);
             if (s.kind == RT_SHAPE_SPHERE)
                 bounds.push_back({make_bound(c, stretch, 1.0 + 1e-4), i, aniso <= 1.001 ? 0 : 2, aniso});
-            else bounds.push_back({make_bound(c, stretch * 0.8660254037844387, tri_scale), i, 2, aniso});
+            else bounds.push_back({make_bound(c, stretch * 0.8660254037844387, TRI_BOUND_SCALE), i, 3, aniso});
             if (first_nan < 0) first_nan = i;
             break;
         case RT_SHAPE_TRIANGLE: {
@@ -503,7 +471,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
                 r = std::max(r, std::sqrt(dx * dx + dy * dy + dz * dz));
             }
             if (!std::isfinite(r)) return fail(RT_ERR_INVALID, "shape %d: non-finite triangle", i);
-            bounds.push_back({make_bound(c, r, tri_scale), i, 1, 1.0});
+            bounds.push_back({make_bound(c, r, TRI_BOUND_SCALE), i, 1, 1.0});
             if (first_nan < 0) first_nan = i;
             break;
         }
@@ -525,6 +493,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         }
         }
     }
+    hs.planes_identity = planes_identity;
     // segments by error class, each padded to SEG_PAD slots; within a class the bounds are put in
     // the leaf order of a median-split tree whose leaves hold exactly GROUP_SLOTS bounds, so that
     // the slots of a group are neighbours in space; slot pairs interleaved for FFMA2
@@ -592,7 +561,7 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
     SweepSegs segs;
     std::memset(&segs, 0, sizeof(segs));
     std::vector<Bound> slots;
-    std::vector<int> bound_shape;
+    std::vector<int> &bound_shape = hs.bound_shape;
     double cmax = 0.0;
     const Bound pad = {0.f, 0.f, 0.f, 3.402823466e+38f, 0.0}; // passes no ray
     for (int j = 0; j < nb;) {
@@ -600,11 +569,13 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         double aniso = 1.0;
         int g = segs.n++;
         segs.begin[g] = (int)slots.size();
+        hs.seg_kind[g] = cls_kind[cls];
         for (; j < nb && bounds[j].cls == cls; ++j) {
             slots.push_back(bounds[j].b);
             bound_shape.push_back(bounds[j].shape);
             aniso = std::max(aniso, bounds[j].aniso);
             cmax = std::max(cmax, bounds[j].b.reach);
+            hs.seg_real[g]++;
         }
         while (slots.size() % SEG_PAD) { slots.push_back(pad); bound_shape.push_back(-1); }
         segs.end[g] = (int)slots.size();
@@ -646,19 +617,20 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         }
         return out;
     };
-    std::vector<float4> bound = paired(slots), group = paired(groups), quad = paired(quads);
-    std::vector<int2> slot_meta(n_slots);
-    std::vector<float4> slot_geom(3 * (size_t)n_slots, make_float4(0.f, 0.f, 0.f, 0.f));
+    hs.bound = paired(slots); hs.group = paired(groups); hs.quad = paired(quads);
+    hs.slot_meta.resize(n_slots);
+    hs.slot_geom.assign(3 * (size_t)n_slots, make_float4(0.f, 0.f, 0.f, 0.f));
     for (int j = 0; j < n_slots; ++j) {
         const int sh = bound_shape[j];
-        slot_meta[j] = make_int2(sh >= 0 ? meta[sh].x : -1, sh);
-        if (sh >= 0) for (int k = 0; k < 3; ++k) slot_geom[3 * (size_t)j + k] = geom[3 * (size_t)sh + k];
+        hs.slot_meta[j] = make_int2(sh >= 0 ? meta[sh].x : -1, sh);
+        if (sh >= 0) for (int k = 0; k < 3; ++k) hs.slot_geom[3 * (size_t)j + k] = geom[3 * (size_t)sh + k];
     }
 
-    std::vector<DevMaterial> mats;
-    int rc = convert_materials(desc->materials, desc->n_materials, mats);
+    int rc = convert_materials(desc->materials, desc->n_materials, hs.materials);
     if (rc != RT_OK) return rc;
-    std::vector<DevLight> lights(desc->n_lights);
+    hs.n_materials = desc->n_materials;
+    std::vector<DevLight> &lights = hs.lights;
+    lights.resize(desc->n_lights);
     int n_point = 0;
     for (int l = 0; l < desc->n_lights; ++l) {
         const rt_light &L = desc->lights[l];
@@ -668,17 +640,10 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
         lights[l].cr = L.color[0]; lights[l].cg = L.color[1]; lights[l].cb = L.color[2];
         lights[l].point_index = (L.kind == RT_LIGHT_POINT) ? n_point++ : -1;
     }
-    std::vector<float4> ctris;
-    cube_tris(ctris);
-
+    cube_tris(hs.cube_tris);
     lap("slot tables, materials");
-    rt_scene *s = new (std::nothrow) rt_scene();
-    if (!s) return fail(RT_ERR_NOMEM, "out of host memory");
-    s->device = device;
-    s->n_materials = desc->n_materials;
-    s->counts[0] = counts[0]; s->counts[1] = counts[1]; s->counts[2] = counts[2]; s->counts[3] = counts[3];
-    s->planes_identity = planes_identity;
-    DevScene &d = s->dev;
+
+    DevScene &d = hs.dev;
     std::memset(&d, 0, sizeof(d));
     d.n_shapes = n; d.n_bounded = nb; d.n_planes = (int)plane_shape.size();
     d.n_slots = n_slots; d.segs = segs; d.cmax = round_up_f32(cmax * (1.0 + 1e-6));
@@ -696,59 +661,152 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
             d.bin_scale[a] = ok ? (float)(2.0 / ext) : 0.f; // (x - lo) * scale - 1 in [-1, 1] inside the box
         }
     }
-    cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
     d.n_lights = desc->n_lights; d.n_point_lights = n_point; d.first_nan_shape = first_nan;
     d.amb_r = desc->ambient[0]; d.amb_g = desc->ambient[1]; d.amb_b = desc->ambient[2];
-    if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) {
-        rt_scene_destroy(s);
-        return cuda_fail(e, "cudaStreamCreate");
-    }
-    s->own_stream = s->stream;
-    lap("stream");
-    const DevMaterial *dm = nullptr;
-    Arena arena;
-    arena.add(bound, &d.bound); arena.add(group, &d.group); arena.add(quad, &d.quad);
-    arena.add(bound_shape, &d.bound_shape); arena.add(slot_meta, &d.slot_meta); arena.add(slot_geom, &d.slot_geom);
-    arena.add(meta, &d.shape_meta); arena.add(geom, &d.geom);
-    arena.add(plane_shape, &d.plane_shape); arena.add(plane_data, &d.plane_data);
-    arena.add(ctris, &d.cube_tris); arena.add(mats, &dm); arena.add(lights, &d.lights);
-    // the bound table seen from every point light, and room for the one seen from the camera
-    std::vector<std::vector<float4>> light_host(n_point);
-    const float4 *cam_tab = nullptr;
-    if (origin_tables_wanted(n_slots)) {
+
+    // the bound table seen from every point light (the one seen from the camera is built at render time)
+    hs.origin = origin_tables_wanted(n_slots);
+    if (hs.origin) {
         auto host_slot = [](const Bound &b) {
             return HostSlot{b.cx, b.cy, b.cz, b.rf, b.w == 3.402823466e+38f ? 1 : (b.w == -3.402823466e+38f ? 2 : 0)};
         };
-        s->slots.reserve(slots.size()); s->groups.reserve(groups.size()); s->quads.reserve(quads.size());
-        for (const Bound &b : slots) s->slots.push_back(host_slot(b));
-        for (const Bound &b : groups) s->groups.push_back(host_slot(b));
-        for (const Bound &b : quads) s->quads.push_back(host_slot(b));
-        s->light_tabs.resize(n_point);
+        hs.slots.reserve(slots.size()); hs.groups.reserve(groups.size()); hs.quads.reserve(quads.size());
+        for (const Bound &b : slots) hs.slots.push_back(host_slot(b));
+        for (const Bound &b : groups) hs.groups.push_back(host_slot(b));
+        for (const Bound &b : quads) hs.quads.push_back(host_slot(b));
+        hs.light_tabs.resize(n_point);
+        hs.light_host.resize(n_point);
         for (int l = 0; l < desc->n_lights; ++l) {
             if (lights[l].point_index < 0) continue;
             const float o[3] = {lights[l].px, lights[l].py, lights[l].pz};
-            OriginTable &t = s->light_tabs[lights[l].point_index];
-            build_origin_table(s, o, light_host[lights[l].point_index], &t, true);
-            arena.add(light_host[lights[l].point_index], &t.bound);
+            build_origin_table(hs, o, hs.light_host[lights[l].point_index], &hs.light_tabs[lights[l].point_index], true);
         }
-        arena.add_raw(nullptr, (size_t)(n_slots + n_groups + n_quads) * sizeof(float4), (const void **)&cam_tab);
     }
     lap("light tables");
+    return RT_OK;
+}
+
+// ---- scene upload (one device) ------------------------------------------------------------------
+
+void scene_free(rt_scene *scene) {
+    if (!scene) return;
+    cudaSetDevice(scene->device);
+    workspace_give_cached(scene->device, scene->ws);
+    for (cudaStream_t a : scene->aux) cudaStreamDestroy(a);
+    if (scene->own_stream) cudaStreamDestroy(scene->own_stream);
+    delete scene;
+}
+
+int upload_scene(const std::shared_ptr<const HostScene> &host, int device, rt_scene **out) {
+    *out = nullptr;
+    const HostScene &hs = *host;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount (no CPU fallback exists)");
+    if (device < 0 || device >= ndev) return fail(RT_ERR_CUDA, "CUDA device %d not present (%d devices)", device, ndev);
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    rt_scene *s = new (std::nothrow) rt_scene();
+    if (!s) return fail(RT_ERR_NOMEM, "out of host memory");
+    s->device = device;
+    s->host = host;
+    s->n_materials = hs.n_materials;
+    s->host_materials = hs.materials;
+    s->dev = hs.dev;
+    DevScene &d = s->dev;
+    cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        scene_free(s);
+        return cuda_fail(e, "cudaStreamCreate");
+    }
+    s->own_stream = s->stream;
+    const DevMaterial *dm = nullptr;
+    Arena arena;
+    arena.add(hs.bound, &d.bound); arena.add(hs.group, &d.group); arena.add(hs.quad, &d.quad);
+    arena.add(hs.bound_shape, &d.bound_shape); arena.add(hs.slot_meta, &d.slot_meta); arena.add(hs.slot_geom, &d.slot_geom);
+    arena.add(hs.meta, &d.shape_meta); arena.add(hs.geom, &d.geom);
+    arena.add(hs.plane_shape, &d.plane_shape); arena.add(hs.plane_data, &d.plane_data);
+    arena.add(hs.cube_tris, &d.cube_tris); arena.add(hs.materials, &dm); arena.add(hs.lights, &d.lights);
+    const float4 *cam_tab = nullptr;
+    const int n_groups = d.n_slots / GROUP_SLOTS, n_quads = d.n_slots / QUAD_SLOTS;
+    if (hs.origin) {
+        s->light_tabs = hs.light_tabs;
+        for (size_t l = 0; l < s->light_tabs.size(); ++l) arena.add(hs.light_host[l], &s->light_tabs[l].bound);
+        arena.add_raw(nullptr, (size_t)(d.n_slots + n_groups + n_quads) * sizeof(float4), (const void **)&cam_tab);
+    }
     s->ws = workspace_take_cached(device);
-    if ((rc = arena.commit(s, s->stream)) != RT_OK) {
-        rt_scene_destroy(s);
+    int rc = arena.commit(s, s->stream);
+    if (rc != RT_OK) {
+        scene_free(s);
         return rc;
     }
     d.materials = dm;
     s->d_materials = const_cast<DevMaterial *>(dm);
     for (OriginTable &t : s->light_tabs) {
-        t.group = t.bound + n_slots;
+        t.group = t.bound + d.n_slots;
         t.quad = t.group + n_groups;
     }
     s->cam_tab = const_cast<float4 *>(cam_tab);
-    lap("uploads");
     *out = s;
     return RT_OK;
+}
+
+} // namespace rt
+
+using namespace rt;
+
+extern "C" {
+
+int rt_abi_version(void) { return RT_B200_ABI_VERSION; }
+const char *rt_last_error(void) { return g_err; }
+
+int rt_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    return n;
+}
+
+void rt_camera_default(int32_t x_res, int32_t y_res, rt_camera *out) {
+    out->origin[0] = 0.f; out->origin[1] = 0.f; out->origin[2] = -8.f;
+    out->x_min = -3.f; out->x_max = 3.f; out->y_min = -3.f; out->y_max = 3.f;
+    out->x_res = x_res; out->y_res = y_res;
+}
+
+int32_t rt_tile_rows_for_rank(int32_t height, int32_t rank, int32_t world, int32_t tile_rows, int32_t *rows,
+                              int32_t cap) {
+    if (height < 0 || world < 1 || rank < 0 || rank >= world || tile_rows < 1) return fail(RT_ERR_INVALID, "bad tiling");
+    int32_t n = 0;
+    for (int32_t v = 0; v < height; ++v)
+        if ((v / tile_rows) % world == rank) {
+            if (rows && n < cap) rows[n] = v;
+            ++n;
+        }
+    return n;
+}
+
+int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out) {
+    if (!desc || !out) return fail(RT_ERR_INVALID, "null argument");
+    *out = nullptr;
+    // validate the device before the host build: "no GPU" must not cost a table build first
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    std::shared_ptr<HostScene> hs;
+    try {
+        hs = std::make_shared<HostScene>();
+    } catch (...) {
+        return fail(RT_ERR_NOMEM, "out of host memory");
+    }
+    int rc = build_host_scene(desc, *hs);
+    if (rc != RT_OK) return rc;
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount (no CPU fallback exists)");
+    if (device < 0 || device >= ndev) return fail(RT_ERR_CUDA, "CUDA device %d not present (%d devices)", device, ndev);
+    const bool trace = tuning().trace != 0;
+    auto t0 = std::chrono::steady_clock::now();
+    rc = upload_scene(hs, device, out);
+    if (trace)
+        std::fprintf(stderr, "[rt_b200] scene create: upload                 %.3f ms\n",
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    return rc;
 }
 
 int rt_scene_set_stream(rt_scene *scene, void *stream) {
@@ -763,23 +821,73 @@ int rt_scene_update_materials(rt_scene *scene, const rt_material *materials, int
     std::vector<DevMaterial> mats;
     int rc = convert_materials(materials, n, mats);
     if (rc != RT_OK) return rc;
+    if (scene->forests > 0) {
+        // A ray forest fixes which child rays exist and where they go (render_tree.rs:166-212 builds the
+        // tree once; render_ray_tree :214-255 only re-reads colours and weights).  Both depend on
+        // reflectivity and refraction_index, so those must not change under a live forest; colours and
+        // power may (the reference's GUI only ever calls set_diffuse, gui.rs:221-235).
+        const std::vector<DevMaterial> &old = scene->host_materials;
+        for (int i = 0; i < n; ++i)
+            if (mats[i].reflectivity != old[i].reflectivity || mats[i].refraction_index != old[i].refraction_index)
+                return fail(RT_ERR_UNSUPPORTED, "material %d: reflectivity / refraction_index cannot change while a ray forest built from this scene exists", i);
+    }
     cudaError_t e = cudaSetDevice(scene->device);
     if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
     if (n) {
         e = cudaMemcpy(scene->d_materials, mats.data(), sizeof(DevMaterial) * n, cudaMemcpyHostToDevice);
         if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(materials)");
     }
+    scene->host_materials = mats;
     return RT_OK;
 }
 
 void rt_scene_destroy(rt_scene *scene) {
     if (!scene) return;
-    cudaSetDevice(scene->device);
-    workspace_give_cached(scene->device, scene->ws);
-    for (void *p : scene->allocs) cudaFree(p);
-    for (cudaStream_t a : scene->aux) cudaStreamDestroy(a);
-    if (scene->own_stream) cudaStreamDestroy(scene->own_stream);
-    delete scene;
+    if (scene->forests > 0) { // forests built from it still use its tables and stream: the last one frees it
+        scene->destroy_pending = true;
+        return;
+    }
+    scene_free(scene);
 }
+
+// ---- debug hooks (include/rt_b200_debug.h) ---------------------------------------------------
+
+namespace {
+struct Knob {
+    const char *name;
+    int Tuning::*field;
+    long long lo, hi;
+};
+const Knob KNOBS[] = {
+    {"rays_per_thread", &Tuning::rays_per_thread, 0, 4},   {"want_light", &Tuning::want_light, 1, 4096},
+    {"want_heavy", &Tuning::want_heavy, 1, 4096},          {"slices", &Tuning::slices, 0, 1 << 20},
+    {"tail_pct", &Tuning::tail_pct, 0, 100},               {"tail_mult", &Tuning::tail_mult, 1, 64},
+    {"item_max", &Tuning::item_max, 0, 32},                {"table_cap", &Tuning::table_cap, 0, 1 << 24},
+    {"merge_lights", &Tuning::merge_lights, 0, 1},         {"heavy_allow", &Tuning::heavy_allow, 0, 1 << 24},
+    {"band_samples", &Tuning::band_samples, 1 << 10, 1 << 28}, {"origin_tables", &Tuning::origin_tables, 0, 1},
+    {"origin_min_slots", &Tuning::origin_min_slots, 0, 1 << 24}, {"host_threads", &Tuning::host_threads, 1, 64},
+    {"shadow_anyhit", &Tuning::shadow_anyhit, 0, 1},       {"trace", &Tuning::trace, 0, 1},
+};
+} // namespace
+
+int rt_debug_set(const char *name, int64_t value) {
+    if (!name) return fail(RT_ERR_INVALID, "null argument");
+    for (const Knob &k : KNOBS)
+        if (std::strcmp(k.name, name) == 0) {
+            if (value < k.lo || value > k.hi) return fail(RT_ERR_INVALID, "%s = %lld is not in %lld..%lld", name, (long long)value, k.lo, k.hi);
+            tuning().*(k.field) = (int)value;
+            return RT_OK;
+        }
+    return fail(RT_ERR_INVALID, "no tuning knob named %s", name);
+}
+
+int64_t rt_debug_get(const char *name) {
+    if (name)
+        for (const Knob &k : KNOBS)
+            if (std::strcmp(k.name, name) == 0) return tuning().*(k.field);
+    return INT64_MIN;
+}
+
+void rt_debug_reset(void) { tuning() = Tuning(); }
 
 } // extern "C"

@@ -36,16 +36,17 @@ struct OriginTable {
     // more than |O' - ray origin| + rmax from O' along the ray cannot hold a hit between the ray
     // origin and the light and is skipped (rmax = largest bound radius, rounded up).  0: no clip.
     float rmax = 0.f;
+    int shadow = 0; // the rays are the shadow rays of the light at O': any occluding hit ends a ray (sweep.cu: SHADOW)
 };
 
 // Nearest-hit query for every ray of s0 then s1 (Scene::intersect, scene/mod.rs:98-116).
-// rays_per_thread: 1, 2 or 4, or 0 to choose by the number of rays.  batch_counters (device,
+// batch_counters (device,
 // n_counters zeroed words) hand ray batches to the persistent warps, one word per launch;
 // *used receives the number consumed (one per shared-memory chunk of the bound table).
 // exact_counter (device, may be null; N_SWEEP_COUNTERS words) accumulates the number of exact pair
-// tests [0] and of filter evaluations [1..3].
+// tests [0], [7], [8] and of filter evaluations [1..6] (sweep.cu: sweep_kernel).
 // origin.bound != null: every ray passes through origin's point; s1 must be empty.
-cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable origin, int rays_per_thread, int sm_count,
+cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable origin, int sm_count,
                          unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
                          cudaStream_t stream);
 // Several sweeps against origin tables in ONE launch (the shadow rays of every light of a
@@ -53,9 +54,11 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
 // b % n_jobs.  Consumes n_jobs batch counters.  cudaErrorNotSupported (nothing launched) when the
 // case does not fit -- fewer than 2 or more than 8 jobs, a table too large to stay resident --
 // and the caller falls back to one launch_sweep per job.
-cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int rays_per_thread,
+cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs,
                               int sm_count, unsigned int *batch_counters, int n_counters, int *used,
                               unsigned long long *exact_counter, cudaStream_t stream);
+// Launches one sweep of this scene's table takes (shared-memory chunks of the bound table; 1 when it is resident).
+int sweep_table_chunks(const DevScene &sc);
 // FMA per (ray, bound) pair of the two filters (for the executed-flop count)
 constexpr int FILTER_FMA_GENERAL = 7, FILTER_FMA_ORIGIN = 4;
 // Same result, every (ray, shape) pair through the exact test in shape order (audit).
@@ -101,7 +104,7 @@ struct FrameParams {
 };
 
 constexpr int N_COUNTERS = 6;
-constexpr int N_SWEEP_COUNTERS = 4; // launch_sweep's exact_counter: exact tests, general evals, origin evals, slot evals
+constexpr int N_SWEEP_COUNTERS = 5 + MAX_SEGS; // launch_sweep's exact_counter: exact tests, general evals, origin evals, slot evals per segment, exact sphere / triangle tests
 constexpr int NODE_BIN_BITS = 5, NODE_FAR_BITS = 4; // per axis: hit points inside / outside the shapes' box
 constexpr int NODE_FAR_BINS = 1 << (3 * NODE_FAR_BITS);
 constexpr int NODE_BINS = NODE_FAR_BINS + (1 << (3 * NODE_BIN_BITS)); // + one bin for the rays that missed

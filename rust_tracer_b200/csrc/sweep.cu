@@ -42,10 +42,10 @@
 // light's rays and origin table (JOBS).
 #include <algorithm>
 #include <cfloat>
-#include <cstdlib>
 #include <type_traits>
 
 #include "kernels.h"
+#include "tuning.h"
 
 namespace rt {
 
@@ -134,6 +134,7 @@ struct SweepCtx {
     const int2 *slot_meta;
     const float4 *slot_geom;
     const float4 *cube_tris;
+    float lx, ly, lz; // SHADOW: the light the rays of this CTA travel towards
 };
 
 // One ray set of a JOBS launch (sweep_kernel) with its origin table, work counter and item shapes.
@@ -151,14 +152,32 @@ struct SweepJobs {
     int n;
 };
 
+// PointLight::get_energy (reference src/scene/mod.rs:195-204) calls the light occluded iff the
+// nearest hit point is nearer to the ray's origin than the light:
+//     (ray.at(t) - origin).len2() < (light - origin).len2()
+// -- the same operations in the same order as shade_kernel (wavefront.cu), so the two agree bit
+// for bit.  For t >= 0 the left side is a non-decreasing function of t even in f32 (a chain of
+// monotone roundings), so once ANY hit with t >= 0 occludes, the nearest hit occludes too.
+RT_DEV bool occludes(V3 o, V3 d, float t, float light_d2) { return vlen2(vsub(ray_at(o, d, t), o)) < light_d2; }
+
+// per-warp counters of the exact stage
+struct ExactCount {
+    unsigned int all, sphere, triangle;
+};
+
 // Run queued pairs 32 at a time, one exact test per lane; a partial batch stays queued unless
 // `all`.  Called by a converged warp.  Returns the number of pairs left in the queue.
+// SHADOW: wd2[local] = squared distance from ray `local` of the batch to its light; a hit that
+// occludes the light sets the ray's bit in wocc[] (the caller then drops the ray from the sweep).
+template <bool SHADOW>
 __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueue, unsigned long long *wbest, int ray0,
-                                        int cnt, int all, unsigned int *n_exact) {
+                                        int cnt, int all, ExactCount *n_exact, const float *wd2, unsigned int *wocc) {
     const int lane = threadIdx.x & 31;
     int done = 0;
+    unsigned int n_sphere = 0, n_triangle = 0;
     while (cnt - done >= 32 || (all && done < cnt)) {
         int idx = done + lane;
+        int kind = -1;
         if (idx < cnt) {
             unsigned int pair = wqueue[idx];
             int local = pair >> 24; // (ray of the warp batch << 24) | bound slot
@@ -168,12 +187,25 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
             const float4 *gp = ctx->slot_geom + 3 * j;
             const float4 g[3] = {gp[0], gp[1], gp[2]};
             RayRegs rr = load_ray(ctx->s0, ctx->s1, ray0 + local);
-            unsigned long long k = exact_slot(sm.x, sm.y, g, ctx->cube_tris, v3(rr.ox, rr.oy, rr.oz), v3(rr.dx, rr.dy, rr.dz));
-            if (k != KEY_MISS) atomicMin(&wbest[local], k);
+            kind = sm.x;
+            const V3 o = v3(rr.ox, rr.oy, rr.oz), d = v3(rr.dx, rr.dy, rr.dz);
+            unsigned long long k = exact_slot(sm.x, sm.y, g, ctx->cube_tris, o, d);
+            if (k != KEY_MISS) {
+                atomicMin(&wbest[local], k);
+                if constexpr (SHADOW) {
+                    if (occludes(o, d, key_t(k), wd2[local])) atomicOr(&wocc[local >> 5], 1u << (local & 31));
+                }
+            }
         }
+        n_sphere += __popc(__ballot_sync(0xffffffffu, kind == KIND_SPHERE));
+        n_triangle += __popc(__ballot_sync(0xffffffffu, kind == KIND_TRIANGLE));
         done += 32;
     }
-    if (lane == 0) *n_exact += (unsigned int)min(done, cnt);
+    if (lane == 0) {
+        n_exact->all += (unsigned int)min(done, cnt);
+        n_exact->sphere += n_sphere;
+        n_exact->triangle += n_triangle;
+    }
     int left = cnt - done;
     unsigned int keep = 0;
     if (left > 0 && lane < left) keep = wqueue[done + lane];
@@ -181,6 +213,32 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
     if (left > 0 && lane < left) wqueue[lane] = keep;
     __syncwarp();
     return left > 0 ? left : 0;
+}
+
+// ---- table staging: one bulk copy per table, completion on an mbarrier ------------------------
+RT_DEV uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+RT_DEV void mbar_init(unsigned long long *bar, unsigned int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+RT_DEV void mbar_expect_tx(unsigned long long *bar, unsigned int bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+// global -> shared, `bytes` a multiple of 16, both addresses 16-byte aligned (cp.async.bulk: the
+// TMA unit moves the block; no thread holds the data in registers on the way)
+RT_DEV void bulk_load(void *dst, const void *src, unsigned int bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+RT_DEV void mbar_wait(unsigned long long *bar, unsigned int phase) {
+    unsigned int ok = 0;
+    while (!ok) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(smem_addr(bar)), "r"(phase)
+                     : "memory");
+    }
 }
 
 // Filter coefficients of one ray (8 registers).  A ray the filter cannot bound (zero or
@@ -254,9 +312,11 @@ RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, cons
 RT_DEV float2 f2(float x) { return make_float2(x, x); }
 
 // One persistent CTA per SM; slots [slot_begin, slot_end) of the bound table stay in shared
-// memory for the whole launch.  A work item is (batch of 32 R rays) x (slice of the resident
-// slots); each WARP fetches its own items from batch_counter, so no block barrier follows the
-// table load, and small launches still spread over every warp of the GPU (n_slices > 1).
+// memory for the whole launch (staged by three bulk copies, cp.async.bulk + mbarrier, which run
+// while the warps fetch their first work item and load its rays).  A work item is (batch of
+// 32 R rays) x (slice of the resident slots); each WARP fetches its own items from
+// batch_counter, so no block barrier follows the table load, and small launches still spread
+// over every warp of the GPU (n_slices > 1).
 // Items come in three runs: the batches of the first s0.heavy rays (heavy_slices slices each), the
 // bulk (reg_batches batches, n_slices each), and the last batches of the launch cut finer
 // (tail_slices each) so that the warps run out of work at about the same time.
@@ -265,23 +325,39 @@ RT_DEV float2 f2(float x) { return make_float2(x, x); }
 // launch also tests the planes (slice 0 does).
 // ORIGIN: the table is `ot` (all rays pass through its point), filter of 4 FMA per pair.
 //
+// SHADOW (with ORIGIN): the rays are the shadow rays of the light at ot's point.  All
+// PointLight::get_energy asks of their nearest hit is whether it is nearer than the light
+// (scene/mod.rs:195-204), so a ray leaves the sweep at the first exact hit that says so (see
+// occludes()): its filter coefficients are neutralised, later quads and groups are only visited
+// for the rays still undecided, and a warp whose rays are all decided drops the rest of its
+// item.  The planes are tested FIRST: a plane may return t < 0 (plane.rs:59-64 keeps it), which
+// no other shape can undercut, so such a hit is the nearest one and decides alone.  The key
+// stored for an occluded ray is the smallest hit found so far, not necessarily the nearest one
+// of all: both occlude, and shading reads nothing else from a shadow key.
+//
 // JOBS: one launch sweeps several independent ray sets, each against its own origin table (the
 // shadow rays of every light of one wavefront level): CTA b works on job b % jobs.n only -- its
 // rays, table, work counter and item shapes come from jobs.j[] (copied to shared memory) instead
 // of the parameters of the same name, which are unused.  A level's L small launches, each
 // needing its table cut into slices to occupy every warp of the GPU, become one launch in which
 // a light has 1/L of the CTAs and L times the batches per warp.
-template <int R, int SWEEP_THREADS, bool ORIGIN, bool JOBS>
+//
+// exact_counter (N_SWEEP_COUNTERS words): [0] exact tests, [1] spheres evaluated by the general
+// filter, [2] by the origin filter (bound, group and quad spheres alike), [3 + g] evaluations of
+// bound slots of segment g, [7] exact tests of spheres, [8] of triangles.
+template <int R, int SWEEP_THREADS, bool ORIGIN, bool JOBS, bool SHADOW>
 __global__ void __launch_bounds__(SWEEP_THREADS, 1)
 sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin, int slot_end, int n_slices_, int slice_slots_,
              int merge_, int planes, int item_max, int heavy_batches_, int heavy_slices_, int heavy_slice_slots_,
              int reg_batches_, int tail_slices_, int tail_slice_slots_,
              unsigned int *batch_counter_, unsigned long long *exact_counter, const __grid_constant__ SweepJobs jobs) {
+    static_assert(!SHADOW || ORIGIN, "shadow rays are swept against their light's origin table");
     constexpr int SWEEP_WARPS = SWEEP_THREADS / 32;
     constexpr unsigned int FULL = 0xffffffffu;
     extern __shared__ float4 smem[];
     __shared__ SweepCtx ctx;
     __shared__ SweepJob job;
+    __shared__ unsigned long long tab_bar; // mbarrier: the table's bulk copies have landed
     if constexpr (JOBS) {
         if (threadIdx.x == 0) job = jobs.j[blockIdx.x % (unsigned int)jobs.n];
         __syncthreads();
@@ -295,36 +371,48 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
     const int reg_batches = JOBS ? job.reg_batches : reg_batches_, tail_slices = JOBS ? job.tail_slices : tail_slices_;
     const int tail_slice_slots = JOBS ? job.tail_slice_slots : tail_slice_slots_;
     unsigned int *const batch_counter = JOBS ? job.batch_counter : batch_counter_;
-    __shared__ unsigned int n_exact[SWEEP_WARPS];
-    __shared__ unsigned long long n_iters[SWEEP_WARPS], n_slot[SWEEP_WARPS];
+    __shared__ ExactCount n_exact[SWEEP_WARPS];
+    __shared__ unsigned long long n_hier[SWEEP_WARPS], n_slot[SWEEP_WARPS][MAX_SEGS];
     const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS, n_qtab = n_tab / QUAD_SLOTS;
     float4 *tab = smem;                                                         // n_tab slots + one slack pair
     float4 *gtab = tab + n_tab + 2;                                             // n_gtab groups
     float4 *qtab = gtab + n_gtab;                                               // n_qtab quads
     unsigned long long *best = (unsigned long long *)(qtab + n_qtab);           // SWEEP_THREADS * R
     unsigned int *queue = (unsigned int *)(best + SWEEP_THREADS * R);           // SWEEP_WARPS * QCAP
+    float *light_d2 = (float *)(queue + SWEEP_WARPS * QCAP);                    // SHADOW: SWEEP_THREADS * R
+    unsigned int *occluded = (unsigned int *)(light_d2 + SWEEP_THREADS * R);    // SHADOW: SWEEP_WARPS * R bit masks
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = s0.n + s1.n;
     unsigned long long *wbest = best + warp * (32 * R);
     unsigned int *wqueue = queue + warp * QCAP;
+    float *wd2 = SHADOW ? light_d2 + warp * (32 * R) : nullptr;
+    unsigned int *wocc = SHADOW ? occluded + warp * R : nullptr;
     const unsigned int lt_mask = (1u << lane) - 1u;
 
-    {
-        const float4 *src = (ORIGIN ? ot.bound : sc.bound) + slot_begin;
-        for (int k = tid; k < n_tab; k += SWEEP_THREADS) tab[k] = src[k];
-        const float4 *gsrc = (ORIGIN ? ot.group : sc.group) + slot_begin / GROUP_SLOTS;
-        for (int k = tid; k < n_gtab; k += SWEEP_THREADS) gtab[k] = gsrc[k];
-        const float4 *qsrc = (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS;
-        for (int k = tid; k < n_qtab; k += SWEEP_THREADS) qtab[k] = qsrc[k];
-        if (tid < 2) tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f); // prefetched past the end, never used
-    }
     if (tid == 0) {
+        mbar_init(&tab_bar, 1);
         ctx.s0 = s0; ctx.s1 = s1;
         ctx.slot_meta = sc.slot_meta; ctx.slot_geom = sc.slot_geom; ctx.cube_tris = sc.cube_tris;
+        ctx.lx = ot.ox; ctx.ly = ot.oy; ctx.lz = ot.oz;
     }
-    if (lane == 0) { n_exact[warp] = 0; n_iters[warp] = 0; n_slot[warp] = 0; }
+    if (tid < 2) tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f); // prefetched past the end, never used
+    if (lane == 0) {
+        n_exact[warp].all = n_exact[warp].sphere = n_exact[warp].triangle = 0;
+        n_hier[warp] = 0;
+#pragma unroll
+        for (int g = 0; g < MAX_SEGS; ++g) n_slot[warp][g] = 0;
+    }
     __syncthreads();
+    if (tid == 0) { // the table: slots, groups, quads -- three contiguous runs of float4
+        const unsigned int b_tab = (unsigned int)n_tab * sizeof(float4), b_g = (unsigned int)n_gtab * sizeof(float4),
+                           b_q = (unsigned int)n_qtab * sizeof(float4);
+        mbar_expect_tx(&tab_bar, b_tab + b_g + b_q);
+        bulk_load(tab, (ORIGIN ? ot.bound : sc.bound) + slot_begin, b_tab, &tab_bar);
+        bulk_load(gtab, (ORIGIN ? ot.group : sc.group) + slot_begin / GROUP_SLOTS, b_g, &tab_bar);
+        bulk_load(qtab, (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS, b_q, &tab_bar);
+    }
+    bool table_ready = false; // this warp has seen the copies land
     const float4 *tab0 = tab - slot_begin;                 // indexed by absolute slot
     const float4 *gtab0 = gtab - slot_begin / GROUP_SLOTS; // indexed by absolute group
     const float4 *qtab0 = qtab - slot_begin / QUAD_SLOTS;  // indexed by absolute quad
@@ -361,57 +449,100 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         const int ray0 = (int)ray0_ll;
         const int sb = slot_begin + slice * ss, se = min(slot_end, sb + ss);
 
-        // vmask bits 2r, 2r+1: ray r of this lane exists and has no NaN component (it can be
-        // queued); nanmask bit r: it exists and has one
+        // vmask bits 2r, 2r+1: ray r of this lane exists, has no NaN component and is still
+        // undecided (it can be queued); nanmask bit r: it exists and has a NaN component
         unsigned int vmask = 0, nanmask = 0;
+        if constexpr (SHADOW) {
+            if (lane < R) wocc[lane] = 0u;
+        }
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             int gi = ray0 + r * 32 + lane;
+            unsigned long long first = KEY_MISS;
             if (gi < total) {
-                if (ray_has_nan(load_ray(s0, s1, gi))) nanmask |= 1u << r;
-                else vmask |= 3u << (2 * r);
+                const RayRegs rr = load_ray(s0, s1, gi);
+                if (ray_has_nan(rr)) nanmask |= 1u << r;
+                else {
+                    vmask |= 3u << (2 * r);
+                    if constexpr (SHADOW) { // planes first: a hit at t < 0 is the nearest of all and decides alone
+                        const V3 o = v3(rr.ox, rr.oy, rr.oz), d = v3(rr.dx, rr.dy, rr.dz);
+                        const float d2 = vlen2(vsub(v3(ctx.lx, ctx.ly, ctx.lz), o));
+                        wd2[r * 32 + lane] = d2;
+                        first = plane_keys(sc.n_planes, sc.plane_shape, sc.plane_data, sc.geom, o, d, KEY_MISS);
+                        if (first != KEY_MISS) {
+                            const float tp = key_t(first);
+                            if (tp < 0.f || occludes(o, d, tp, d2)) vmask &= ~(3u << (2 * r));
+                        }
+                    }
+                }
             }
-            wbest[r * 32 + lane] = KEY_MISS;
+            wbest[r * 32 + lane] = first;
         }
         __syncwarp();
         int qn = 0; // queued pairs of this warp (warp-uniform)
+        bool alive = true; // SHADOW: some ray of the warp is still undecided
+        if constexpr (SHADOW) alive = __any_sync(FULL, vmask != 0u);
 
         // ---- phase 1 + 2 --------------------------------------------------------------
-        // filter evaluations of this item, in units of 32 (one per lane): against bound slots,
-        // and against group / quad spheres
-        unsigned int evals = 0, evals_hier = 0;
-        for (int g = 0; g < sc.segs.n; ++g) {
-            const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
-            if (gb >= ge) continue;
-            typename std::conditional<ORIGIN, RayCoefO, RayCoef>::type c[R];
+        typename std::conditional<ORIGIN, RayCoefO, RayCoef>::type c[R];
+        float k_cur = -1.f; // margin factor the coefficients were built with
+        // e[r] = (filter value of ray r against the two spheres packed in T0, T1)
+        // level: 0 bound slots, 1 group spheres, 2 quad spheres (wider margins, see GROUP_MARGIN)
+        auto pair_e = [&](const float4 &T0, const float4 &T1, float2 (&e)[R], int level) {
+            const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                bool usable = (vmask >> (2 * r)) & 1u;
-                RayRegs rr;
-                rr.ox = rr.oy = rr.oz = rr.dx = rr.dy = rr.dz = 0.f;
-                if (usable) rr = load_ray(s0, s1, ray0 + r * 32 + lane);
-                if constexpr (ORIGIN) c[r] = ray_coef_origin(rr, sc.segs.kx[g], sc.cmax, ot, usable);
-                else c[r] = ray_coef(rr, sc.segs.k[g], sc.cmax, usable);
+                if constexpr (ORIGIN) {
+                    float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __fmul2_rn(cz, f2(c[r].dz))));
+                    e[r] = __ffma2_rn(b, b, f2(level == 0 ? c[r].mu : (level == 1 ? c[r].mu_g : QUAD_MARGIN * c[r].mu_g)));
+                } else {
+                    float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
+                    float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2),
+                                           f2(level == 0 ? c[r].seed : (level == 1 ? c[r].seed_g : fmaf(QUAD_SEED, c[r].seed_g - c[r].seed, c[r].seed_g))))));
+                    // a centre behind the origin (b < 0): only s decides, i.e. whether the origin is inside the sphere
+                    e[r] = __ffma2_rn(b, make_float2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f)), s);
+                }
             }
-            // e[r] = (filter value of ray r against the two spheres packed in T0, T1)
-            // level: 0 bound slots, 1 group spheres, 2 quad spheres (wider margins, see GROUP_MARGIN)
-            auto pair_e = [&](const float4 &T0, const float4 &T1, float2 (&e)[R], int level) {
-                const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
+        };
+        // SHADOW, after a flush: rays the exact stage has just found occluded leave the sweep -- they
+        // pass no quad, group or slot any more (margin -> -3e38) and can no longer be queued
+        auto drop_occluded = [&]() {
+            if constexpr (SHADOW) {
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (((vmask >> (2 * r)) & 1u) && ((wocc[r] >> lane) & 1u)) {
+                        vmask &= ~(3u << (2 * r));
+                        c[r].mu = c[r].mu_g = -3.0e38f;
+                    }
+                alive = __any_sync(FULL, vmask != 0u);
+            }
+        };
+        // filter evaluations of this item, in units of 32 (one per lane): against group / quad spheres,
+        // and (per segment) against bound slots
+        unsigned int evals_hier = 0;
+        for (int g = 0; g < sc.segs.n && alive; ++g) {
+            const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
+            if (gb >= ge) continue;
+            // the coefficients depend on the segment through its margin factor only: rebuilt when it changes
+            const float k_seg = ORIGIN ? sc.segs.kx[g] : sc.segs.k[g];
+            if (k_seg != k_cur) {
+                k_cur = k_seg;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    if constexpr (ORIGIN) {
-                        float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __fmul2_rn(cz, f2(c[r].dz))));
-                        e[r] = __ffma2_rn(b, b, f2(level == 0 ? c[r].mu : (level == 1 ? c[r].mu_g : QUAD_MARGIN * c[r].mu_g)));
-                    } else {
-                        float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
-                        float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2),
-                                               f2(level == 0 ? c[r].seed : (level == 1 ? c[r].seed_g : fmaf(QUAD_SEED, c[r].seed_g - c[r].seed, c[r].seed_g))))));
-                        // a centre behind the origin (b < 0): only s decides, i.e. whether the origin is inside the sphere
-                        e[r] = __ffma2_rn(b, make_float2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f)), s);
-                    }
+                    bool usable = (vmask >> (2 * r)) & 1u;
+                    RayRegs rr;
+                    rr.ox = rr.oy = rr.oz = rr.dx = rr.dy = rr.dz = 0.f;
+                    if (usable) rr = load_ray(s0, s1, ray0 + r * 32 + lane);
+                    if constexpr (ORIGIN) c[r] = ray_coef_origin(rr, k_seg, sc.cmax, ot, usable);
+                    else c[r] = ray_coef(rr, k_seg, sc.cmax, usable);
                 }
-            };
-            for (int jq = gb; jq < ge; jq += 2 * QUAD_SLOTS) {
+            }
+            if (!table_ready) { // first use of the table by this warp
+                mbar_wait(&tab_bar, 0);
+                table_ready = true;
+            }
+            unsigned int evals = 0;
+            for (int jq = gb; jq < ge && alive; jq += 2 * QUAD_SLOTS) {
             // which of the two quads (4 groups each) can any ray of this warp touch?
             unsigned int quads_hit;
             {
@@ -429,7 +560,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
             if (!quads_hit) continue;
             constexpr int GP_PER_QUAD = QUAD_SLOTS / (2 * GROUP_SLOTS); // pairs of groups in a quad
             const int gp_begin = (quads_hit & 1u) ? 0 : GP_PER_QUAD, gp_end = (quads_hit & 2u) ? 2 * GP_PER_QUAD : GP_PER_QUAD;
-            for (int gp = gp_begin; gp < gp_end; ++gp) { // the pairs of groups of the touched quads
+            for (int gp = gp_begin; gp < gp_end && alive; ++gp) { // the pairs of groups of the touched quads
                 const int j0 = jq + gp * 2 * GROUP_SLOTS;
                 // which of the two groups can any ray of this warp touch?
                 unsigned int ball0, ball1, pm = 0;
@@ -453,7 +584,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                         pm &= vmask;
                     }
                 }
-                for (int h = 0; h < 2; ++h) {
+                for (int h = 0; h < 2 && alive; ++h) {
                     const unsigned int gball = h ? ball1 : ball0; // lanes with a ray that may touch group h
                     if (!gball) continue;
                     const int jg = j0 + h * GROUP_SLOTS;
@@ -491,14 +622,20 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                                 const bool cand = ev >= sw && ev <= clip && (lane < 16 || l1 >= 0);
                                 const unsigned int cball = __ballot_sync(FULL, cand);
                                 if (cball) {
-                                    if (qn > QCAP - 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
+                                    if (qn > QCAP - 32) {
+                                        qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
+                                        drop_occluded(); // (a ray dropped here may still be queued once more by this loop: harmless)
+                                    }
                                     if (cand) wqueue[qn + __popc(cball & lt_mask)] = ((unsigned int)(r * 32 + src) << 24) | (unsigned int)js;
                                     qn += __popc(cball);
                                     __syncwarp();
                                 }
                             }
                         }
-                        if (qn >= 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
+                        if (qn >= 32) {
+                            qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
+                            drop_occluded();
+                        }
                         continue;
                     }
                     const float4 *tp = tab0 + jg;
@@ -528,7 +665,11 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                             mask &= vmask;
                             unsigned int ball;
                             while ((ball = __ballot_sync(FULL, mask != 0)) != 0) { // one queue slot per lane per round
-                                if (qn > QCAP - 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
+                                if (qn > QCAP - 32) {
+                                    qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
+                                    drop_occluded();
+                                    mask &= vmask;
+                                }
                                 if (mask) {
                                     int bit = __ffs(mask) - 1;
                                     mask &= mask - 1;
@@ -540,14 +681,18 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                             }
                         }
                     }
-                    if (qn >= 32) qn = sweep_flush(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp]);
+                    if (qn >= 32) {
+                        qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
+                        drop_occluded();
+                    }
                 }
             }
             }
+            if (lane == 0) n_slot[warp][g] += evals;
         }
-        if (lane == 0) { n_iters[warp] += evals + evals_hier; n_slot[warp] += evals; }
+        if (lane == 0) n_hier[warp] += evals_hier;
         __syncwarp();
-        sweep_flush(&ctx, wqueue, wbest, ray0, qn, 1, &n_exact[warp]);
+        sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 1, &n_exact[warp], wd2, wocc);
 
         // ---- phase 3 + output -----------------------------------------------------------
 #pragma unroll
@@ -561,7 +706,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                         : KEY_MISS;
             } else {
                 k = wbest[r * 32 + lane];
-                if (planes && slice == 0) {
+                if (!SHADOW && planes && slice == 0) { // (SHADOW: the planes went first, into wbest)
                     RayRegs rr = load_ray(s0, s1, gi);
                     k = plane_keys(sc.n_planes, sc.plane_shape, sc.plane_data, sc.geom, v3(rr.ox, rr.oy, rr.oz),
                                    v3(rr.dx, rr.dy, rr.dz), k);
@@ -573,11 +718,21 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         }
         __syncwarp();
     }
+    if (!table_ready) mbar_wait(&tab_bar, 0); // never leave a CTA with its bulk copies in flight
     if (exact_counter && lane == 0) {
-        if (n_exact[warp]) atomicAdd(exact_counter, (unsigned long long)n_exact[warp]);
+        if (n_exact[warp].all) {
+            atomicAdd(exact_counter, (unsigned long long)n_exact[warp].all);
+            atomicAdd(exact_counter + 3 + MAX_SEGS, (unsigned long long)n_exact[warp].sphere);
+            atomicAdd(exact_counter + 4 + MAX_SEGS, (unsigned long long)n_exact[warp].triangle);
+        }
         // (ray, sphere) pairs the filter evaluated: 2 spheres x 32 R rays per iteration
-        if (n_iters[warp]) atomicAdd(exact_counter + (ORIGIN ? 2 : 1), n_iters[warp] * 32ull);
-        if (n_slot[warp]) atomicAdd(exact_counter + 3, n_slot[warp] * 32ull); // of which against bound slots
+        unsigned long long slots = 0;
+#pragma unroll
+        for (int g = 0; g < MAX_SEGS; ++g) {
+            if (n_slot[warp][g]) atomicAdd(exact_counter + 3 + g, n_slot[warp][g] * 32ull); // evaluations of bound slots, by segment
+            slots += n_slot[warp][g];
+        }
+        if (slots + n_hier[warp]) atomicAdd(exact_counter + (ORIGIN ? 2 : 1), (slots + n_hier[warp]) * 32ull);
     }
 }
 
@@ -607,15 +762,19 @@ sweep_all_pairs_kernel(DevScene sc, RaySeg s0, RaySeg s1, unsigned long long *ex
     (void)exact_counter; // rays x n_bounded, added by the host
 }
 
-template <int R, int T> static size_t sweep_smem_fixed() {
-    return 2 * sizeof(float4) + (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int);
+template <int R, int T, bool SHADOW> static size_t sweep_smem_fixed() {
+    return 2 * sizeof(float4) + (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int) +
+           (SHADOW ? (size_t)T * R * sizeof(float) + (size_t)(T / 32) * R * sizeof(unsigned int) : 0);
 }
 
 // Bound slots one launch can keep in shared memory.
-template <int R, int T> static int sweep_table_cap() {
+template <int R, int T, bool SHADOW> static int sweep_table_cap() {
     // per slot: its float4, 1/GROUP_SLOTS of its group's and 1/QUAD_SLOTS of its quad's
-    return (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T>()) * QUAD_SLOTS / (sizeof(float4) * (QUAD_SLOTS + QUAD_SLOTS / GROUP_SLOTS + 1))) /
-           SEG_PAD * SEG_PAD;
+    int cap = (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T, SHADOW>()) * QUAD_SLOTS / (sizeof(float4) * (QUAD_SLOTS + QUAD_SLOTS / GROUP_SLOTS + 1))) /
+              SEG_PAD * SEG_PAD;
+    const int forced = tuning().table_cap / SEG_PAD * SEG_PAD; // tests force several table chunks
+    if (forced >= SEG_PAD && forced < cap) cap = forced;
+    return cap;
 }
 
 // How the rays of one sweep are cut into work items (ray batches x table slices), for `warps`
@@ -629,15 +788,9 @@ struct ItemPlan {
     long long items = 0;
 };
 
-static int sweep_env(const char *name, int dflt, int lo, int hi) {
-    const char *e = std::getenv(name);
-    if (!e) return dflt;
-    const int v = std::atoi(e);
-    return v < lo || v > hi ? dflt : v;
-}
-
 template <int R>
 static ItemPlan plan_items(long long total, int heavy, int per, long long warps, int n_chunks) {
+    const Tuning &tn = tuning();
     ItemPlan pl;
     const long long batches = (total + 32ll * R - 1) / (32ll * R);
     // Work items = ray batches x table slices.  A launch with few rays is cut into slices of
@@ -652,11 +805,10 @@ static ItemPlan plan_items(long long total, int heavy, int per, long long warps,
         return std::max(1, (per + *slots - 1) / *slots);
     };
     pl.heavy_batches = std::min<long long>(batches, ((long long)std::max(heavy, 0) + 32ll * R - 1) / (32ll * R));
-    long long want_light = 4ll * warps, want_heavy = 48ll * warps; // measured: RT_B200_WANT
-    if (const char *e = std::getenv("RT_B200_WANT")) want_light = std::max(1, std::atoi(e)) * warps;
+    const long long want_light = (long long)tn.want_light * warps, want_heavy = (long long)tn.want_heavy * warps; // measured (tuning.h)
     pl.n_slices = slicing(want_light, batches - pl.heavy_batches, &pl.slice_slots);
-    if (const char *e = std::getenv("RT_B200_SLICES")) {
-        pl.n_slices = std::max(1, std::min(std::atoi(e), std::max(1, per / SEG_PAD)));
+    if (tn.slices > 0) {
+        pl.n_slices = std::max(1, std::min(tn.slices, std::max(1, per / SEG_PAD)));
         pl.slice_slots = std::max(SEG_PAD, ((per + pl.n_slices - 1) / pl.n_slices + SEG_PAD - 1) / SEG_PAD * SEG_PAD);
         pl.n_slices = std::max(1, (per + pl.slice_slots - 1) / pl.slice_slots);
     }
@@ -665,9 +817,9 @@ static ItemPlan plan_items(long long total, int heavy, int per, long long warps,
         if (pl.heavy_slices < pl.n_slices) { pl.heavy_slices = pl.n_slices; pl.heavy_slice_slots = pl.slice_slots; }
     }
     // A warp's last item ends, on average, half an item before the launch does.  The last
-    // 15 % of the batches (at most 2 per warp) are therefore cut 4 times finer (measured: RT_B200_TAIL_PCT, _MULT).
+    // tail_pct % of the batches (at most 2 per warp) are therefore cut tail_mult times finer (measured: 15 %, 4 x).
     const long long regular = batches - pl.heavy_batches;
-    const int tail_pct = sweep_env("RT_B200_TAIL_PCT", 15, 0, 100), tail_mult = sweep_env("RT_B200_TAIL_MULT", 4, 1, 64);
+    const int tail_pct = tn.tail_pct, tail_mult = tn.tail_mult;
     long long tail_batches = std::min<long long>(regular * tail_pct / 100, 2 * warps);
     pl.tail_slices = pl.n_slices; pl.tail_slice_slots = pl.slice_slots;
     if (tail_batches > 0 && tail_mult > 1) {
@@ -682,29 +834,16 @@ static ItemPlan plan_items(long long total, int heavy, int per, long long warps,
     return pl;
 }
 
-// lanes of a warp with a ray touching a group up to which the group is swept (ray, group)
-// pair by pair (lane = slot) rather than all 32 R rays against all its slots: about where the
-// two cost the same
-static int sweep_item_max() {
-    int item_max = 16;
-    if (const char *e = std::getenv("RT_B200_ITEM_MAX")) item_max = std::atoi(e);
-    return item_max;
+template <int R, int T, bool SHADOW> static size_t sweep_smem_bytes(int slots) {
+    return (size_t)(slots + slots / GROUP_SLOTS + slots / QUAD_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T, SHADOW>();
 }
 
-template <int R, int T> static size_t sweep_smem_bytes(int slots) {
-    return (size_t)(slots + slots / GROUP_SLOTS + slots / QUAD_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T>();
-}
-
-template <int R, int T, bool ORIGIN>
+template <int R, int T, bool ORIGIN, bool SHADOW>
 static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, long long total, int sm_count,
                                   unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
                                   cudaStream_t stream) {
     constexpr int SWEEP_WARPS = T / 32;
-    int cap = sweep_table_cap<R, T>();
-    if (const char *e = std::getenv("RT_B200_TABLE_CAP")) { // test knob: force several table chunks
-        int v = std::atoi(e) / SEG_PAD * SEG_PAD;
-        if (v >= SEG_PAD && v < cap) cap = v;
-    }
+    const int cap = sweep_table_cap<R, T, SHADOW>();
     const int n_chunks = std::max(1, (sc.n_slots + cap - 1) / cap);
     if (n_chunks > n_counters) return cudaErrorInvalidValue;
     // chunks of equal size (rounded to SEG_PAD) rather than cap, cap, ..., rest
@@ -723,14 +862,14 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
     static const SweepJobs no_jobs{};
     for (int c = 0; c < n_chunks; ++c) {
         int b = c * per, e = std::min(sc.n_slots, b + per);
-        const size_t smem = sweep_smem_bytes<R, T>(e - b);
-        cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        const size_t smem = sweep_smem_bytes<R, T, SHADOW>(e - b);
+        cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN, false, SHADOW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
-        sweep_kernel<R, T, ORIGIN, false><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, pl.n_slices, pl.slice_slots, pl.merge,
-                                                                     c == n_chunks - 1 ? 1 : 0, sweep_item_max(), (int)pl.heavy_batches,
-                                                                     pl.heavy_slices, pl.heavy_slice_slots, (int)pl.reg_batches,
-                                                                     pl.tail_slices, pl.tail_slice_slots, batch_counters + c,
-                                                                     exact_counter, no_jobs);
+        sweep_kernel<R, T, ORIGIN, false, SHADOW><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, pl.n_slices, pl.slice_slots, pl.merge,
+                                                                             c == n_chunks - 1 ? 1 : 0, tuning().item_max, (int)pl.heavy_batches,
+                                                                             pl.heavy_slices, pl.heavy_slice_slots, (int)pl.reg_batches,
+                                                                             pl.tail_slices, pl.tail_slice_slots, batch_counters + c,
+                                                                             exact_counter, no_jobs);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
     }
     *used = n_chunks;
@@ -738,8 +877,8 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
 }
 
 // Rays per thread of a launch: fewer only when even table slicing cannot occupy the warps.
-static int pick_rays_per_thread(int wanted, long long total, int n_slots, int sm_count) {
-    if (wanted > 0) return wanted;
+static int pick_rays_per_thread(long long total, int n_slots, int sm_count) {
+    if (tuning().rays_per_thread > 0) return tuning().rays_per_thread;
     const long long want = 2ll * sm_count * 16;
     const long long max_slices = std::max(1, n_slots / MIN_SLICE_SLOTS);
     int r = 4;
@@ -747,10 +886,11 @@ static int pick_rays_per_thread(int wanted, long long total, int n_slots, int sm
     return r;
 }
 
-template <int R, int T>
+template <int R, int T, bool SHADOW>
 static cudaError_t launch_sweep_jobs_r(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int sm_count,
                                        unsigned int *batch_counters, unsigned long long *exact_counter, cudaStream_t stream) {
     constexpr int SWEEP_WARPS = T / 32;
+    if (sc.n_slots > sweep_table_cap<R, T, SHADOW>()) return cudaErrorNotSupported; // one resident table only
     SweepJobs jobs{};
     jobs.n = n_jobs;
     const unsigned int grid = (unsigned int)sm_count;
@@ -763,37 +903,41 @@ static cudaError_t launch_sweep_jobs_r(const DevScene &sc, const RaySeg *segs, c
         J.heavy_batches = (int)pl.heavy_batches; J.heavy_slices = pl.heavy_slices; J.heavy_slice_slots = pl.heavy_slice_slots;
         J.reg_batches = (int)pl.reg_batches; J.tail_slices = pl.tail_slices; J.tail_slice_slots = pl.tail_slice_slots;
     }
-    const size_t smem = sweep_smem_bytes<R, T>(sc.n_slots);
-    cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = sweep_smem_bytes<R, T, SHADOW>(sc.n_slots);
+    cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, true, true, SHADOW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     const RaySeg none{nullptr, nullptr, nullptr, 0};
-    sweep_kernel<R, T, true, true><<<grid, T, smem, stream>>>(sc, none, none, OriginTable{}, 0, sc.n_slots, 1, SEG_PAD, 0, 1, sweep_item_max(),
-                                                              0, 1, SEG_PAD, 0, 1, SEG_PAD, nullptr, exact_counter, jobs);
+    sweep_kernel<R, T, true, true, SHADOW><<<grid, T, smem, stream>>>(sc, none, none, OriginTable{}, 0, sc.n_slots, 1, SEG_PAD, 0, 1, tuning().item_max,
+                                                                      0, 1, SEG_PAD, 0, 1, SEG_PAD, nullptr, exact_counter, jobs);
     return cudaGetLastError();
 }
 
-cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int rays_per_thread,
-                              int sm_count, unsigned int *batch_counters, int n_counters, int *used,
-                              unsigned long long *exact_counter, cudaStream_t stream) {
+cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int sm_count,
+                              unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
+                              cudaStream_t stream) {
     *used = 0;
     if (n_jobs < 2 || n_jobs > MAX_SWEEP_JOBS || n_jobs > n_counters || sm_count < n_jobs) return cudaErrorNotSupported;
-    if (sc.n_slots > sweep_table_cap<4, 512>() || std::getenv("RT_B200_TABLE_CAP")) return cudaErrorNotSupported; // one resident table only
     long long most = 0;
     for (int j = 0; j < n_jobs; ++j) {
         // keys are folded in with atomicMin when a job's items are table slices: the caller presets them
         if (!tabs[j].bound || segs[j].n <= 0 || !segs[j].preset) return cudaErrorNotSupported;
         most = std::max<long long>(most, segs[j].n);
     }
-    const int r = pick_rays_per_thread(rays_per_thread, most, sc.n_slots, std::max(1, sm_count / n_jobs));
+    const int r = pick_rays_per_thread(most, sc.n_slots, std::max(1, sm_count / n_jobs));
+    const bool anyhit = tuning().shadow_anyhit != 0;
     cudaError_t err;
-    if (r >= 4) err = launch_sweep_jobs_r<4, 512>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream);
-    else if (r >= 2) err = launch_sweep_jobs_r<2, 512>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream);
-    else err = launch_sweep_jobs_r<1, 512>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream);
+#define RT_JOBS(R_) \
+    (anyhit ? launch_sweep_jobs_r<R_, 512, true>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream) \
+            : launch_sweep_jobs_r<R_, 512, false>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream))
+    if (r >= 4) err = RT_JOBS(4);
+    else if (r >= 2) err = RT_JOBS(2);
+    else err = RT_JOBS(1);
+#undef RT_JOBS
     if (err == cudaSuccess) *used = n_jobs;
     return err;
 }
 
-cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, int rays_per_thread, int sm_count,
+cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, int sm_count,
                          unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
                          cudaStream_t stream) {
     long long total = (long long)s0.n + s1.n;
@@ -801,18 +945,28 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
     if (total <= 0) return cudaSuccess;
     if (ot.bound && s1.n > 0) return cudaErrorInvalidValue;
     if (sm_count < 1) sm_count = 1;
-    const int r = pick_rays_per_thread(rays_per_thread, total, sc.n_slots, sm_count);
-#define RT_SWEEP(R_, T_, O_) \
-    launch_sweep_r<R_, T_, O_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
-    if (ot.bound) {
-        if (r >= 4) return RT_SWEEP(4, 512, true);
-        if (r >= 2) return RT_SWEEP(2, 512, true);
-        return RT_SWEEP(1, 512, true);
+    const int r = pick_rays_per_thread(total, sc.n_slots, sm_count);
+#define RT_SWEEP(R_, T_, O_, S_) \
+    launch_sweep_r<R_, T_, O_, S_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
+    if (ot.bound && ot.shadow && tuning().shadow_anyhit) { // the shadow rays of one light
+        if (r >= 4) return RT_SWEEP(4, 512, true, true);
+        if (r >= 2) return RT_SWEEP(2, 512, true, true);
+        return RT_SWEEP(1, 512, true, true);
     }
-    if (r >= 4) return RT_SWEEP(4, 512, false); // 16 warps x <= 128 registers; more warps spill the filter loop
-    if (r >= 2) return RT_SWEEP(2, 512, false);
-    return RT_SWEEP(1, 512, false);
+    if (ot.bound) {
+        if (r >= 4) return RT_SWEEP(4, 512, true, false);
+        if (r >= 2) return RT_SWEEP(2, 512, true, false);
+        return RT_SWEEP(1, 512, true, false);
+    }
+    if (r >= 4) return RT_SWEEP(4, 512, false, false); // 16 warps x <= 128 registers; more warps spill the filter loop
+    if (r >= 2) return RT_SWEEP(2, 512, false, false);
+    return RT_SWEEP(1, 512, false, false);
 #undef RT_SWEEP
+}
+
+int sweep_table_chunks(const DevScene &sc) {
+    const int cap = sweep_table_cap<4, 512, true>(); // the smallest of the kernels' capacities
+    return std::max(1, (sc.n_slots + cap - 1) / cap);
 }
 
 void launch_sweep_all_pairs(const DevScene &sc, RaySeg s0, RaySeg s1, unsigned long long *exact_counter,

@@ -1,0 +1,34 @@
+// tuning.h -- scheduling constants of the library, in one place.
+//
+// The library never reads the environment: a drop-in must not change its behaviour because of
+// what the caller's process happens to export.  Every value below is a compile-time default;
+// tests and measurement tools can override the scheduling ones through rt_debug_set
+// (include/rt_b200_debug.h), which is not part of the drop-in ABI.  None of them can change a
+// result: correctness margins (the bound radii and filter margins of api_scene.cu / sweep.cu)
+// are constants and are NOT here.
+#pragma once
+
+namespace rt {
+
+struct Tuning {
+    int rays_per_thread = 0;    // sweep: rays per thread (1, 2, 4); 0 = by the number of rays
+    int want_light = 4;         // sweep: work items per warp aimed at for ordinary batches ...
+    int want_heavy = 48;        // ... and for the expensive first batches of a launch
+    int slices = 0;             // sweep: force this many table slices per batch; 0 = plan
+    int tail_pct = 15;          // sweep: the last tail_pct % of a launch's batches ...
+    int tail_mult = 4;          // ... are cut tail_mult times finer
+    int item_max = 16;          // sweep: lanes with a touching ray up to which a group is swept pair by pair
+    int table_cap = 0;          // sweep: bound slots per shared-memory chunk; 0 = what fits (tests force chunks)
+    int merge_lights = 1;       // wavefront: all lights' shadow rays of a level in one launch
+    int heavy_allow = 65536;    // wavefront: slack on the count of expensive child rays
+    int band_samples = 1 << 23; // render: samples per band
+    int origin_tables = 1;      // scene: build per-light / camera origin tables
+    int origin_min_slots = 256; // scene: ... only for tables of at least this many slots
+    int host_threads = 4;       // scene: host threads of the table build
+    int shadow_anyhit = 1;      // sweep: a shadow ray stops at the first hit that occludes its light
+    int trace = 0;              // print per-phase host laps and per-sweep counters to stderr
+};
+
+Tuning &tuning();
+
+} // namespace rt

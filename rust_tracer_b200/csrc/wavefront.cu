@@ -372,7 +372,9 @@ shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level
             reflected = cscale(fresnel, reflected_energy(m, v3(cr.x, cr.y, cr.z), h.eye, h));
             dir = v3(0.f, 0.f, 0.f);
             if (ct.w != 0.f) {
-                V3 ro, rd;
+                // the child exists, so refract_ray succeeded at build time; n1 / n2 cannot have changed since
+                // (rt_scene_update_materials refuses that while a forest is alive)
+                V3 ro, rd = v3(0.f, 0.f, 0.f);
                 refract_ray(d, h, n1, n2, ro, rd);
                 dir = vnorm(rd); // -(child eye_dir) = norm(child ray direction)
             }

@@ -26,7 +26,12 @@ def test_library_exports_every_declared_symbol():
     handle = rt.lib()
     for name in declared:
         assert hasattr(handle, name), name
-    assert handle.rt_abi_version() == 3
+    assert handle.rt_abi_version() == 4
+    # the debug hooks have their own header and are not part of the drop-in ABI
+    debug = _declared_functions("rt_b200_debug.h")
+    assert debug == set(_lib.DEBUG_EXPORTS) and not (debug & declared)
+    for name in debug:
+        assert hasattr(handle, name), name
 
 
 def test_struct_sizes_match_the_header():
@@ -37,7 +42,7 @@ def test_struct_sizes_match_the_header():
     assert C.sizeof(abi.rt_light) == 28
     assert C.sizeof(abi.rt_camera) == 36
     assert C.sizeof(abi.rt_render_params) == 32
-    assert C.sizeof(abi.rt_stats) == 112
+    assert C.sizeof(abi.rt_stats) == 184
 
 
 def _bytes(ptr, n, T):
@@ -137,6 +142,26 @@ def test_compute_fails_loudly_without_a_gpu():
     assert e.value.code == abi.RT_ERR_CUDA
     with pytest.raises(rt.RtError):
         rt.measure_fp32_peak(0)
+
+
+def test_library_does_not_read_the_environment():
+    """A drop-in must not change its behaviour because of what the caller's process exports: the
+    library has no getenv at all; its scheduling constants are only reachable through
+    rt_debug_set (include/rt_b200_debug.h)."""
+    import subprocess
+    out = subprocess.run(["nm", "-D", "--undefined-only", _lib.LIB_PATH], capture_output=True, text=True)
+    assert out.returncode == 0
+    assert "getenv" not in out.stdout
+    L = rt.lib()
+    assert L.rt_debug_get(b"item_max") == 16 and L.rt_debug_get(b"no_such_knob") == -(1 << 63)
+    assert L.rt_debug_set(b"tri_bound_scale", 1) == abi.RT_ERR_INVALID  # correctness margins are not knobs
+    assert L.rt_debug_set(b"item_max", 99) == abi.RT_ERR_INVALID
+    with rt.tuned(item_max=3, table_cap=256):
+        assert L.rt_debug_get(b"item_max") == 3 and L.rt_debug_get(b"table_cap") == 256
+    assert L.rt_debug_get(b"item_max") == 16 and L.rt_debug_get(b"table_cap") == 0
+    L.rt_debug_set(b"want_light", 9)
+    L.rt_debug_reset()
+    assert L.rt_debug_get(b"want_light") == 4
 
 
 def test_package_does_not_import_the_oracle():

@@ -58,19 +58,24 @@ def _scene_with_spheres(spheres):
     return rt.SceneDesc.from_arrays(shapes, mats, lights, (0.1, 0.1, 0.1)), base
 
 
-def test_chunked_bound_table_equals_resident_table(monkeypatch):
+def test_chunked_bound_table_equals_resident_table():
     """A bound table larger than shared memory is swept in chunks, one launch each, the keys
     accumulating in global memory; forced here with a tiny chunk size."""
     desc = rt.SceneDesc.synthetic(400, 400, 4242, 0.03, 0.1)
     w, h = 192, 108
     sc = rt.Scene(desc)
     f0, u0, s0 = sc.render(w, h, 5)
-    monkeypatch.setenv("RT_B200_TABLE_CAP", "128")
-    f1, u1, s1 = sc.render(w, h, 5)
-    monkeypatch.delenv("RT_B200_TABLE_CAP")
+    with rt.tuned(table_cap=128):
+        f1, u1, s1 = sc.render(w, h, 5)
+    with rt.tuned(shadow_anyhit=0):  # every sweep finds the nearest hit: the exact tests are then the same set of pairs
+        f2, u2, s2 = sc.render(w, h, 5)
+        with rt.tuned(table_cap=128):
+            f3, u3, s3 = sc.render(w, h, 5)
     sc.close()
     assert np.array_equal(f0, f1, equal_nan=True) and (u0 == u1).all()
-    assert s0["rays"] == s1["rays"] and s0["exact_tests"] == s1["exact_tests"]
+    assert np.array_equal(f0, f2, equal_nan=True) and np.array_equal(f0, f3, equal_nan=True)
+    assert s0["rays"] == s1["rays"] and s2["exact_tests"] == s3["exact_tests"]
+    assert s0["exact_tests"] <= s2["exact_tests"]  # shadow rays that stop at the first occluder test fewer pairs
     assert s1["kernel_launches"] > s0["kernel_launches"]  # the chunks really were separate launches
     of, ou, oc = orc.render(desc.desc, abi.default_camera(w, h), 5)
     assert (u1 == ou).all() and s1["rays"] == oc.rays
@@ -157,7 +162,7 @@ def _moved_camera(w, h, origin):
 
 
 @pytest.mark.parametrize("origin", [(0.0, 0.0, -8.0), (0.5, 0.7, 1.5), (300.0, -120.0, -4000.0)])
-def test_origin_tables_equal_general_filter_and_audit(monkeypatch, origin):
+def test_origin_tables_equal_general_filter_and_audit(origin):
     """Primary rays are swept against the bound table re-centred on the camera, the shadow rays
     of each light against the table re-centred on that light (4 FMA per pair instead of 7);
     the nearest hits must be those of the general filter and of the all-pairs audit -- also
@@ -173,12 +178,12 @@ def test_origin_tables_equal_general_filter_and_audit(monkeypatch, origin):
         b4 = sc.render(w, h, depth, cam=cam, spp=4, seed=11, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS)
     finally:
         sc.close()
-    monkeypatch.setenv("RT_B200_NO_ORIGIN", "1")
-    sc = rt.Scene(desc)
-    try:
-        g = sc.render(w, h, depth, cam=cam)
-    finally:
-        sc.close()
+    with rt.tuned(origin_tables=0):
+        sc = rt.Scene(desc)
+        try:
+            g = sc.render(w, h, depth, cam=cam)
+        finally:
+            sc.close()
     _assert_same(a, b)
     _assert_same(a4, b4)
     _assert_same(a, g)
@@ -221,29 +226,27 @@ def test_origin_tables_with_a_light_inside_a_shape_and_far_lights():
     assert (a[1] == ou).all() and a[2]["rays"] == oc.rays
 
 
-def test_work_item_shapes_do_not_change_the_image(monkeypatch):
-    """The sweep's scheduling knobs -- table slices per work item (RT_B200_WANT, RT_B200_SLICES),
-    the threshold between sweeping a group ray-by-ray or pair-by-pair (RT_B200_ITEM_MAX) -- and
+def test_work_item_shapes_do_not_change_the_image():
+    """The sweep's scheduling knobs (rt_debug_set) -- table slices per work item (want_light, slices),
+    the threshold between sweeping a group ray-by-ray or pair-by-pair (item_max) -- and
     the node order must not change a single key: same image, same ray and node counts, and
     the same as the all-pairs audit (which uses none of them)."""
     desc = rt.SceneDesc.synthetic(600, 600, 31, 0.03, 0.1)  # floor plane: hit points far outside the shapes' box
     w, h, depth = 256, 144, 4
     ref = None
-    for env in ({}, {"RT_B200_WANT": "1"}, {"RT_B200_WANT": "64"}, {"RT_B200_SLICES": "1"}, {"RT_B200_ITEM_MAX": "0"},
-                {"RT_B200_ITEM_MAX": "32"}, {"RT_B200_RAYS_PER_THREAD": "1"}, {"RT_B200_RAYS_PER_THREAD": "2"}):
-        for k, v in env.items():
-            monkeypatch.setenv(k, v)
-        sc = rt.Scene(desc)
-        try:
-            out = sc.render(w, h, depth)
-            if ref is None:
-                ref = out
-                audit = sc.render(w, h, depth, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS)
-                _assert_same(ref, audit)
-        finally:
-            sc.close()
-        for k in env:
-            monkeypatch.delenv(k)
+    for knobs in ({}, {"want_light": 1}, {"want_light": 64}, {"slices": 1}, {"slices": 5}, {"item_max": 0},
+                  {"item_max": 32}, {"rays_per_thread": 1}, {"rays_per_thread": 2}, {"shadow_anyhit": 0},
+                  {"shadow_anyhit": 0, "slices": 3}):
+        with rt.tuned(**knobs):
+            sc = rt.Scene(desc)
+            try:
+                out = sc.render(w, h, depth)
+                if ref is None:
+                    ref = out
+                    audit = sc.render(w, h, depth, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS)
+                    _assert_same(ref, audit)
+            finally:
+                sc.close()
         _assert_same(ref, out)
 
 
@@ -262,7 +265,7 @@ def test_far_hit_points_take_the_heavy_path():
     assert (a[1] == ou).all() and a[2]["rays"] == oc.rays and a[2]["nodes"] == oc.nodes
 
 
-def test_bands_do_not_change_the_image(monkeypatch):
+def test_bands_do_not_change_the_image():
     """A frame larger than one band of samples is cast band by band (each with its own ray pools,
     node order and counters); cutting a small frame into many bands must give the same image,
     ray and node counts as one band, for 1 and 4 samples per pixel."""
@@ -272,10 +275,9 @@ def test_bands_do_not_change_the_image(monkeypatch):
     try:
         one = sc.render(w, h, depth)
         one4 = sc.render(w, h, depth, spp=4, seed=5)
-        monkeypatch.setenv("RT_B200_BAND_SAMPLES", "3000")
-        many = sc.render(w, h, depth)
-        many4 = sc.render(w, h, depth, spp=4, seed=5)
-        monkeypatch.delenv("RT_B200_BAND_SAMPLES")
+        with rt.tuned(band_samples=3000):
+            many = sc.render(w, h, depth)
+            many4 = sc.render(w, h, depth, spp=4, seed=5)
     finally:
         sc.close()
     _assert_same(one, many)
@@ -294,30 +296,28 @@ def test_tested_pairs_counter():
     assert a[2]["tested_pairs"] >= a[2]["plane_tests"]
 
 
-def test_merged_light_sweeps_and_tail_items_do_not_change_the_image(monkeypatch):
+def test_merged_light_sweeps_and_tail_items_do_not_change_the_image():
     """One launch for every light's shadow rays (launch_sweep_jobs: CTA b serves light b % L) against
-    one launch per light (RT_B200_MERGE_LIGHTS=0), and the finer work items at the end of a launch
-    (RT_B200_TAIL_PCT, RT_B200_TAIL_MULT): scheduling only -- same keys, so the same image and counts,
+    one launch per light (merge_lights = 0), and the finer work items at the end of a launch
+    (tail_pct, tail_mult): scheduling only -- the same image and counts,
     and the same as the all-pairs audit.  Also at fewer rays per thread, where the jobs kernel is
     another instantiation."""
     desc = rt.SceneDesc.synthetic(500, 500, 77, 0.03, 0.1)
     w, h, depth = 224, 126, 4
     ref = None
-    for env in ({}, {"RT_B200_MERGE_LIGHTS": "0"}, {"RT_B200_TAIL_PCT": "0"}, {"RT_B200_TAIL_PCT": "100", "RT_B200_TAIL_MULT": "8"},
-                {"RT_B200_TAIL_PCT": "50", "RT_B200_TAIL_MULT": "64"}, {"RT_B200_RAYS_PER_THREAD": "1"},
-                {"RT_B200_RAYS_PER_THREAD": "2", "RT_B200_WANT": "16"}):
-        for k, v in env.items():
-            monkeypatch.setenv(k, v)
-        sc = rt.Scene(desc)
-        try:
-            out = sc.render(w, h, depth)
-            if ref is None:
-                ref = out
-                _assert_same(ref, sc.render(w, h, depth, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS))
-        finally:
-            sc.close()
-        for k in env:
-            monkeypatch.delenv(k)
+    for knobs in ({}, {"merge_lights": 0}, {"tail_pct": 0}, {"tail_pct": 100, "tail_mult": 8},
+                  {"tail_pct": 50, "tail_mult": 64}, {"rays_per_thread": 1},
+                  {"rays_per_thread": 2, "want_light": 16}, {"shadow_anyhit": 0}, {"shadow_anyhit": 0, "merge_lights": 0},
+                  {"merge_lights": 0, "rays_per_thread": 2}, {"merge_lights": 0, "table_cap": 256}):
+        with rt.tuned(**knobs):
+            sc = rt.Scene(desc)
+            try:
+                out = sc.render(w, h, depth)
+                if ref is None:
+                    ref = out
+                    _assert_same(ref, sc.render(w, h, depth, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS))
+            finally:
+                sc.close()
         _assert_same(ref, out)
     assert ref[2]["kernel_launches"] > 0
 

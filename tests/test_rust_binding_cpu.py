@@ -116,7 +116,7 @@ def test_structs_have_the_fields_and_sizes_of_the_ctypes_mirror():
 
 def test_constants_match():
     consts = {k: int(v) for k, v in re.findall(r"pub const (RT_\w+): \w+ = (-?\d+);", RS_NOCOMMENT)}
-    assert consts.pop("RT_B200_ABI_VERSION") == 3
+    assert consts.pop("RT_B200_ABI_VERSION") == 4
     for k, v in consts.items():
         assert getattr(abi, k) == v, k
     for k in dir(abi):
