@@ -32,7 +32,24 @@ CASES = {
 }
 
 
+def scene_files():
+    """The benchmark scenes (SURVEY 8d generators, host side of the library) as scene description
+    files: bench.py --impl reference renders them with the oracle and must not load the product."""
+    import lzma
+    import tempfile
+    for name in ("s1k", "m10k"):
+        with tempfile.TemporaryDirectory() as tmp:
+            path = os.path.join(tmp, name + ".rtscene")
+            rt.SceneDesc.builtin(name).save(path)
+            with open(path, "rb") as fh:
+                raw = fh.read()
+        with open(os.path.join(HERE, name + ".rtscene.xz"), "wb") as fh:
+            fh.write(lzma.compress(raw, preset=9))
+        print(name, len(raw), "bytes")
+
+
 def main():
+    scene_files()
     for name, (mk, w, h, depth, mode, spp, seed) in CASES.items():
         desc = mk()
         f, u, c = orc.render(desc.desc, abi.default_camera(w, h), depth, mode=mode, spp=spp, seed=seed)

@@ -4,15 +4,34 @@ Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl refere
 import this module; the product package never does.
 """
 import ctypes as C
+import lzma
 import os
+import struct
 import subprocess
+import sys
 
 import numpy as np
 
-from rust_tracer_b200 import abi
-
 _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _SO = os.path.join(_ROOT, "oracle", "liborc.so")
+
+
+def _abi_mirror():
+    """The ctypes mirror of include/rt_b200.h (struct layouts only, no library loading).  Inside the
+    tests it is the product package's module; bench.py --impl reference must not import the product
+    package at all, so there the same file is loaded on its own."""
+    mod = sys.modules.get("rust_tracer_b200.abi")
+    if mod is None and "rust_tracer_b200" not in sys.modules and os.environ.get("RT_ORC_STANDALONE"):
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("rt_abi_mirror", os.path.join(_ROOT, "rust_tracer_b200", "abi.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    if mod is None:
+        from rust_tracer_b200 import abi as mod
+    return mod
+
+
+abi = _abi_mirror()
 
 
 def build(force=False):
@@ -77,6 +96,30 @@ def default_scene():
     amb = (C.c_float * 3)()
     assert lib().orc_default_scene(shapes, mats, lights, amb) == 0
     return SceneArrays(shapes, mats, lights, list(amb))
+
+
+_RTSCENE_HEADER = struct.Struct("<8sII3I3i3fIQ")  # rust_tracer_b200/csrc/host/scene_file.cpp: 64 bytes
+
+
+def load_rtscene(path):
+    """Independent reader of a scene description file (.rtscene, optionally .xz): header with record
+    sizes and counts, then the rt_shape / rt_material / rt_light arrays as they are.  Lets the oracle
+    render the benchmark scenes from committed fixtures without the product library."""
+    opener = lzma.open if str(path).endswith(".xz") else open
+    with opener(path, "rb") as fh:
+        raw = fh.read()
+    magic, version, _abi_v, sb, mb, lb, ns, nm, nl, ar, ag, ab, _zero, _checksum = _RTSCENE_HEADER.unpack_from(raw)
+    if magic != b"RTSCENE\0" or version != 1 or (sb, mb, lb) != (C.sizeof(abi.rt_shape), C.sizeof(abi.rt_material), C.sizeof(abi.rt_light)):
+        raise ValueError("%s is not a scene description file of this layout" % path)
+    off = _RTSCENE_HEADER.size
+    if len(raw) != off + sb * ns + mb * nm + lb * nl:
+        raise ValueError("%s: truncated" % path)
+    shapes = (abi.rt_shape * ns).from_buffer_copy(raw, off)
+    off += sb * ns
+    mats = (abi.rt_material * nm).from_buffer_copy(raw, off)
+    off += mb * nm
+    lights = (abi.rt_light * nl).from_buffer_copy(raw, off)
+    return SceneArrays(shapes, mats, lights, (ar, ag, ab))
 
 
 def render(desc, cam, depth, rows=None, mode=0, threads=None, spp=1, seed=0, want_f32=True):

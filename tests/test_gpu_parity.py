@@ -78,16 +78,69 @@ def _row_subset(h):
     return np.array(rows, dtype=np.int32)
 
 
+def aligned_rows(h):
+    """Pixel rows whose primary rays meet the floor of the synthetic scenes (y = -2, camera at z = -8)
+    at an integer z: the ray through row v has y = -(v - h/2) * 6/h at z = 0, so it reaches y = -2 at
+    z = 8 h / (3 (v - h/2)) - 8; for v - h/2 = (8h/3) / m that is z = m - 8.  There
+    the checkerboard (src/my_scene.rs:26-43) is decided by the last bit of p.z (hard part 1)."""
+    return sorted({h // 2 + (8 * h // 3) // m for m in (10, 9, 8, 6) if (8 * h // 3) % m == 0})
+
+
 @pytest.mark.parametrize("name,depth", [("s1k", 5), ("m10k", 5)])
 def test_config3_4_true_resolution_row_subset(name, depth):
-    """BASELINE configs 3 / 4 at 3840x2160: the oracle renders a deterministic row subset
-    (rows v = 7 mod 64 here, to keep the CPU time bounded) at the true resolution."""
+    """BASELINE configs 3 / 4 at 3840x2160: the oracle renders rows v = 7 mod 16, the
+    checkerboard-aligned floor rows 1656 / 1720 / 1800 / 2040, the middle row and the last row at the
+    true resolution; every aligned row is asserted on its own, bit for bit."""
     w, h = 3840, 2160
     desc = rt.SceneDesc.builtin(name)
     f, u, st = gpu_render(desc, w, h, depth, want_f32=False)
-    rows = np.array(sorted(set(range(7, h, 64))), dtype=np.int32)
-    _, ou, _ = orc.render(desc.desc, abi.default_camera(w, h), depth, rows=rows, want_f32=False)
-    assert_parity(u[rows], ou, f"{name} 4K rows 7 mod 64")
+    special = aligned_rows(h)
+    assert special == [1656, 1720, 1800, 2040]
+    rows = np.array(sorted(set(range(7, h, 16)) | set(special) | {h // 2, h - 1}), dtype=np.int32)
+    _, ou, _ = orc.render(desc.desc, abi.default_camera(w, h), depth, rows=rows, want_f32=False, threads=os.cpu_count())
+    assert_parity(u[rows], ou, f"{name} 4K rows 7 mod 16 + aligned rows")
+    for v in special + [h // 2, h - 1]:
+        i = int(np.searchsorted(rows, v))
+        assert (u[v] == ou[i]).all(), f"{name} 4K row {v}: {int((u[v] != ou[i]).any(axis=-1).sum())} pixels differ"
+    assert (u[rows] == ou).all(), f"{name} 4K: {int((u[rows] != ou).any(axis=-1).sum())} pixels differ from the oracle"
+
+
+def test_config5_true_size_8k_spp4_depth8():
+    """BASELINE config 5 at its real size: 7680x4320, 4 spp jittered, depth 8, m10k -- a frame of 133 M
+    samples, cast in 16 bands.  The oracle renders 10 rows of it, among them the rows where the floor
+    is reached at an integer z (3312, 3440, 3600, 4080); bit-exact on the RGB8 rows."""
+    w, h, depth, spp, seed = 7680, 4320, 8, 4, 2024
+    desc = rt.SceneDesc.builtin("m10k")
+    f, u, st = gpu_render(desc, w, h, depth, spp=spp, seed=seed, want_f32=False)
+    special = aligned_rows(h)
+    assert special == [3312, 3440, 3600, 4080]
+    rows = np.array(sorted(set(special) | {7, 1000, 2160, 2700, 3000, h - 1}), dtype=np.int32)
+    _, ou, oc = orc.render(desc.desc, abi.default_camera(w, h), depth, rows=rows, spp=spp, seed=seed, want_f32=False,
+                           threads=os.cpu_count())
+    assert_parity(u[rows], ou, "config 5 at 7680x4320")
+    assert (u[rows] == ou).all(), f"config 5: {int((u[rows] != ou).any(axis=-1).sum())} pixels differ from the oracle"
+    assert st["pixels"] == w * h and st["rays"] > 10 * w * h * spp
+
+
+def test_filter_equals_all_pairs_audit_on_a_4k_share():
+    """One rank's share of the 4K m10k frame as 8 GPUs split it (row tiles of 8, rank 3): the image and
+    the counters with the bound filter, the group / quad culling, the node order and shadow rays that
+    stop at their first occluder must equal those with every (ray, shape) pair tested exactly in shape
+    order -- the reference's literal loop (src/scene/mod.rs:98-116)."""
+    desc = rt.SceneDesc.builtin("m10k")
+    w, h, depth = 3840, 2160, 5
+    sc = rt.Scene(desc)
+    try:
+        f1, u1, s1 = sc.render(w, h, depth, rank=3, world=8, rows_per_tile=8)
+        f2, u2, s2 = sc.render(w, h, depth, rank=3, world=8, rows_per_tile=8, flags=abi.RT_FLAG_AUDIT_ALL_PAIRS)
+    finally:
+        sc.close()
+    assert (u1 == u2).all(), f"{int((u1 != u2).any(axis=-1).sum())} pixels differ"
+    assert np.array_equal(f1, f2, equal_nan=True)
+    for k in ("pixels", "rays", "shadow_rays", "nodes"):
+        assert s1[k] == s2[k], k
+    assert s2["exact_tests"] == s2["rays"] * desc.desc.n_shapes
+    assert s1["exact_tests"] < s2["exact_tests"] / 100
 
 
 @pytest.mark.parametrize("name,depth", [("s1k", 5), ("m10k", 5)])
@@ -101,7 +154,7 @@ def test_config3_4_full_frame_at_eighth_resolution(name, depth):
 
 
 def test_config5_spp4_depth8_row_subset():
-    """BASELINE config 5 (4 spp jitter, depth 8) on m10k, reduced to 960x540."""
+    """BASELINE config 5 (4 spp jitter, depth 8) on m10k, reduced to 960x540 (the real size: test_config5_true_size_8k_spp4_depth8)."""
     desc = rt.SceneDesc.builtin("m10k")
     w, h = 960, 540
     f, u, st = gpu_render(desc, w, h, 8, spp=4, seed=2024, want_f32=False)
@@ -323,3 +376,67 @@ def test_scene_loaded_from_a_file_renders_the_same_frame(tmp_path):
     _, ou, oc = orc.render(back.desc, abi.default_camera(160, 90), 4)
     assert_parity(u1, ou, "scene file")
     assert st1["rays"] == oc.rays
+
+
+def test_multi_gpu_frame_equals_single_gpu_frame():
+    """rt_multi (one host call drives n devices, include/rt_b200.h) against the single-device frame:
+    host buffers (every device copies its own rows home) and the peer-mapped device frame (every
+    device's resolve kernel stores into device 0's memory).  Needs two devices; with one, the same
+    calls run on a one-device rt_multi."""
+    import torch
+    n_dev = rt.device_count()
+    devices = list(range(min(n_dev, 8)))
+    desc = rt.SceneDesc.builtin("s1k")
+    w, h, depth = 1280, 715, 5  # 715 rows: a ragged last tile
+    sc = rt.Scene(desc)
+    f0, u0, s0 = sc.render(w, h, depth)
+    sc.close()
+    for devs in ([0], devices[:2], devices):
+        m = rt.MultiScene(desc, devs)
+        try:
+            f1, u1, s1 = m.render(w, h, depth)
+            assert (u1 == u0).all() and np.array_equal(f1, f0, equal_nan=True), devs
+            for k in ("pixels", "rays", "shadow_rays", "nodes"):
+                assert s1[k] == s0[k], (k, devs)
+            frame = torch.zeros((h, w, 3), dtype=torch.uint8, device="cuda:%d" % devs[0])
+            m.render_device(w, h, depth, d_rgb_u8=frame.data_ptr())
+            torch.cuda.synchronize(devs[0])
+            assert (frame.cpu().numpy() == u0).all(), devs
+            # 4 spp, other tile height
+            _, u4, _ = m.render(w, h, depth, spp=4, seed=9, rows_per_tile=5, want_f32=False)
+        finally:
+            m.close()
+        sc = rt.Scene(desc)
+        _, r4, _ = sc.render(w, h, depth, spp=4, seed=9, want_f32=False)
+        sc.close()
+        assert (u4 == r4).all(), devs
+    u5, st5 = rt.render_multi(desc, devices, 320, 180, 3)
+    sc = rt.Scene(desc)
+    _, r5, _ = sc.render(320, 180, 3, want_f32=False)
+    sc.close()
+    assert (u5 == r5).all()
+    with pytest.raises(rt.RtError):
+        rt.MultiScene(desc, [0, 0])
+    with pytest.raises(rt.RtError):
+        rt.MultiScene(desc, [99])
+
+
+def test_scene_may_be_destroyed_before_its_forest():
+    """rt_scene_destroy with a live forest defers the free to the last rt_forest_destroy (either order
+    of the two calls is fine); reflectivity / refraction_index are frozen while a forest is alive."""
+    desc = rt.SceneDesc.builtin("default")
+    sc = rt.Scene(desc)
+    forest = sc.build_forest(96, 64, 4)
+    f0, u0, _ = forest.eval()
+    mats = desc.materials_copy()
+    mats[1].refraction_index = 1.7
+    with pytest.raises(rt.RtError) as e:
+        sc.update_materials(mats)
+    assert e.value.code == abi.RT_ERR_UNSUPPORTED
+    mats = desc.materials_copy()
+    mats[1].diffuse.rgb[:] = [0.0, 1.0, 0.0]
+    sc.update_materials(mats)  # colours may change
+    sc.close()                 # scene first ...
+    f1, u1, _ = forest.eval()  # ... the forest still works
+    assert (u1 != u0).any()
+    forest.close()

@@ -179,3 +179,17 @@ def test_cli_dump_and_reload_without_a_gpu(tmp_path):
     out = subprocess.run([CLI, "--scene-file", str(tmp_path / "none"), "--dump-scene", str(b)], capture_output=True,
                          text=True, cwd=tmp_path)
     assert out.returncode == 101 and "cannot open" in out.stderr
+
+
+def test_committed_benchmark_scene_files_equal_the_generators():
+    """tests/golden/{s1k,m10k}.rtscene.xz (what bench.py --impl reference renders, read by the oracle
+    binding's own struct-level reader) hold exactly what rt_builtin_scene builds today."""
+    for name in ("s1k", "m10k"):
+        arrays = orc.load_rtscene(os.path.join(HERE, "golden", name + ".rtscene.xz"))
+        desc = rt.SceneDesc.builtin(name)
+        d = desc.desc
+        assert (arrays.desc.n_shapes, arrays.desc.n_materials, arrays.desc.n_lights) == (d.n_shapes, d.n_materials, d.n_lights)
+        assert bytes(arrays.shapes) == C.string_at(d.shapes, C.sizeof(abi.rt_shape) * d.n_shapes)
+        assert bytes(arrays.materials) == C.string_at(d.materials, C.sizeof(abi.rt_material) * d.n_materials)
+        assert bytes(arrays.lights) == C.string_at(d.lights, C.sizeof(abi.rt_light) * d.n_lights)
+        assert list(arrays.desc.ambient) == list(d.ambient)
