@@ -5,8 +5,10 @@
 //
 //   rt_cli [-w W] [-h H] [-d DEPTH] [--method basic|rayforest] [--stats] [-t] [-i]
 //          [--scene default|s1k|m10k] [--scene-file FILE] [--dump-scene FILE] [--seed N]
-//          [--spp 1|4] [--out FILE] [--device N]
+//          [--spp 1|4] [--out FILE] [--device N] [--gpus N]
 //          [bench [-n RUNS] [-f]]
+// --gpus N renders Basic mode on the first N CUDA devices with ONE rt_multi_render call per frame
+// (the library splits the frame into interleaved row tiles and drives the devices itself).
 // --scene-file renders a scene description file (include/rt_b200_host.h) instead of a built-in
 // scene; --dump-scene writes the chosen scene as such a file and exits (no GPU needed).
 // --gui needs a display server (src/gui.rs, GTK): unavailable here, it is rejected.
@@ -94,7 +96,7 @@ struct Config {
     // extensions
     std::string scene = "default", scene_file, dump_scene, out;
     uint64_t seed = 0;
-    int spp = 1, device = 0;
+    int spp = 1, device = 0, gpus = 1;
 };
 
 [[noreturn]] void die(const std::string &msg) { // the reference panics (cli.rs:123 ff.)
@@ -143,6 +145,7 @@ Config parse_args(int argc, char **argv) {
         else if (a == "--spp") c.spp = (int)parse_int(value(i), "spp");
         else if (a == "--out") c.out = value(i);
         else if (a == "--device") c.device = (int)parse_int(value(i), "device");
+        else if (a == "--gpus") c.gpus = (int)parse_int(value(i), "gpus");
         else die("unexpected argument: " + a);
     }
     return c;
@@ -196,16 +199,17 @@ void draw_to_terminal(const Config &c, rt_scene *scene) {
     std::printf("\x1b[0m");
 }
 
-// render_scene_basic (main.rs:244-261)
-std::vector<uint8_t> render_scene_basic(const Config &c, rt_scene *scene) {
+// render_scene_basic (main.rs:244-261); multi != null: on all its devices with one call
+std::vector<uint8_t> render_scene_basic(const Config &c, rt_scene *scene, rt_multi *multi) {
     rt_camera cam;
     rt_camera_default((int32_t)c.width, (int32_t)c.height, &cam);
     rt_render_params p = params(c, c.depth);
     std::vector<uint8_t> u8((size_t)c.width * c.height * 3);
     auto t0 = Clock::now();
-    CHECK(rt_render(scene, &cam, &p, nullptr, u8.data(), nullptr));
+    if (multi) CHECK(rt_multi_render(multi, &cam, &p, nullptr, u8.data(), nullptr));
+    else CHECK(rt_render(scene, &cam, &p, nullptr, u8.data(), nullptr));
     std::printf("render_scene: %lldms\n", ms_since(t0));
-    if (c.to_terminal) draw_to_terminal(c, scene);
+    if (c.to_terminal && scene) draw_to_terminal(c, scene);
     return u8;
 }
 
@@ -270,7 +274,19 @@ int main(int argc, char **argv) {
         return 0;
     }
     rt_scene *scene = nullptr;
-    CHECK(rt_scene_create(desc, c.device, &scene));
+    rt_multi *multi = nullptr;
+    if (c.gpus > 1) {
+        if (c.rayforest) die("--gpus: the ray forest lives on one device; use --method basic");
+        int n = rt_device_count();
+        if (n < 0) die(std::string("rt_device_count: ") + rt_last_error());
+        if (c.gpus > n) die("--gpus " + std::to_string(c.gpus) + ": only " + std::to_string(n) + " CUDA devices");
+        std::vector<int32_t> devices;
+        for (int d = 0; d < c.gpus; ++d) devices.push_back(d);
+        CHECK(rt_multi_create(desc, devices.data(), c.gpus, &multi));
+        if (c.to_terminal) CHECK(rt_scene_create(desc, 0, &scene)); // the 100x50 terminal preview: one device
+    } else {
+        CHECK(rt_scene_create(desc, c.device, &scene));
+    }
     std::printf("Done Creating Scene\n");
     const float *ambient = desc->ambient;
 
@@ -279,7 +295,7 @@ int main(int argc, char **argv) {
         if (!c.rayforest) {
             std::printf("Rendering in Basic Mode\n");
             auto t0 = Clock::now();
-            save(c, render_scene_basic(c, scene));
+            save(c, render_scene_basic(c, scene, multi));
             std::printf("render_basic_to_file: %lldms\n", ms_since(t0));
         } else {
             std::printf("Rendering in RayForest Mode\nGenerate Forest\n");
@@ -304,7 +320,7 @@ int main(int argc, char **argv) {
         }
     } else if (!c.rayforest) { // handle_benchmark_mode, Basic (main.rs:136-151)
         auto t0 = Clock::now();
-        for (int i = 0; i < c.runs; ++i) render_scene_basic(c, scene);
+        for (int i = 0; i < c.runs; ++i) render_scene_basic(c, scene, multi);
         print_totals(ns_since(t0), c.runs);
     } else { // RayForest (main.rs:153-217)
         std::printf("This will benchmark evaluating the complete forest\nRendering in RayForest Mode\nGenerate Forest\n");
@@ -334,6 +350,7 @@ int main(int argc, char **argv) {
         print_totals(ns, c.runs);
         rt_forest_destroy(forest);
     }
+    rt_multi_destroy(multi);
     rt_scene_destroy(scene);
     rt_scene_desc_free(desc);
     return 0;

@@ -92,3 +92,21 @@ def test_cli_renders_a_scene_file(tmp_path):
     assert r.returncode == 0, r.stderr
     _, ou, _ = orc.render(orc.default_scene().desc, abi.default_camera(w, h), d)
     assert (read_png_rgb8(out) == ou).all()
+
+
+@pytest.mark.gpu
+def test_cli_gpus_flag_renders_the_same_image(tmp_path):
+    """--gpus N (SURVEY 5): Basic mode through one rt_multi_render call per frame on the first N devices;
+    the PNG equals the one-device PNG.  With one device in the box only the refusals are checked."""
+    import rust_tracer_b200 as rt
+    n = rt.device_count()
+    assert "only %d CUDA devices" % n in run("--gpus", str(n + 1), "-w", "8", "-h", "8").stderr
+    assert "--method basic" in run("--gpus", "2", "--method", "rayforest", "-w", "8", "-h", "8").stderr
+    if n < 2:
+        return
+    w, h, d = 200, 131, 4
+    one, many = str(tmp_path / "one.png"), str(tmp_path / "many.png")
+    assert run("-w", str(w), "-h", str(h), "-d", str(d), "--out", one).returncode == 0
+    r = run("-w", str(w), "-h", str(h), "-d", str(d), "--gpus", str(min(n, 8)), "--out", many)
+    assert r.returncode == 0, r.stderr
+    assert (read_png_rgb8(one) == read_png_rgb8(many)).all()
