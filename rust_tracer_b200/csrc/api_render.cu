@@ -50,9 +50,11 @@ void Workspace::release_pools() {
     cudaFree(p.t_crefl); cudaFree(p.t_crefr); cudaFree(p.t_root); cudaFree(p.t_hitid); cudaFree(p.t_order);
     cudaFree(p.s_a); cudaFree(p.s_b); cudaFree(p.s_key);
     unsigned int *c = p.counters, *b = p.bins;
+    const int bits = p.node_bits;
     std::memset(&p, 0, sizeof(p));
     p.counters = c;
     p.bins = b;
+    p.node_bits = bits;
 }
 
 void Workspace::release() {
@@ -174,7 +176,8 @@ int Workspace::ensure_batch_counters(int n) {
 int Workspace::ensure_misc() {
     int rc;
     if (!pools.counters && (rc = dev_alloc(&pools.counters, N_COUNTERS, "counters"))) return rc;
-    if (!pools.bins && (rc = dev_alloc(&pools.bins, NODE_BINS + 2, "bins"))) return rc;
+    if (!pools.bins && (rc = dev_alloc(&pools.bins, (size_t)node_bins(NODE_BIN_BITS_MAX) + 2, "bins"))) return rc;
+    pools.node_bits = std::min(std::max(tuning().node_bits, 3), NODE_BIN_BITS_MAX);
     if (!exact_counter && (rc = dev_alloc(&exact_counter, N_SWEEP_COUNTERS, "exact_counter"))) return rc;
     if (!h_counters) {
         cudaError_t e = cudaMallocHost((void **)&h_counters, N_COUNTERS * sizeof(unsigned int) + N_SWEEP_COUNTERS * sizeof(unsigned long long));

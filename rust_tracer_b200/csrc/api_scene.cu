@@ -647,7 +647,7 @@ int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
     std::memset(&d, 0, sizeof(d));
     d.n_shapes = n; d.n_bounded = nb; d.n_planes = (int)plane_shape.size();
     d.n_slots = n_slots; d.segs = segs; d.cmax = round_up_f32(cmax * (1.0 + 1e-6));
-    { // node cells: the box around the bounded shapes, NODE_BIN_BITS bits per axis (hit points outside are clamped)
+    { // node cells: the box around the bounded shapes, Pools::node_bits bits per axis (hit points outside are clamped)
         double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
         for (const Bound &b : slots) {
             if (b.w == 3.402823466e+38f || b.w == -3.402823466e+38f) continue;
@@ -864,6 +864,7 @@ const Knob KNOBS[] = {
     {"tail_pct", &Tuning::tail_pct, 0, 100},               {"tail_mult", &Tuning::tail_mult, 1, 64},
     {"item_max", &Tuning::item_max, 0, 32},                {"table_cap", &Tuning::table_cap, 0, 1 << 24},
     {"merge_lights", &Tuning::merge_lights, 0, 1},         {"heavy_allow", &Tuning::heavy_allow, 0, 1 << 24},
+    {"node_bits", &Tuning::node_bits, 3, NODE_BIN_BITS_MAX},
     {"band_samples", &Tuning::band_samples, 1 << 10, 1 << 28}, {"origin_tables", &Tuning::origin_tables, 0, 1},
     {"origin_min_slots", &Tuning::origin_min_slots, 0, 1 << 24}, {"host_threads", &Tuning::host_threads, 1, 64},
     {"shadow_anyhit", &Tuning::shadow_anyhit, 0, 1},       {"trace", &Tuning::trace, 0, 1},

@@ -81,7 +81,8 @@ struct Pools {
     // node order (may be null: tree-ray order): the tree rays of the level being spawned, hits
     // first in Morton order of their hit points, then the misses; bins[] is its histogram
     int *t_order;
-    unsigned int *bins;           // NODE_BINS + 2 words
+    unsigned int *bins;           // node_bins(NODE_BIN_BITS_MAX) + 2 words
+    int node_bits;                // bits per axis of the node cells inside the shapes' box (tuning.h: node_bits)
     // shadow rays
     float4 *s_a, *s_b;            // per level: [light][node] (ordered spawn) or [node][light]
     unsigned long long *s_key;
@@ -105,9 +106,10 @@ struct FrameParams {
 
 constexpr int N_COUNTERS = 6;
 constexpr int N_SWEEP_COUNTERS = 5 + MAX_SEGS; // launch_sweep's exact_counter: exact tests, general evals, origin evals, slot evals per segment, exact sphere / triangle tests
-constexpr int NODE_BIN_BITS = 5, NODE_FAR_BITS = 4; // per axis: hit points inside / outside the shapes' box
+constexpr int NODE_BIN_BITS_MAX = 7, NODE_FAR_BITS = 4; // per axis: hit points inside (Pools::node_bits <= MAX) / outside the shapes' box
 constexpr int NODE_FAR_BINS = 1 << (3 * NODE_FAR_BITS);
-constexpr int NODE_BINS = NODE_FAR_BINS + (1 << (3 * NODE_BIN_BITS)); // + one bin for the rays that missed
+// bins of the node order for `bits` bits per axis; bin node_bins(bits) itself counts the rays that missed
+__host__ __device__ constexpr int node_bins(int bits) { return NODE_FAR_BINS + (1 << (3 * bits)); }
 
 // Primary rays for samples [s0, s0 + n) of this call into tree rays [0, n).
 void launch_raygen(const FrameParams &fp, const Pools &p, long long sample0, int n, cudaStream_t stream);

@@ -49,6 +49,12 @@
 
 namespace rt {
 
+#ifndef RT_SWEEP_COEF_ONCE
+#define RT_SWEEP_COEF_ONCE 0
+#endif
+#ifndef RT_SWEEP_BULK_TABLE
+#define RT_SWEEP_BULK_TABLE 1 // 0: the table is copied by the CTA's threads behind a block barrier (A/B builds only)
+#endif
 constexpr int QCAP = 256;                // queued pairs per warp
 constexpr float U24 = 5.9604645e-08f;    // 2^-24, unit round-off of f32
 constexpr float GROUP_MARGIN = 17.f;     // margin of a group sphere / margin of a bound (make_group: a / rho <= 16)
@@ -404,6 +410,18 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         for (int g = 0; g < MAX_SEGS; ++g) n_slot[warp][g] = 0;
     }
     __syncthreads();
+#if !RT_SWEEP_BULK_TABLE
+    {
+        const float4 *src = (ORIGIN ? ot.bound : sc.bound) + slot_begin;
+        for (int k = tid; k < n_tab; k += SWEEP_THREADS) tab[k] = src[k];
+        const float4 *gsrc = (ORIGIN ? ot.group : sc.group) + slot_begin / GROUP_SLOTS;
+        for (int k = tid; k < n_gtab; k += SWEEP_THREADS) gtab[k] = gsrc[k];
+        const float4 *qsrc = (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS;
+        for (int k = tid; k < n_qtab; k += SWEEP_THREADS) qtab[k] = qsrc[k];
+    }
+    __syncthreads();
+    bool table_ready = true;
+#else
     if (tid == 0) { // the table: slots, groups, quads -- three contiguous runs of float4
         const unsigned int b_tab = (unsigned int)n_tab * sizeof(float4), b_g = (unsigned int)n_gtab * sizeof(float4),
                            b_q = (unsigned int)n_qtab * sizeof(float4);
@@ -413,6 +431,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         bulk_load(qtab, (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS, b_q, &tab_bar);
     }
     bool table_ready = false; // this warp has seen the copies land
+#endif
     const float4 *tab0 = tab - slot_begin;                 // indexed by absolute slot
     const float4 *gtab0 = gtab - slot_begin / GROUP_SLOTS; // indexed by absolute group
     const float4 *qtab0 = qtab - slot_begin / QUAD_SLOTS;  // indexed by absolute quad
@@ -523,9 +542,12 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         for (int g = 0; g < sc.segs.n && alive; ++g) {
             const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
             if (gb >= ge) continue;
-            // the coefficients depend on the segment through its margin factor only: rebuilt when it changes
+            // the coefficients depend on the segment through its margin factor only
             const float k_seg = ORIGIN ? sc.segs.kx[g] : sc.segs.k[g];
-            if (k_seg != k_cur) {
+#if RT_SWEEP_COEF_ONCE
+            if (k_seg != k_cur) // rebuilt only when it changes (costs registers: the old set stays live across the rebuild)
+#endif
+            {
                 k_cur = k_seg;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {

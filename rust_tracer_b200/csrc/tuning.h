@@ -21,6 +21,7 @@ struct Tuning {
     int table_cap = 0;          // sweep: bound slots per shared-memory chunk; 0 = what fits (tests force chunks)
     int merge_lights = 1;       // wavefront: all lights' shadow rays of a level in one launch
     int heavy_allow = 65536;    // wavefront: slack on the count of expensive child rays
+    int node_bits = 5;          // wavefront: bits per axis of the node order's cells (3..7)
     int band_samples = 1 << 23; // render: samples per band
     int origin_tables = 1;      // scene: build per-light / camera origin tables
     int origin_min_slots = 256; // scene: ... only for tables of at least this many slots

@@ -1,7 +1,7 @@
 """Device time of one workload's frame under scheduling knobs (rt_debug_set), for A/B runs on the GPU box.
 
-    python tools/frame_time.py c4 [world=8 rank=0] [knob=value ...] [-- knob=value ...]
-Each `--` starts another variant; prints ms per frame (total, sweeps) and the sweeps' counters for every variant.
+    python tools/frame_time.py c4 [lib=build/variants/X/librt_b200.so] [world=8 rank=0] [knob=value ...] [-- knob=value ...]
+lib= loads another build of the library (tools/build_variant.sh) for the whole run.  Each `--` starts another variant; prints ms per frame (total, sweeps) and the sweeps' counters for every variant.
 """
 import os
 import sys
@@ -16,7 +16,11 @@ def main():
     wl = bench.WORKLOADS[sys.argv[1]]
     variants, cur = [], {}
     for a in sys.argv[2:]:
-        if a == "--":
+        if a.startswith("lib="):
+            from rust_tracer_b200 import _lib
+            _lib.LIB_PATH = os.path.join(ROOT, a[4:])
+            print("library:", a[4:], flush=True)
+        elif a == "--":
             variants.append(cur)
             cur = {}
         else:
