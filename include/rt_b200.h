@@ -228,7 +228,8 @@ int rt_scene_set_stream(rt_scene *scene, void *stream);
  * last of them is destroyed (either order of the two destroy calls is fine).                  */
 void rt_scene_destroy(rt_scene *scene);
 /* Destroyed scenes and forests leave their ray pools (device memory) cached, one set per
- * device, for the next scene; rt_trim frees the cache of `device` (-1: every device).     */
+ * device, for the next scene; rt_trim frees the cache of `device` (-1: every device, and the
+ * host-side tables kept for the last scene description built).                            */
 int rt_trim(int32_t device);
 
 /* ---- Basic renderer ------------------------------------------------------------------ */

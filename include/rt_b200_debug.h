@@ -21,7 +21,7 @@ extern "C" {
 
 /* name: a field of rt::Tuning ("rays_per_thread", "want_light", "want_heavy", "slices",
  * "tail_pct", "tail_mult", "item_max", "table_cap", "merge_lights", "heavy_allow", "node_bits",
- * "band_samples", "origin_tables", "origin_min_slots", "host_threads", "shadow_anyhit",
+ * "band_samples", "origin_tables", "origin_min_slots", "host_threads", "scene_cache", "shadow_anyhit",
  * "trace").  Process-wide; takes effect at the next call (scene knobs: at the next
  * rt_scene_create).  RT_ERR_INVALID for an unknown name or a value out of range.          */
 int rt_debug_set(const char *name, int64_t value);

@@ -23,6 +23,8 @@ struct Workspace {
     int rows_cap = 0;
     unsigned char *mask = nullptr; // per-sample "re-shade" flags (filtered forest eval)
     long long mask_cap = 0;
+    int *idx = nullptr;            // the re-shaded pixels of a filtered forest eval (+ their count behind the list)
+    long long idx_cap = 0;
     unsigned int *h_counters = nullptr; // pinned mirror of pools.counters
     unsigned long long *exact_counter = nullptr;
     unsigned int *batch_counters = nullptr; // one work counter per sweep launch of a band
@@ -36,6 +38,7 @@ struct Workspace {
     int ensure_samples(long long n);
     int ensure_rows(int n);
     int ensure_mask(long long n);
+    int ensure_idx(long long n);
     int ensure_misc();
     int ensure_batch_counters(int n);
     void release_pools();
@@ -95,6 +98,9 @@ struct HostScene {
 };
 
 int build_host_scene(const rt_scene_desc *desc, HostScene &hs);
+// The tables for `desc`: those of the last description built if it is the same one byte for byte, else a new build.
+int host_scene_for(const rt_scene_desc *desc, std::shared_ptr<const HostScene> *out);
+void drop_scene_cache();
 } // namespace rt
 
 struct rt_scene {
@@ -134,7 +140,7 @@ struct Outputs {
 int check_params(const rt_scene *scene, const rt_camera *cam, const rt_render_params *pr);
 // The whole render of one call on the scene's device; returns after the work is complete.
 int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_params *pr, Outputs out, rt_stats *stats);
-int ensure_staging(rt_scene *scene, size_t n_ch, bool want_f32, bool want_u8);
+int ensure_staging(Workspace &ws, size_t n_ch, bool want_f32, bool want_u8);
 // Free a scene whose last user is gone (rt_scene_destroy, or the last forest of a destroyed scene).
 void scene_free(rt_scene *scene);
 } // namespace rt

@@ -180,10 +180,9 @@ int rt_multi_create(const rt_scene_desc *desc, const int32_t *devices, int32_t n
         for (int j = 0; j < i; ++j)
             if (devices[j] == devices[i]) return fail(RT_ERR_INVALID, "device %d listed twice", devices[i]);
     }
-    std::shared_ptr<HostScene> hs;
+    std::shared_ptr<const HostScene> hs;
     rt_multi *m = nullptr;
     try {
-        hs = std::make_shared<HostScene>();
         m = new rt_multi();
         m->devices.assign(devices, devices + n_devices);
         m->scenes.assign(n_devices, nullptr);
@@ -193,7 +192,7 @@ int rt_multi_create(const rt_scene_desc *desc, const int32_t *devices, int32_t n
         delete m;
         return fail(RT_ERR_NOMEM, "out of host memory or threads");
     }
-    int rc = build_host_scene(desc, *hs); // once, for all devices
+    int rc = host_scene_for(desc, &hs); // once, for all devices
     if (rc != RT_OK) {
         delete m;
         return rc;
@@ -257,7 +256,7 @@ int rt_multi_render(rt_multi *m, const rt_camera *camera, const rt_render_params
         CK(cudaSetDevice(scene->device), "cudaSetDevice");
         const int32_t my_rows = rt_tile_rows_for_rank(camera->y_res, i, n, pr.tile_rows, nullptr, 0);
         const size_t n_ch = (size_t)my_rows * (size_t)camera->x_res * 3;
-        int rc = ensure_staging(scene, n_ch, rgb_f32 != nullptr, rgb_u8 != nullptr);
+        int rc = ensure_staging(scene->ws, n_ch, rgb_f32 != nullptr, rgb_u8 != nullptr);
         if (rc != RT_OK) return rc;
         Outputs out;
         out.d_f32 = rgb_f32 ? (float *)scene->ws.out_f32 : nullptr;

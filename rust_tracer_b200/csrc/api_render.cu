@@ -49,11 +49,12 @@ void Workspace::release_pools() {
     cudaFree(p.t_a); cudaFree(p.t_b); cudaFree(p.t_key); cudaFree(p.t_parent); cudaFree(p.t_sbase);
     cudaFree(p.t_crefl); cudaFree(p.t_crefr); cudaFree(p.t_root); cudaFree(p.t_hitid); cudaFree(p.t_order);
     cudaFree(p.s_a); cudaFree(p.s_b); cudaFree(p.s_key);
-    unsigned int *c = p.counters, *b = p.bins;
+    unsigned int *c = p.counters, *b = p.bins, *bs = p.bin_sums;
     const int bits = p.node_bits;
     std::memset(&p, 0, sizeof(p));
     p.counters = c;
     p.bins = b;
+    p.bin_sums = bs;
     p.node_bits = bits;
 }
 
@@ -61,9 +62,11 @@ void Workspace::release() {
     release_pools();
     cudaFree(pools.counters); pools.counters = nullptr;
     cudaFree(pools.bins); pools.bins = nullptr;
+    cudaFree(pools.bin_sums); pools.bin_sums = nullptr;
     cudaFree(sample_rgb); sample_rgb = nullptr; sample_cap = 0;
     cudaFree(rows); rows = nullptr; rows_cap = 0;
     cudaFree(mask); mask = nullptr; mask_cap = 0;
+    cudaFree(idx); idx = nullptr; idx_cap = 0;
     if (h_counters) cudaFreeHost(h_counters);
     h_counters = nullptr;
     cudaFree(exact_counter); exact_counter = nullptr;
@@ -163,6 +166,15 @@ int Workspace::ensure_mask(long long n) {
     return rc;
 }
 
+int Workspace::ensure_idx(long long n) {
+    if (idx_cap >= n && idx) return RT_OK;
+    cudaFree(idx);
+    idx = nullptr; idx_cap = 0;
+    int rc = dev_alloc(&idx, (size_t)std::max<long long>(n, 1) + 1, "idx"); // + the counter behind the list
+    if (rc == RT_OK) idx_cap = std::max<long long>(n, 1);
+    return rc;
+}
+
 int Workspace::ensure_batch_counters(int n) {
     n = std::max(n, BATCH_COUNTERS_MIN);
     if (batch_counters && batch_cap >= n) return RT_OK;
@@ -177,7 +189,8 @@ int Workspace::ensure_misc() {
     int rc;
     if (!pools.counters && (rc = dev_alloc(&pools.counters, N_COUNTERS, "counters"))) return rc;
     if (!pools.bins && (rc = dev_alloc(&pools.bins, (size_t)node_bins(NODE_BIN_BITS_MAX) + 2, "bins"))) return rc;
-    pools.node_bits = std::min(std::max(tuning().node_bits, 3), NODE_BIN_BITS_MAX);
+    if (!pools.bin_sums && (rc = dev_alloc(&pools.bin_sums, NODE_BIN_CHUNKS_MAX, "bin_sums"))) return rc;
+    pools.node_bits = tuning().node_bits == 0 ? 5 : std::min(std::max(tuning().node_bits, 3), NODE_BIN_BITS_MAX); // 0: by level size (cast_band)
     if (!exact_counter && (rc = dev_alloc(&exact_counter, N_SWEEP_COUNTERS, "exact_counter"))) return rc;
     if (!h_counters) {
         cudaError_t e = cudaMallocHost((void **)&h_counters, N_COUNTERS * sizeof(unsigned int) + N_SWEEP_COUNTERS * sizeof(unsigned long long));
@@ -408,8 +421,11 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     int k = 0;
     for (; k < fp.depth; ++k) {
         sweep_level(k, tb, te, sb, se, heavy_tree, heavy_nodes);
+        // cells of the node order: the more nodes a level has, the finer (a warp's 128 consecutive nodes then lie
+        // closer together and its beam touches fewer groups); measured on c4: 7 bits at 8 M nodes, 5 below 250 k
+        if (tuning().node_bits == 0) p.node_bits = (te - tb) >= (2 << 20) ? 7 : ((te - tb) >= (1 << 18) ? 6 : 5);
         launch_spawn(sc, fp, p, tb, te, (k + 1 < fp.depth) ? 1 : 0, by_origin ? 1 : 0, se, st);
-        if (te > tb) scene->launches += by_origin ? 4 : 1;
+        if (te > tb) scene->launches += by_origin ? 5 : 1;
         CK(cudaMemcpyAsync(ws.h_counters, p.counters, N_COUNTERS * sizeof(unsigned int), cudaMemcpyDeviceToHost, st), "counters readback");
         CK(cudaStreamSynchronize(st), "wavefront level");
         if (ws.h_counters[3]) return 1; // pool overflow
@@ -556,8 +572,7 @@ static int cast_band_sized(rt_scene *scene, Workspace &ws, const FrameParams &fp
 }
 
 // Device staging buffers of n_ch channels for a host-buffer call (kept with the workspace).
-int ensure_staging(rt_scene *scene, size_t n_ch, bool want_f32, bool want_u8) {
-    Workspace &ws = scene->ws;
+int ensure_staging(Workspace &ws, size_t n_ch, bool want_f32, bool want_u8) {
     int rc;
     if (want_f32 && ws.out_f32_cap < n_ch * sizeof(float)) {
         cudaFree(ws.out_f32);
@@ -684,7 +699,7 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_render_params *
     Workspace &ws = scene->ws;
     int32_t n_rows = rt_tile_rows_for_rank(camera->y_res, params->rank, params->world, params->tile_rows, nullptr, 0);
     size_t n_ch = (size_t)n_rows * (size_t)camera->x_res * 3;
-    if ((rc = ensure_staging(scene, n_ch, rgb_f32 != nullptr, rgb_u8 != nullptr)) != RT_OK) return rc;
+    if ((rc = ensure_staging(scene->ws, n_ch, rgb_f32 != nullptr, rgb_u8 != nullptr)) != RT_OK) return rc;
     Outputs out;
     out.d_f32 = rgb_f32 ? (float *)ws.out_f32 : nullptr;
     out.d_u8 = rgb_u8 ? (unsigned char *)ws.out_u8 : nullptr;
@@ -789,6 +804,7 @@ void rt_forest_destroy(rt_forest *forest) {
 }
 
 int rt_trim(int32_t device) {
+    if (device < 0) drop_scene_cache();
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
@@ -823,9 +839,7 @@ static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *i
     uint64_t evaluated = (uint64_t)n;
     struct Temps { // freed on every way out
         int *d_ids = nullptr;
-        float *d_f32 = nullptr;
-        unsigned char *d_u8 = nullptr;
-        ~Temps() { cudaFree(d_ids); cudaFree(d_f32); cudaFree(d_u8); }
+        ~Temps() { cudaFree(d_ids); }
     } tmp;
     int *&d_ids = tmp.d_ids;
     if (filtered) {
@@ -845,32 +859,52 @@ static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *i
     lv.se = f->se;
     lv.light_major = f->light_major;
     if ((rc = shade_band(scene, sc, ws, f->fp, lv, mask)) != RT_OK) return rc;
-    size_t n_ch = (size_t)n * 3;
-    float *&d_f32 = tmp.d_f32;
-    unsigned char *&d_u8 = tmp.d_u8;
-    if (rgb_f32 && n_ch) {
-        CK(cudaMalloc((void **)&d_f32, n_ch * sizeof(float)), "cudaMalloc(out)");
-        if (filtered) CK(cudaMemcpyAsync(d_f32, rgb_f32, n_ch * sizeof(float), cudaMemcpyHostToDevice, st), "H2D inout");
+    const size_t n_ch = (size_t)n * 3;
+    // device staging kept with the forest's workspace: no allocation per call
+    if ((rc = ensure_staging(ws, std::max<size_t>(n_ch, 1), rgb_f32 != nullptr, rgb_u8 != nullptr)) != RT_OK) return rc;
+    float *d_f32 = rgb_f32 ? (float *)ws.out_f32 : nullptr;
+    unsigned char *d_u8 = rgb_u8 ? (unsigned char *)ws.out_u8 : nullptr;
+    if (!filtered) {
+        launch_resolve(ws.sample_rgb, 0, n, 1, d_f32, d_u8, nullptr, nullptr, 0, st);
+        cudaEventRecord(ev1, st);
+        if (d_f32 && n_ch) CK(cudaMemcpyAsync(rgb_f32, d_f32, n_ch * sizeof(float), cudaMemcpyDeviceToHost, st), "D2H");
+        if (d_u8 && n_ch) CK(cudaMemcpyAsync(rgb_u8, d_u8, n_ch, cudaMemcpyDeviceToHost, st), "D2H");
+        CK(cudaStreamSynchronize(st), "forest eval");
+    } else {
+        // render_forest_filter leaves the pixels of untouched trees as they are (render_tree.rs:129-145): only
+        // the re-shaded pixels travel -- compacted on the device as (pixel number, colour), scattered into the
+        // caller's buffers here.  Nothing of the caller's image goes to the device.
+        if ((rc = ws.ensure_idx(n)) != RT_OK) return rc;
+        unsigned int *d_count = (unsigned int *)(ws.idx + ws.idx_cap);
+        CK(cudaMemsetAsync(d_count, 0, sizeof(unsigned int), st), "count clear");
+        launch_resolve_compact(ws.sample_rgb, n, mask, ws.idx, d_count, d_f32, d_u8, st);
+        cudaEventRecord(ev1, st);
+        unsigned int count = 0;
+        CK(cudaMemcpyAsync(&count, d_count, sizeof(count), cudaMemcpyDeviceToHost, st), "D2H count");
+        CK(cudaStreamSynchronize(st), "forest eval");
+        evaluated = count;
+        if (count > 0 && (rgb_f32 || rgb_u8)) {
+            std::vector<int> idx(count);
+            std::vector<float> cf;
+            std::vector<unsigned char> cu;
+            CK(cudaMemcpyAsync(idx.data(), ws.idx, sizeof(int) * count, cudaMemcpyDeviceToHost, st), "D2H idx");
+            if (rgb_f32) {
+                cf.resize((size_t)count * 3);
+                CK(cudaMemcpyAsync(cf.data(), d_f32, sizeof(float) * 3 * count, cudaMemcpyDeviceToHost, st), "D2H");
+            }
+            if (rgb_u8) {
+                cu.resize((size_t)count * 3);
+                CK(cudaMemcpyAsync(cu.data(), d_u8, (size_t)3 * count, cudaMemcpyDeviceToHost, st), "D2H");
+            }
+            CK(cudaStreamSynchronize(st), "forest eval");
+            for (unsigned int k = 0; k < count; ++k) {
+                const size_t o = (size_t)idx[k] * 3;
+                if (rgb_f32) { rgb_f32[o] = cf[3 * k]; rgb_f32[o + 1] = cf[3 * k + 1]; rgb_f32[o + 2] = cf[3 * k + 2]; }
+                if (rgb_u8) { rgb_u8[o] = cu[3 * k]; rgb_u8[o + 1] = cu[3 * k + 1]; rgb_u8[o + 2] = cu[3 * k + 2]; }
+            }
+        }
     }
-    if (rgb_u8 && n_ch) {
-        CK(cudaMalloc((void **)&d_u8, n_ch), "cudaMalloc(out)");
-        if (filtered) CK(cudaMemcpyAsync(d_u8, rgb_u8, n_ch, cudaMemcpyHostToDevice, st), "H2D inout");
-    }
-    launch_resolve(ws.sample_rgb, 0, n, 1, d_f32, d_u8, mask, nullptr, 0, st);
-    cudaEventRecord(ev1, st);
-    if (d_f32) CK(cudaMemcpyAsync(rgb_f32, d_f32, n_ch * sizeof(float), cudaMemcpyDeviceToHost, st), "D2H");
-    if (d_u8) CK(cudaMemcpyAsync(rgb_u8, d_u8, n_ch, cudaMemcpyDeviceToHost, st), "D2H");
-    std::vector<unsigned char> hmask;
-    if (filtered && n > 0) {
-        hmask.resize(n);
-        CK(cudaMemcpyAsync(hmask.data(), ws.mask, (size_t)n, cudaMemcpyDeviceToHost, st), "D2H mask");
-    }
-    CK(cudaStreamSynchronize(st), "forest eval");
     CK(cudaGetLastError(), "forest eval");
-    if (filtered) {
-        evaluated = 0;
-        for (unsigned char m : hmask) evaluated += m ? 1 : 0;
-    }
     if (n_evaluated) *n_evaluated = evaluated;
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));

@@ -81,7 +81,8 @@ struct Pools {
     // node order (may be null: tree-ray order): the tree rays of the level being spawned, hits
     // first in Morton order of their hit points, then the misses; bins[] is its histogram
     int *t_order;
-    unsigned int *bins;           // node_bins(NODE_BIN_BITS_MAX) + 2 words
+    unsigned int *bins;           // node_bins(NODE_BIN_BITS_MAX) + 2 words (16-byte aligned)
+    unsigned int *bin_sums;       // NODE_BIN_CHUNKS_MAX words: totals / prefixes of the bins' scan chunks (wavefront.cu)
     int node_bits;                // bits per axis of the node cells inside the shapes' box (tuning.h: node_bits)
     // shadow rays
     float4 *s_a, *s_b;            // per level: [light][node] (ordered spawn) or [node][light]
@@ -110,6 +111,7 @@ constexpr int NODE_BIN_BITS_MAX = 7, NODE_FAR_BITS = 4; // per axis: hit points 
 constexpr int NODE_FAR_BINS = 1 << (3 * NODE_FAR_BITS);
 // bins of the node order for `bits` bits per axis; bin node_bins(bits) itself counts the rays that missed
 __host__ __device__ constexpr int node_bins(int bits) { return NODE_FAR_BINS + (1 << (3 * bits)); }
+constexpr int NODE_BIN_CHUNKS_MAX = 1024; // scan chunks of 4096 bins: covers node_bins(NODE_BIN_BITS_MAX) + 1
 
 // Primary rays for samples [s0, s0 + n) of this call into tree rays [0, n).
 void launch_raygen(const FrameParams &fp, const Pools &p, long long sample0, int n, cudaStream_t stream);
@@ -136,6 +138,11 @@ void launch_shade(const DevScene &sc, const FrameParams &fp, const Pools &p, int
 void launch_resolve(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp, float *rgb_f32,
                     unsigned char *rgb_u8, const unsigned char *pixel_mask, const int *frame_rows, int width,
                     cudaStream_t stream);
+
+// render_forest_filter's write-back: the pixels with pixel_mask set, compacted as out_idx[k] = pixel number and
+// its colour at 3 k of rgb_f32 / rgb_u8 (either may be null), in no particular order; *count = how many.
+void launch_resolve_compact(const float4 *sample_rgb, int n_pixels, const unsigned char *pixel_mask, int *out_idx,
+                            unsigned int *count, float *rgb_f32, unsigned char *rgb_u8, cudaStream_t stream);
 
 // Forest bookkeeping over tree rays [0, n): sizes[root] += 1 per node (RayTree::size,
 // render_tree.rs:39-48); mask[root] = 1 if a node's Intersection::id is in ids[]

@@ -70,6 +70,9 @@ struct SweepSegs {
     float k[MAX_SEGS];
     float kx[MAX_SEGS]; // the reference's exact-test share of k: 1.5 x (25 + 15 aniso^2)
 };
+// Segments hold one kind of shape each (the sweeps count their filter evaluations per segment); what the
+// filter needs is coarser: consecutive segments with the same margin factors form one RUN, and a ray's
+// filter coefficients are built once per run (m10k: spheres and triangles share k = 108: one run).
 
 struct DevScene {
     int n_shapes;
@@ -77,6 +80,7 @@ struct DevScene {
     int n_slots;    // bound slots including pads (multiple of SEG_PAD)
     float cmax;     // max over bounds of |C| + R, rounded up
     SweepSegs segs;
+    SweepSegs runs; // segs merged where k and kx agree
     int n_planes;
     int n_lights;
     int n_point_lights;

@@ -49,9 +49,6 @@
 
 namespace rt {
 
-#ifndef RT_SWEEP_COEF_ONCE
-#define RT_SWEEP_COEF_ONCE 0
-#endif
 #ifndef RT_SWEEP_BULK_TABLE
 #define RT_SWEEP_BULK_TABLE 1 // 0: the table is copied by the CTA's threads behind a block barrier (A/B builds only)
 #endif
@@ -101,6 +98,16 @@ RT_DEV unsigned long long exact_pair(const int4 *shape_meta, const float4 *geom,
     return make_key(t, shape);
 }
 
+// A cube's 12 triangle tests, out of line: cubes are rare, and the exact stage's code is fetched by warps
+// that come from all over the filter loops (its instruction-cache misses were 45 % of its stall samples)
+__device__ __noinline__ bool exact_cube_t(const float4 *g, const float4 *cube_tris, V3 o, V3 d, float *t_out) {
+    float t, u, v, det;
+    int which;
+    if (!exact_cube(load_m34(g), cube_tris, o, d, t, which, u, v, det)) return false;
+    *t_out = t;
+    return true;
+}
+
 // The same from a slot's own copy of (kind, shape id, geometry).
 RT_DEV unsigned long long exact_slot(int kind, int shape, const float4 *g, const float4 *cube_tris, V3 o, V3 d) {
     float t;
@@ -111,9 +118,7 @@ RT_DEV unsigned long long exact_slot(int kind, int shape, const float4 *g, const
         float u, v, det;
         if (!exact_triangle(load_tri(g), o, d, t, u, v, det)) return KEY_MISS;
     } else { // cube
-        float u, v, det;
-        int which;
-        if (!exact_cube(load_m34(g), cube_tris, o, d, t, which, u, v, det)) return KEY_MISS;
+        if (!exact_cube_t(g, cube_tris, o, d, &t)) return KEY_MISS;
     }
     return make_key(t, shape);
 }
@@ -279,7 +284,7 @@ RT_DEV RayCoef ray_coef(const RayRegs &r, float k_seg, float cmax, bool usable) 
 }
 
 // Same for a launch with an origin table: direction and margin only (4 registers).
-// mu = 2^-24 (kx A^2 + 26 B^2 + 8 A B), A = |O| + cmax, B = |O'| + cmax: the reference's exact
+// mu = 2^-24 (kx A^2 + 32 B^2 + 8 A B), A = |O| + cmax, B = |O'| + cmax: the reference's exact
 // test, the filter's own rounding, and the distance of O' from the ray's line (a shadow ray's
 // direction is the rounded, normalised  light - origin).  DESIGN.md, "filter margins".
 // tf: far clip of a shadow ray in units of e = (C'.dh)^2 + mu -- a bound with e > tf lies wholly
@@ -289,6 +294,20 @@ struct RayCoefO {
     float dx, dy, dz, mu, mu_g, tf;
 };
 
+// sqrt.approx / rsqrt.approx (2 ulp): the filter's margins allow dh 4 u of error per component and every length
+// here is rounded UP by a factor far above 2 ulp, so the IEEE sqrt and the three IEEE divisions (some 90
+// instructions per ray, once per work item) are not needed
+RT_DEV float sqrt_approx(float x) {
+    float y;
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+RT_DEV float rsqrt_approx(float x) {
+    float y;
+    asm("rsqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, const OriginTable &ot, bool usable) {
     const float reach = ot.reach;
     RayCoefO c;
@@ -296,19 +315,22 @@ RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, cons
     c.mu = c.mu_g = -3.0e38f;
     c.tf = 3.4e38f;
     if (!usable) return c;
-    float n = sqrtf(fmaf(r.dx, r.dx, fmaf(r.dy, r.dy, r.dz * r.dz)));
-    float o2 = fmaf(r.ox, r.ox, fmaf(r.oy, r.oy, r.oz * r.oz));
-    float A = (sqrtf(o2) + cmax) * 1.000001f;
-    if (!(n > 0.f) || !(n < 1e18f) || !(A < 1e15f) || !(reach < 1e15f)) {
+    const float n2 = fmaf(r.dx, r.dx, fmaf(r.dy, r.dy, r.dz * r.dz));
+    const float o2 = fmaf(r.ox, r.ox, fmaf(r.oy, r.oy, r.oz * r.oz));
+    const float A = (sqrt_approx(o2) + cmax) * 1.000002f;
+    // |d| in (1e-18, 1e18): its square is a normal f32 and rsqrt.approx is good to 2 ulp
+    if (!(n2 > 1e-36f) || !(n2 < 1e36f) || !(A < 1e15f) || !(reach < 1e15f)) {
         c.mu = c.mu_g = 3.0e38f;
         return c;
     }
-    c.dx = __fdiv_rn(r.dx, n); c.dy = __fdiv_rn(r.dy, n); c.dz = __fdiv_rn(r.dz, n);
-    c.mu = U24 * 1.000001f * fmaf(kx_seg * A, A, fmaf(26.f * reach, reach, 8.f * A * reach));
+    const float inv = rsqrt_approx(n2); // dh = d / |d| to 5.3 u (2^-24) per component, which the margin below budgets
+    c.dx = r.dx * inv; c.dy = r.dy * inv; c.dz = r.dz * inv;
+    // 32 >= 1.5 x (2 x (5.3 [dh: n2 0.75 u, rsqrt.approx 2 ulp = 4 u, the product 0.5 u] + 3 [the FMA chain of b]) + 1 [the square] + 2)
+    c.mu = U24 * 1.000001f * fmaf(kx_seg * A, A, fmaf(32.f * reach, reach, 8.f * A * reach));
     c.mu_g = GROUP_MARGIN * c.mu;
     if (ot.rmax > 0.f) {
         float lx = ot.ox - r.ox, ly = ot.oy - r.oy, lz = ot.oz - r.oz;
-        float D = fmaf(1.0001f, sqrtf(fmaf(lx, lx, fmaf(ly, ly, lz * lz))) + ot.rmax, 1e-4f * reach);
+        float D = fmaf(1.0001f, sqrt_approx(fmaf(lx, lx, fmaf(ly, ly, lz * lz))) + ot.rmax, 1e-4f * reach);
         float t = fmaf(D, D, c.mu) * 1.0001f;
         if (t < 3.0e38f) c.tf = t; // NaN or overflow: no clip
     }
@@ -504,7 +526,6 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
 
         // ---- phase 1 + 2 --------------------------------------------------------------
         typename std::conditional<ORIGIN, RayCoefO, RayCoef>::type c[R];
-        float k_cur = -1.f; // margin factor the coefficients were built with
         // e[r] = (filter value of ray r against the two spheres packed in T0, T1)
         // level: 0 bound slots, 1 group spheres, 2 quad spheres (wider margins, see GROUP_MARGIN)
         auto pair_e = [&](const float4 &T0, const float4 &T1, float2 (&e)[R], int level) {
@@ -536,19 +557,21 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 alive = __any_sync(FULL, vmask != 0u);
             }
         };
+        if (!table_ready) { // first use of the table by this warp: the copies ran while it fetched and loaded its rays
+            mbar_wait(&tab_bar, 0);
+            table_ready = true;
+        }
         // filter evaluations of this item, in units of 32 (one per lane): against group / quad spheres,
-        // and (per segment) against bound slots
+        // and (per segment of the table = per kind of shape) against bound slots
         unsigned int evals_hier = 0;
-        for (int g = 0; g < sc.segs.n && alive; ++g) {
-            const int gb = max(sc.segs.begin[g], sb), ge = min(sc.segs.end[g], se);
+        // the segment of slot j (segments hold one kind of shape each; ends of unused segments are INT_MAX)
+        auto seg_of = [&](int j) { return (j >= sc.segs.end[0] ? 1 : 0) + (j >= sc.segs.end[1] ? 1 : 0) + (j >= sc.segs.end[2] ? 1 : 0); };
+        for (int g = 0; g < sc.runs.n && alive; ++g) { // runs of segments that share their margin factors
+            const int gb = max(sc.runs.begin[g], sb), ge = min(sc.runs.end[g], se);
             if (gb >= ge) continue;
-            // the coefficients depend on the segment through its margin factor only
-            const float k_seg = ORIGIN ? sc.segs.kx[g] : sc.segs.k[g];
-#if RT_SWEEP_COEF_ONCE
-            if (k_seg != k_cur) // rebuilt only when it changes (costs registers: the old set stays live across the rebuild)
-#endif
+            // the coefficients depend on the run through its margin factor only
+            const float k_seg = ORIGIN ? sc.runs.kx[g] : sc.runs.k[g];
             {
-                k_cur = k_seg;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     bool usable = (vmask >> (2 * r)) & 1u;
@@ -559,11 +582,6 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                     else c[r] = ray_coef(rr, k_seg, sc.cmax, usable);
                 }
             }
-            if (!table_ready) { // first use of the table by this warp
-                mbar_wait(&tab_bar, 0);
-                table_ready = true;
-            }
-            unsigned int evals = 0;
             for (int jq = gb; jq < ge && alive; jq += 2 * QUAD_SLOTS) {
             // which of the two quads (4 groups each) can any ray of this warp touch?
             unsigned int quads_hit;
@@ -615,6 +633,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                         const int js = jg + (lane & (GROUP_SLOTS - 1));
                         const float *ts = (const float *)(tab0 + (js & ~1)) + (js & 1);
                         const float scx = ts[0], scy = ts[2], scz = ts[4], sw = ts[6];
+                        unsigned int evals = 0;
 #pragma unroll
                         for (int r = 0; r < R; ++r) {
                             unsigned int ball = __ballot_sync(FULL, (pm >> (2 * r + h)) & 1u);
@@ -654,6 +673,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                                 }
                             }
                         }
+                        if (lane == 0) n_slot[warp][seg_of(jg)] += evals;
                         if (qn >= 32) {
                             qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
                             drop_occluded();
@@ -662,7 +682,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                     }
                     const float4 *tp = tab0 + jg;
                     float4 N0 = tp[0], N1 = tp[1]; // next slot pair, fetched one iteration ahead
-                    evals += (GROUP_SLOTS / 2) * 2 * R;
+                    if (lane == 0) n_slot[warp][seg_of(jg)] += (GROUP_SLOTS / 2) * 2 * R;
 #pragma unroll 2
                     for (int i = 0; i < GROUP_SLOTS / 2; ++i) {
                         const float4 T0 = N0, T1 = N1;
@@ -710,7 +730,6 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 }
             }
             }
-            if (lane == 0) n_slot[warp][g] += evals;
         }
         if (lane == 0) n_hier[warp] += evals_hier;
         __syncwarp();

@@ -21,11 +21,12 @@ struct Tuning {
     int table_cap = 0;          // sweep: bound slots per shared-memory chunk; 0 = what fits (tests force chunks)
     int merge_lights = 1;       // wavefront: all lights' shadow rays of a level in one launch
     int heavy_allow = 65536;    // wavefront: slack on the count of expensive child rays
-    int node_bits = 5;          // wavefront: bits per axis of the node order's cells (3..7)
+    int node_bits = 0;          // wavefront: bits per axis of the node order's cells (3..7); 0 = by the size of the level
     int band_samples = 1 << 23; // render: samples per band
     int origin_tables = 1;      // scene: build per-light / camera origin tables
     int origin_min_slots = 256; // scene: ... only for tables of at least this many slots
     int host_threads = 4;       // scene: host threads of the table build
+    int scene_cache = 1;        // scene: keep the tables of the last description built (api_scene.cu: host_scene_for)
     int shadow_anyhit = 1;      // sweep: a shadow ray stops at the first hit that occludes its light
     int trace = 0;              // print per-phase host laps and per-sweep counters to stderr
 };

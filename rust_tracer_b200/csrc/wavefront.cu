@@ -111,56 +111,96 @@ __global__ void __launch_bounds__(256) node_bin_kernel(DevScene sc, Pools p, int
     if (live && (threadIdx.x & 31) == __ffs(same) - 1) atomicAdd(&p.bins[bin], (unsigned int)__popc(same));
 }
 
-// One block: exclusive scan of bins[0 .. n_bins] in place (n_bins = node_bins(p.node_bits)); counters[1] = end
-// of the level's shadow rays.  Warp w owns the consecutive bins [w per, (w + 1) per): it first adds them up
-// (coalesced rounds of 32, four in flight), the block meets once to scan the 32 warp totals, then every
-// warp walks its run again (it is in L1 / L2 by now) with a running carry and writes the exclusive prefix.
-// 36,865 bins (5 bits per axis) take ~7 us.
-__global__ void __launch_bounds__(1024) node_scan_kernel(Pools p, int s_begin, int n_point_lights) {
+// Exclusive scan of bins[0 .. n_bins] (n_bins = node_bins(p.node_bits); up to 2 M bins) in two launches:
+//   node_scan_chunks_kernel  block b scans its chunk of SCAN_CHUNK bins in place (exclusive within the chunk)
+//                            and leaves the chunk's total in bin_sums[b];
+//   node_scan_top_kernel     one block scans the <= 1024 chunk totals in place, and reads off the two prefixes
+//                            the level needs: hits outside the box (counters[4]) and all hits (-> counters[1],
+//                            the end of the level's shadow rays).
+// The prefix of bin j is then bins[j] + bin_sums[j / SCAN_CHUNK]; node_scatter_kernel adds the two when it
+// claims places, so there is no third pass over the bins.
+constexpr int SCAN_CHUNK = 4096, SCAN_THREADS = 512, SCAN_PER_THREAD = SCAN_CHUNK / SCAN_THREADS;
+
+__global__ void __launch_bounds__(SCAN_THREADS) node_scan_chunks_kernel(Pools p) {
+    __shared__ unsigned int warp_sum[SCAN_THREADS / 32];
+    const int n = node_bins(p.node_bits) + 1;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int base = blockIdx.x * SCAN_CHUNK + tid * SCAN_PER_THREAD; // a thread owns SCAN_PER_THREAD consecutive bins (two 16-byte loads)
+    unsigned int v[SCAN_PER_THREAD];
+    if (base + SCAN_PER_THREAD <= n) {
+        const uint4 a = *(const uint4 *)(p.bins + base), b = *(const uint4 *)(p.bins + base + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < SCAN_PER_THREAD; ++k) v[k] = base + k < n ? p.bins[base + k] : 0u;
+    }
+    unsigned int mine = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_PER_THREAD; ++k) { const unsigned int x = v[k]; v[k] = mine; mine += x; } // exclusive within the thread
+    unsigned int t = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int y = __shfl_up_sync(0xffffffffu, t, o);
+        if (lane >= o) t += y;
+    }
+    if (lane == 31) warp_sum[warp] = t;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned int w = lane < SCAN_THREADS / 32 ? warp_sum[lane] : 0u, z = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int y = __shfl_up_sync(0xffffffffu, z, o);
+            if (lane >= o) z += y;
+        }
+        if (lane < SCAN_THREADS / 32) warp_sum[lane] = z - w;
+        if (lane == SCAN_THREADS / 32 - 1) p.bin_sums[blockIdx.x] = z; // the chunk's total
+    }
+    __syncthreads();
+    const unsigned int before = warp_sum[warp] + t - mine; // bins of the chunk before this thread's
+    if (base + SCAN_PER_THREAD <= n) {
+        *(uint4 *)(p.bins + base) = make_uint4(before + v[0], before + v[1], before + v[2], before + v[3]);
+        *(uint4 *)(p.bins + base + 4) = make_uint4(before + v[4], before + v[5], before + v[6], before + v[7]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < SCAN_PER_THREAD; ++k)
+            if (base + k < n) p.bins[base + k] = before + v[k];
+    }
+}
+
+__global__ void __launch_bounds__(1024) node_scan_top_kernel(Pools p, int n_chunks, int s_begin, int n_point_lights) {
     __shared__ unsigned int warp_sum[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n_bins = node_bins(p.node_bits), n = n_bins + 1;
-    const int per = ((n + 31) / 32 + 31) / 32 * 32; // bins per warp, a whole number of rounds
-    const int begin = warp * per, end = min(n, begin + per);
-    unsigned int sum = 0;
-#pragma unroll 4
-    for (int j = begin + lane; j < end; j += 32) sum += p.bins[j];
+    const unsigned int v = tid < n_chunks ? p.bin_sums[tid] : 0u; // n_chunks <= 1024
+    unsigned int t = v;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (lane == 0) warp_sum[warp] = sum;
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int y = __shfl_up_sync(0xffffffffu, t, o);
+        if (lane >= o) t += y;
+    }
+    if (lane == 31) warp_sum[warp] = t;
     __syncthreads();
     if (warp == 0) {
         unsigned int w = warp_sum[lane], z = w;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            unsigned int y = __shfl_up_sync(0xffffffffu, z, o);
+            const unsigned int y = __shfl_up_sync(0xffffffffu, z, o);
             if (lane >= o) z += y;
         }
-        warp_sum[lane] = z - w; // exclusive
+        warp_sum[lane] = z - w;
     }
     __syncthreads();
-    unsigned int carry = warp_sum[warp]; // bins before this round of the warp's run
-    for (int j0 = begin; j0 < end; j0 += 32) {
-        const int j = j0 + lane;
-        const unsigned int v = j < end ? p.bins[j] : 0u;
-        unsigned int t = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            unsigned int y = __shfl_up_sync(0xffffffffu, t, o);
-            if (lane >= o) t += y;
-        }
-        const unsigned int excl = carry + t - v;
-        carry += __shfl_sync(0xffffffffu, t, 31);
-        if (j < end) p.bins[j] = excl;
-        if (j == NODE_FAR_BINS) { // excl = number of hits outside the box
-            p.counters[4] = excl;
-            p.counters[5] = 0u;
-        }
-        if (j == n_bins) { // excl = number of hits
-            unsigned long long s_end = (unsigned long long)s_begin + (unsigned long long)excl * (unsigned long long)n_point_lights;
-            if (s_end > (unsigned long long)p.s_cap) p.counters[3] = 1u;
-            else p.counters[1] = (unsigned int)s_end;
-        }
+    const unsigned int excl = warp_sum[warp] + t - v;
+    if (tid < n_chunks) p.bin_sums[tid] = excl;
+    const int n_bins = node_bins(p.node_bits);
+    if (tid == NODE_FAR_BINS / SCAN_CHUNK) { // prefix of bin NODE_FAR_BINS = number of hits outside the box
+        p.counters[4] = excl + p.bins[NODE_FAR_BINS];
+        p.counters[5] = 0u;
+    }
+    if (tid == n_bins / SCAN_CHUNK) { // prefix of the last bin (the misses) = number of hits
+        const unsigned int hits = excl + p.bins[n_bins];
+        unsigned long long s_end = (unsigned long long)s_begin + (unsigned long long)hits * (unsigned long long)n_point_lights;
+        if (s_end > (unsigned long long)p.s_cap) p.counters[3] = 1u;
+        else p.counters[1] = (unsigned int)s_end;
     }
 }
 
@@ -172,7 +212,7 @@ __global__ void __launch_bounds__(256) node_scatter_kernel(Pools p, int begin, i
     const unsigned int same = __match_any_sync(0xffffffffu, bin);
     const int leader = __ffs(same) - 1;
     unsigned int base = 0;
-    if (live && lane == leader) base = atomicAdd(&p.bins[bin], (unsigned int)__popc(same));
+    if (live && lane == leader) base = atomicAdd(&p.bins[bin], (unsigned int)__popc(same)) + p.bin_sums[bin / SCAN_CHUNK];
     base = __shfl_sync(0xffffffffu, base, leader);
     if (live) p.t_order[begin + base + __popc(same & ((1u << lane) - 1u))] = i;
 }
@@ -414,6 +454,26 @@ resolve_kernel(const float4 *sample_rgb, long long pixel0, int n_pixels, int spp
     if (rgb_u8) { rgb_u8[o] = as_u8(c.x); rgb_u8[o + 1] = as_u8(c.y); rgb_u8[o + 2] = as_u8(c.z); }
 }
 
+// One slot per masked pixel: a warp counts its masked lanes and takes that many slots with one atomic.
+__global__ void __launch_bounds__(256)
+resolve_compact_kernel(const float4 *sample_rgb, int n_pixels, const unsigned char *pixel_mask, int *out_idx, unsigned int *count,
+                       float *rgb_f32, unsigned char *rgb_u8) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool on = i < n_pixels && pixel_mask[i];
+    const unsigned int ball = __ballot_sync(0xffffffffu, on);
+    if (!ball) return;
+    const int lane = threadIdx.x & 31;
+    unsigned int base = 0;
+    if (lane == 0) base = atomicAdd(count, (unsigned int)__popc(ball));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (!on) return;
+    const size_t k = base + __popc(ball & ((1u << lane) - 1u));
+    const float4 s = sample_rgb[i];
+    out_idx[k] = i;
+    if (rgb_f32) { rgb_f32[3 * k] = s.x; rgb_f32[3 * k + 1] = s.y; rgb_f32[3 * k + 2] = s.z; }
+    if (rgb_u8) { rgb_u8[3 * k] = as_u8(s.x); rgb_u8[3 * k + 1] = as_u8(s.y); rgb_u8[3 * k + 2] = as_u8(s.z); }
+}
+
 __global__ void forest_sizes_kernel(Pools p, int n, int *sizes) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n && p.t_hitid[i] >= 0) atomicAdd(&sizes[p.t_root[i]], 1);
@@ -439,7 +499,9 @@ void launch_spawn(const DevScene &sc, const FrameParams &fp, const Pools &p, int
     if (ordered) {
         cudaMemsetAsync(p.bins, 0, (size_t)(node_bins(p.node_bits) + 2) * sizeof(unsigned int), stream);
         node_bin_kernel<<<nblk(end - begin, 256), 256, 0, stream>>>(sc, p, begin, end);
-        node_scan_kernel<<<1, 1024, 0, stream>>>(p, s_begin, sc.n_point_lights);
+        const int n_chunks = (node_bins(p.node_bits) + 1 + SCAN_CHUNK - 1) / SCAN_CHUNK;
+        node_scan_chunks_kernel<<<n_chunks, SCAN_THREADS, 0, stream>>>(p);
+        node_scan_top_kernel<<<1, 1024, 0, stream>>>(p, n_chunks, s_begin, sc.n_point_lights);
         node_scatter_kernel<<<nblk(end - begin, 256), 256, 0, stream>>>(p, begin, end);
     }
     spawn_kernel<<<nblk(end - begin, SPAWN_BLOCK), SPAWN_BLOCK, 0, stream>>>(sc, fp, p, begin, end, spawn_children, ordered, s_begin);
@@ -456,6 +518,12 @@ void launch_resolve(const float4 *sample_rgb, long long pixel0, int n_pixels, in
     if (n_pixels > 0)
         resolve_kernel<<<nblk(n_pixels, 256), 256, 0, stream>>>(sample_rgb, pixel0, n_pixels, spp, rgb_f32, rgb_u8,
                                                                 pixel_mask, frame_rows, width);
+}
+
+void launch_resolve_compact(const float4 *sample_rgb, int n_pixels, const unsigned char *pixel_mask, int *out_idx,
+                            unsigned int *count, float *rgb_f32, unsigned char *rgb_u8, cudaStream_t stream) {
+    if (n_pixels > 0)
+        resolve_compact_kernel<<<nblk(n_pixels, 256), 256, 0, stream>>>(sample_rgb, n_pixels, pixel_mask, out_idx, count, rgb_f32, rgb_u8);
 }
 
 void launch_forest_sizes(const Pools &p, int n, int *sizes, cudaStream_t stream) {

@@ -236,7 +236,7 @@ def test_work_item_shapes_do_not_change_the_image():
     ref = None
     for knobs in ({}, {"want_light": 1}, {"want_light": 64}, {"slices": 1}, {"slices": 5}, {"item_max": 0},
                   {"item_max": 32}, {"rays_per_thread": 1}, {"rays_per_thread": 2}, {"shadow_anyhit": 0},
-                  {"shadow_anyhit": 0, "slices": 3}):
+                  {"shadow_anyhit": 0, "slices": 3}, {"node_bits": 3}, {"node_bits": 5}, {"node_bits": 6}, {"node_bits": 7}):
         with rt.tuned(**knobs):
             sc = rt.Scene(desc)
             try:
@@ -344,3 +344,38 @@ def test_any_number_of_point_lights(n_lights):
     diff = np.abs(a[1].astype(np.int32) - ou.astype(np.int32)).max(axis=-1)
     assert float((diff <= 1).mean()) >= 0.999, int(diff.max())
     assert a[2]["rays"] == oc.rays and a[2]["shadow_rays"] == oc.shadow_rays
+
+
+def test_scene_tables_kept_for_an_identical_description():
+    """rt_scene_create keeps the host-side tables of the last description it built and hands them to the
+    next scene if its description is the same byte for byte (csrc/api_scene.cu: host_scene_for); a
+    description that differs in one float gets its own build.  Same images either way."""
+    desc = rt.SceneDesc.synthetic(200, 200, 17, 0.04, 0.12)
+    w, h, depth = 160, 90, 4
+    with rt.tuned(scene_cache=0):
+        ref = _render_once(desc, w, h, depth)
+    a = _render_once(desc, w, h, depth)  # builds and keeps
+    b = _render_once(desc, w, h, depth)  # reuses
+    _assert_same(ref, a)
+    _assert_same(ref, b)
+    d = desc.desc
+    shapes = (abi.rt_shape * d.n_shapes)(*[d.shapes[i] for i in range(d.n_shapes)])
+    mats = (abi.rt_material * d.n_materials)(*[d.materials[i] for i in range(d.n_materials)])
+    lights = (abi.rt_light * d.n_lights)(*[d.lights[i] for i in range(d.n_lights)])
+    lights[0].color[0] += 0.25
+    other = rt.SceneDesc.from_arrays(shapes, mats, lights, list(d.ambient))
+    c = _render_once(other, w, h, depth)
+    assert not np.array_equal(c[0], a[0], equal_nan=True)  # not served from the kept tables
+    with rt.tuned(scene_cache=0):
+        _assert_same(c, _render_once(other, w, h, depth))
+    _assert_same(a, _render_once(desc, w, h, depth))  # and back
+    rt.trim(-1)
+    _assert_same(a, _render_once(desc, w, h, depth))
+
+
+def _render_once(desc, w, h, depth):
+    sc = rt.Scene(desc)
+    try:
+        return sc.render(w, h, depth)
+    finally:
+        sc.close()
