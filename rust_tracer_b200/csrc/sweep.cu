@@ -49,10 +49,20 @@
 
 namespace rt {
 
+#ifndef RT_SWEEP_QUAD2
+#define RT_SWEEP_QUAD2 0 // 1: quad spheres are evaluated two pairs at a time (A/B builds)
+#endif
+#ifndef RT_SWEEP_BRUTE_UNROLL
+#define RT_SWEEP_BRUTE_UNROLL 2
+#endif
+#ifndef RT_SWEEP_FLUSH_AT
+#define RT_SWEEP_FLUSH_AT 32 // queued pairs at which a group's end runs the exact stage
+#endif
 #ifndef RT_SWEEP_BULK_TABLE
 #define RT_SWEEP_BULK_TABLE 1 // 0: the table is copied by the CTA's threads behind a block barrier (A/B builds only)
 #endif
 constexpr int QCAP = 256;                // queued pairs per warp
+constexpr int BRUTE_UNROLL = RT_SWEEP_BRUTE_UNROLL;
 constexpr float U24 = 5.9604645e-08f;    // 2^-24, unit round-off of f32
 constexpr float GROUP_MARGIN = 17.f;     // margin of a group sphere / margin of a bound (make_group: a / rho <= 16)
 constexpr float QUAD_MARGIN = 3.f;       // margin of a quad sphere / margin of a group sphere (a / rho <= 2)
@@ -582,9 +592,30 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                     else c[r] = ray_coef(rr, k_seg, sc.cmax, usable);
                 }
             }
+#if RT_SWEEP_QUAD2
+            unsigned int quads_next = 0; // the verdict on the quad pair after this one, evaluated with it
+#endif
             for (int jq = gb; jq < ge && alive; jq += 2 * QUAD_SLOTS) {
             // which of the two quads (4 groups each) can any ray of this warp touch?
             unsigned int quads_hit;
+#if RT_SWEEP_QUAD2
+            // two quad pairs per evaluation: twice the independent FFMA2 chains between one vote and the next
+            if ((jq - gb) & (2 * QUAD_SLOTS)) quads_hit = quads_next;
+            else {
+                const bool two = jq + 2 * QUAD_SLOTS < ge;
+                const float4 T0 = qtab0[jq >> 6], T1 = qtab0[(jq >> 6) + 1];
+                const float4 U0 = two ? qtab0[(jq >> 6) + 2] : T0, U1 = two ? qtab0[(jq >> 6) + 3] : T1;
+                float2 e[R], f[R];
+                pair_e(T0, T1, e, 2);
+                pair_e(U0, U1, f, 2);
+                float m0 = e[0].x, m1 = e[0].y, n0 = f[0].x, n1 = f[0].y;
+#pragma unroll
+                for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); n0 = fmaxf(n0, f[r].x); n1 = fmaxf(n1, f[r].y); }
+                quads_hit = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
+                quads_next = (__any_sync(FULL, n0 >= U1.z) ? 1u : 0u) | (__any_sync(FULL, n1 >= U1.w) ? 2u : 0u);
+                evals_hier += two ? 4 * R : 2 * R;
+            }
+#else
             {
                 const float4 T0 = qtab0[jq >> 6], T1 = qtab0[(jq >> 6) + 1];
                 float2 e[R];
@@ -595,6 +626,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 quads_hit = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
                 evals_hier += 2 * R;
             }
+#endif
             // most quad pairs are touched by no ray of the warp: leave before the group loop is set up
             // (its control flow for skipped quads was 12 % of the instructions executed)
             if (!quads_hit) continue;
@@ -674,7 +706,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                             }
                         }
                         if (lane == 0) n_slot[warp][seg_of(jg)] += evals;
-                        if (qn >= 32) {
+                        if (qn >= (SHADOW ? 32 : RT_SWEEP_FLUSH_AT)) {
                             qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
                             drop_occluded();
                         }
@@ -683,7 +715,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                     const float4 *tp = tab0 + jg;
                     float4 N0 = tp[0], N1 = tp[1]; // next slot pair, fetched one iteration ahead
                     if (lane == 0) n_slot[warp][seg_of(jg)] += (GROUP_SLOTS / 2) * 2 * R;
-#pragma unroll 2
+#pragma unroll BRUTE_UNROLL
                     for (int i = 0; i < GROUP_SLOTS / 2; ++i) {
                         const float4 T0 = N0, T1 = N1;
                         N0 = tp[2 * i + 2]; N1 = tp[2 * i + 3]; // past the group: the next one's, or the table's slack pair
@@ -723,7 +755,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                             }
                         }
                     }
-                    if (qn >= 32) {
+                    if (qn >= (SHADOW ? 32 : RT_SWEEP_FLUSH_AT)) {
                         qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
                         drop_occluded();
                     }

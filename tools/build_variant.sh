@@ -8,8 +8,8 @@ NAME=$1; DEFS=${2:-}
 ROOT=$(cd "$(dirname "$0")/.." && pwd)
 V=$ROOT/build/variants
 mkdir -p $V/$NAME
-rm -rf $V/$NAME/csrc $V/include
-cp -r $ROOT/include $V/include
+rm -rf $V/$NAME/csrc
+mkdir -p $V/include && cp $ROOT/include/*.h $V/include/
 mkdir -p $V/$NAME/csrc
 (cd $ROOT/rust_tracer_b200/csrc && cp -r *.cu *.cuh *.h Makefile host $V/$NAME/csrc/)
 rm -f $V/$NAME/csrc/*.o $V/$NAME/csrc/host/*.o
