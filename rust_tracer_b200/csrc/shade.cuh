@@ -11,6 +11,7 @@ namespace rt {
 struct Hit {
     int id;       // shape id; for a cube the inner triangle 0..11 (cube.rs:93-101 never overwrites it)
     int shape;    // top-level shape id
+    int kind;     // KIND_* of the top-level shape
     int material;
     float t;
     V3 point, eye, normal;
@@ -25,13 +26,16 @@ RT_DEV void sphere_tex(V3 n, float &u, float &v) {
 }
 
 // Rebuild the Intersection the winning shape's intersect() returns.  The key only names
-// the winner; t and everything else are recomputed with the exact chain.
+// the winner; t and everything else are recomputed with the exact chain.  A sphere's texture coordinates
+// (sphere.rs:40-45: atan2f + acosf, ~250 instructions) are left to hit_tex(): nothing but a textured
+// material reads them, and the spheres of the big scenes have none.
 RT_DEV bool hit_record(const DevScene &sc, unsigned long long key, V3 o, V3 d, Hit &h) {
     if (key == KEY_MISS) return false;
     int shape = key_shape(key);
     int4 meta = sc.shape_meta[shape];
     const float4 *g = sc.geom + 3 * shape;
     h.shape = shape;
+    h.kind = meta.x;
     h.id = shape;
     h.material = meta.y;
     h.eye = vneg(vnorm(d));
@@ -46,7 +50,7 @@ RT_DEV bool hit_record(const DevScene &sc, unsigned long long key, V3 o, V3 d, H
         if (!entering) n = vneg(n);
         h.normal = n;
         h.entering = entering;
-        sphere_tex(n, h.tu, h.tv);
+        h.tu = 0.f; h.tv = 0.f; // hit_tex()
     } else if (meta.x == KIND_PLANE) { // plane.rs:59-84
         const float4 *pd = sc.plane_data + 7 * meta.z;
         V3 origin = v3(pd[0].x, pd[0].y, pd[0].z), normal = v3(pd[1].x, pd[1].y, pd[1].z);
@@ -80,6 +84,13 @@ RT_DEV bool hit_record(const DevScene &sc, unsigned long long key, V3 o, V3 d, H
     h.point = ray_at(o, d, t);
     return true;
 }
+
+// The part of the Intersection hit_record leaves out: call before evaluating a colour function that reads
+// the texture coordinate (m.ambient / diffuse / specular of kind CHECKERBOARD).
+RT_DEV void hit_tex(Hit &h) {
+    if (h.kind == KIND_SPHERE) sphere_tex(h.normal, h.tu, h.tv);
+}
+RT_DEV bool material_reads_tex(const DevMaterial &m) { return (m.ambient.kind | m.diffuse.kind | m.specular.kind) != 0; }
 
 // ---- materials (material.rs) ------------------------------------------------------------
 

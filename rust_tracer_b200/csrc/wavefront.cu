@@ -352,6 +352,7 @@ shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level
     bool is_node = hit_record(sc, p.t_key[i], o, d, h);
     if (is_node) {
         const DevMaterial m = sc.materials[h.material];
+        if (material_reads_tex(m)) hit_tex(h);
         float n1, n2;
         refraction_indices(m, h.entering, n1, n2);
         V3 ambient = cmul(eval_colorfn(m.ambient, h.tu, h.tv), v3(sc.amb_r, sc.amb_g, sc.amb_b));
