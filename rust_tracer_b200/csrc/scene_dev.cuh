@@ -31,7 +31,28 @@
 //   materials[m]   DevMaterial (64 B)
 //   lights[l]      DevLight (32 B)
 #pragma once
+#include <cstdio>
+
 #include "exact.cuh"
+
+// Checked build (tools/build_variant.sh checked "-DRT_DEBUG_CHECKS=1"): every index the kernels compute into
+// a queue, a table, a pool or a key array is tested against its bounds; a violation prints its place and
+// traps, which fails the launch.  compute-sanitizer is closed on this pool (profiles/
+// r02_compute_sanitizer_closed.txt), so this is how the GPU tests look for bad accesses.
+#ifndef RT_DEBUG_CHECKS
+#define RT_DEBUG_CHECKS 0
+#endif
+#if RT_DEBUG_CHECKS
+#define RT_CHECK(cond)                                                                  \
+    do {                                                                                \
+        if (!(cond)) {                                                                  \
+            printf("RT_CHECK failed: %s  (%s:%d, block %d thread %d)\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, (int)threadIdx.x); \
+            __trap();                                                                   \
+        }                                                                               \
+    } while (0)
+#else
+#define RT_CHECK(cond) ((void)0)
+#endif
 
 namespace rt {
 

@@ -49,6 +49,12 @@
 
 namespace rt {
 
+#ifndef RT_SWEEP_PRELOAD
+#define RT_SWEEP_PRELOAD 1 // the prologue loads the lane's R rays before it works on any of them
+#endif
+#ifndef RT_SWEEP_FLUSH_PIPE
+#define RT_SWEEP_FLUSH_PIPE 0 // 1: the exact stage fetches the next 32 pairs' operands while it tests the current 32 (A/B builds)
+#endif
 #ifndef RT_SWEEP_QUAD2
 #define RT_SWEEP_QUAD2 0 // 1: quad spheres are evaluated two pairs at a time (A/B builds)
 #endif
@@ -57,6 +63,9 @@ namespace rt {
 #endif
 #ifndef RT_SWEEP_FLUSH_AT
 #define RT_SWEEP_FLUSH_AT 32 // queued pairs at which a group's end runs the exact stage
+#endif
+#ifndef RT_SWEEP_FLUSH_AT_SHADOW
+#define RT_SWEEP_FLUSH_AT_SHADOW 32 // the same for shadow rays (sooner = rays leave the sweep sooner)
 #endif
 #ifndef RT_SWEEP_BULK_TABLE
 #define RT_SWEEP_BULK_TABLE 1 // 0: the table is copied by the CTA's threads behind a block barrier (A/B builds only)
@@ -80,6 +89,7 @@ RT_DEV bool ray_has_nan(const RayRegs &r) {
 }
 
 RT_DEV RayRegs load_ray(const RaySeg &s0, const RaySeg &s1, int gi) {
+    RT_CHECK(gi >= 0 && gi < s0.n + s1.n);
     float4 a, b;
     if (gi < s0.n) { a = s0.a[(long long)gi * s0.stride]; b = s0.b[(long long)gi * s0.stride]; }
     else { a = s1.a[gi - s0.n]; b = s1.b[gi - s0.n]; }
@@ -156,6 +166,7 @@ struct SweepCtx {
     const float4 *slot_geom;
     const float4 *cube_tris;
     float lx, ly, lz; // SHADOW: the light the rays of this CTA travel towards
+    int n_slots;      // (checked build)
 };
 
 // One ray set of a JOBS launch (sweep_kernel) with its origin table, work counter and item shapes.
@@ -190,27 +201,60 @@ struct ExactCount {
 // `all`.  Called by a converged warp.  Returns the number of pairs left in the queue.
 // SHADOW: wd2[local] = squared distance from ray `local` of the batch to its light; a hit that
 // occludes the light sets the ray's bit in wocc[] (the caller then drops the ray from the sweep).
+// The operands of one queued pair: its ray, and kind / shape id / geometry of its slot.
+struct PairOperands {
+    RayRegs rr;
+    int2 sm;
+    float4 g0, g1, g2;
+    int local;
+};
+RT_DEV PairOperands fetch_pair(const SweepCtx *ctx, const unsigned int *wqueue, int idx, int ray0) {
+    PairOperands p;
+    const unsigned int pair = wqueue[idx];
+    p.local = pair >> 24; // (ray of the warp batch << 24) | bound slot
+    const int j = pair & 0xFFFFFF;
+    RT_CHECK(p.local < 128 && j < ctx->n_slots && idx < QCAP);
+    // ray, kind and geometry are all addressed by the queue entry: independent loads, one round trip
+    p.sm = ctx->slot_meta[j];
+    const float4 *gp = ctx->slot_geom + 3 * j;
+    p.g0 = gp[0]; p.g1 = gp[1]; p.g2 = gp[2];
+    p.rr = load_ray(ctx->s0, ctx->s1, ray0 + p.local);
+    return p;
+}
+
 template <bool SHADOW>
 __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueue, unsigned long long *wbest, int ray0,
                                         int cnt, int all, ExactCount *n_exact, const float *wd2, unsigned int *wocc) {
     const int lane = threadIdx.x & 31;
     int done = 0;
     unsigned int n_sphere = 0, n_triangle = 0;
+#if RT_SWEEP_FLUSH_PIPE
+    PairOperands next;
+    bool have_next = (cnt >= 32 || (all && cnt > 0)) && lane < cnt;
+    if (have_next) next = fetch_pair(ctx, wqueue, lane, ray0);
+#endif
     while (cnt - done >= 32 || (all && done < cnt)) {
         int idx = done + lane;
         int kind = -1;
+#if RT_SWEEP_FLUSH_PIPE
+        const bool have = have_next;
+        PairOperands cur;
+        if (have) cur = next;
+        { // the batch after this one, if it will run: its loads fly while this one is tested
+            const int nd = done + 32;
+            have_next = (cnt - nd >= 32 || (all && nd < cnt)) && nd + lane < cnt;
+            if (have_next) next = fetch_pair(ctx, wqueue, nd + lane, ray0);
+        }
+        if (have) {
+#else
         if (idx < cnt) {
-            unsigned int pair = wqueue[idx];
-            int local = pair >> 24; // (ray of the warp batch << 24) | bound slot
-            int j = pair & 0xFFFFFF;
-            // ray, kind and geometry are all addressed by the queue entry: independent loads, one round trip
-            const int2 sm = ctx->slot_meta[j];
-            const float4 *gp = ctx->slot_geom + 3 * j;
-            const float4 g[3] = {gp[0], gp[1], gp[2]};
-            RayRegs rr = load_ray(ctx->s0, ctx->s1, ray0 + local);
-            kind = sm.x;
-            const V3 o = v3(rr.ox, rr.oy, rr.oz), d = v3(rr.dx, rr.dy, rr.dz);
-            unsigned long long k = exact_slot(sm.x, sm.y, g, ctx->cube_tris, o, d);
+            const PairOperands cur = fetch_pair(ctx, wqueue, idx, ray0);
+#endif
+            const float4 g[3] = {cur.g0, cur.g1, cur.g2};
+            const int local = cur.local;
+            kind = cur.sm.x;
+            const V3 o = v3(cur.rr.ox, cur.rr.oy, cur.rr.oz), d = v3(cur.rr.dx, cur.rr.dy, cur.rr.dz);
+            unsigned long long k = exact_slot(cur.sm.x, cur.sm.y, g, ctx->cube_tris, o, d);
             if (k != KEY_MISS) {
                 atomicMin(&wbest[local], k);
                 if constexpr (SHADOW) {
@@ -218,6 +262,7 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
                 }
             }
         }
+        (void)idx;
         n_sphere += __popc(__ballot_sync(0xffffffffu, kind == KIND_SPHERE));
         n_triangle += __popc(__ballot_sync(0xffffffffu, kind == KIND_TRIANGLE));
         done += 32;
@@ -433,6 +478,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         ctx.s0 = s0; ctx.s1 = s1;
         ctx.slot_meta = sc.slot_meta; ctx.slot_geom = sc.slot_geom; ctx.cube_tris = sc.cube_tris;
         ctx.lx = ot.ox; ctx.ly = ot.oy; ctx.lz = ot.oz;
+        ctx.n_slots = sc.n_slots;
     }
     if (tid < 2) tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f); // prefetched past the end, never used
     if (lane == 0) {
@@ -497,6 +543,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         }
         const long long ray0_ll = (long long)batch * (R * 32);
         if (ray0_ll >= total) break;
+        RT_CHECK(slice >= 0 && slot_begin + slice * ss < slot_end && ss % SEG_PAD == 0);
         const int ray0 = (int)ray0_ll;
         const int sb = slot_begin + slice * ss, se = min(slot_end, sb + ss);
 
@@ -506,12 +553,27 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         if constexpr (SHADOW) {
             if (lane < R) wocc[lane] = 0u;
         }
+#if RT_SWEEP_PRELOAD
+        // all R rays of the lane first, in one round trip: the plane tests below are calls the loads of the
+        // later rays would otherwise queue up behind (long-scoreboard stalls were 60 % of this prologue's samples)
+        RayRegs pre[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int gi = ray0 + r * 32 + lane;
+            if (gi < total) pre[r] = load_ray(s0, s1, gi);
+            else pre[r].ox = pre[r].oy = pre[r].oz = pre[r].dx = pre[r].dy = pre[r].dz = 0.f;
+        }
+#endif
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             int gi = ray0 + r * 32 + lane;
             unsigned long long first = KEY_MISS;
             if (gi < total) {
+#if RT_SWEEP_PRELOAD
+                const RayRegs rr = pre[r];
+#else
                 const RayRegs rr = load_ray(s0, s1, gi);
+#endif
                 if (ray_has_nan(rr)) nanmask |= 1u << r;
                 else {
                     vmask |= 3u << (2 * r);
@@ -596,6 +658,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
             unsigned int quads_next = 0; // the verdict on the quad pair after this one, evaluated with it
 #endif
             for (int jq = gb; jq < ge && alive; jq += 2 * QUAD_SLOTS) {
+            RT_CHECK(jq >= slot_begin && jq + 2 * QUAD_SLOTS <= slot_end && (jq & (2 * QUAD_SLOTS - 1)) == 0);
             // which of the two quads (4 groups each) can any ray of this warp touch?
             unsigned int quads_hit;
 #if RT_SWEEP_QUAD2
@@ -699,6 +762,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                                         qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
                                         drop_occluded(); // (a ray dropped here may still be queued once more by this loop: harmless)
                                     }
+                                    RT_CHECK(qn + 32 <= QCAP && js >= sb && js < se);
                                     if (cand) wqueue[qn + __popc(cball & lt_mask)] = ((unsigned int)(r * 32 + src) << 24) | (unsigned int)js;
                                     qn += __popc(cball);
                                     __syncwarp();
@@ -706,7 +770,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                             }
                         }
                         if (lane == 0) n_slot[warp][seg_of(jg)] += evals;
-                        if (qn >= (SHADOW ? 32 : RT_SWEEP_FLUSH_AT)) {
+                        if (qn >= (SHADOW ? RT_SWEEP_FLUSH_AT_SHADOW : RT_SWEEP_FLUSH_AT)) {
                             qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
                             drop_occluded();
                         }
@@ -744,6 +808,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                                     drop_occluded();
                                     mask &= vmask;
                                 }
+                                RT_CHECK(qn + 32 <= QCAP);
                                 if (mask) {
                                     int bit = __ffs(mask) - 1;
                                     mask &= mask - 1;
@@ -755,7 +820,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                             }
                         }
                     }
-                    if (qn >= (SHADOW ? 32 : RT_SWEEP_FLUSH_AT)) {
+                    if (qn >= (SHADOW ? RT_SWEEP_FLUSH_AT_SHADOW : RT_SWEEP_FLUSH_AT)) {
                         qn = sweep_flush<SHADOW>(&ctx, wqueue, wbest, ray0, qn, 0, &n_exact[warp], wd2, wocc);
                         drop_occluded();
                     }
@@ -785,6 +850,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                                    v3(rr.dx, rr.dy, rr.dz), k);
                 }
             }
+            RT_CHECK(gi >= 0 && gi < total);
             unsigned long long *kp = gi < s0.n ? s0.key + (long long)gi * s0.stride : s1.key + (gi - s0.n);
             if (!merge) *kp = k;
             else if (k != KEY_MISS) atomicMin(kp, k);

@@ -214,6 +214,7 @@ __global__ void __launch_bounds__(256) node_scatter_kernel(Pools p, int begin, i
     unsigned int base = 0;
     if (live && lane == leader) base = atomicAdd(&p.bins[bin], (unsigned int)__popc(same)) + p.bin_sums[bin / SCAN_CHUNK];
     base = __shfl_sync(0xffffffffu, base, leader);
+    RT_CHECK(!live || (int)(base + __popc(same & ((1u << lane) - 1u))) < end - begin);
     if (live) p.t_order[begin + base + __popc(same & ((1u << lane) - 1u))] = i;
 }
 
@@ -232,6 +233,7 @@ spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn
     do {
         if (begin + rank >= end) break;
         i = ordered ? p.t_order[begin + rank] : begin + rank;
+        RT_CHECK(i >= begin && i < end);
         p.t_sbase[i] = -1;
         p.t_crefl[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         p.t_crefr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -271,6 +273,7 @@ spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn
                     DevLight L = sc.lights[l];
                     if (L.kind != 0) continue;
                     V3 ldir = vnorm(vsub(v3(L.px, L.py, L.pz), sp)); // scene/mod.rs:191
+                    RT_CHECK(sb + L.point_index * lstride < (unsigned long long)p.s_cap);
                     p.s_a[sb + L.point_index * lstride] = make_float4(sp.x, sp.y, sp.z, ldir.x);
                     p.s_b[sb + L.point_index * lstride] = make_float4(ldir.y, ldir.z, 0.f, 0.f);
                 }
@@ -367,6 +370,7 @@ shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level
             if (L.kind == 0) { // PointLight::get_energy (scene/mod.rs:189-206)
                 V3 lpos = v3(L.px, L.py, L.pz);
                 ldir = vnorm(vsub(lpos, sp));
+                RT_CHECK(sb >= 0 && sb + (long long)L.point_index * light_stride < p.s_cap);
                 unsigned long long sk = p.s_key[sb + (long long)L.point_index * light_stride];
                 if (sk != KEY_MISS) {
                     V3 hp = ray_at(sp, ldir, key_t(sk));
@@ -420,6 +424,7 @@ shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level
         }
         colour = vadd(vadd(vadd(ambient, lights), reflected), refracted); // render.rs:100
     }
+    RT_CHECK(level == 0 || ((p.t_parent[i] >> 1) >= 0 && (p.t_parent[i] >> 1) < begin));
     if (level == 0) {
         sample_rgb[p.t_parent[i]] = make_float4(colour.x, colour.y, colour.z, is_node ? 1.f : 0.f);
     } else if (is_node) {

@@ -9,6 +9,13 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
         sys.path.insert(0, p)
 
 
+# RT_B200_TEST_LIB=<path>: run the tests against another build of the library (the checked build of
+# tools/build_variant.sh).  Read here, by the test harness; the library itself never reads the environment.
+if os.environ.get("RT_B200_TEST_LIB"):
+    from rust_tracer_b200 import _lib as _product_lib
+    _product_lib.LIB_PATH = os.path.join(ROOT, os.environ["RT_B200_TEST_LIB"])
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
     # build the product library and the oracle if they are not there yet (seconds)
