@@ -59,7 +59,7 @@ namespace rt {
 #define RT_SWEEP_QUAD2 0 // 1: quad spheres are evaluated two pairs at a time (A/B builds)
 #endif
 #ifndef RT_SWEEP_BRUTE_UNROLL
-#define RT_SWEEP_BRUTE_UNROLL 2
+#define RT_SWEEP_BRUTE_UNROLL 1 // measured: 1 beats 2 by 0.3 ms per c4 frame, 4 loses 5.6 ms (instruction cache)
 #endif
 #ifndef RT_SWEEP_FLUSH_AT
 #define RT_SWEEP_FLUSH_AT 32 // queued pairs at which a group's end runs the exact stage
@@ -68,7 +68,9 @@ namespace rt {
 #define RT_SWEEP_FLUSH_AT_SHADOW 32 // the same for shadow rays (sooner = rays leave the sweep sooner)
 #endif
 #ifndef RT_SWEEP_BULK_TABLE
-#define RT_SWEEP_BULK_TABLE 1 // 0: the table is copied by the CTA's threads behind a block barrier (A/B builds only)
+#define RT_SWEEP_BULK_TABLE 2 // how the table reaches shared memory: 0 = copied by the CTA's 512 threads behind a block barrier;
+                              // 1 = cp.async.bulk (three copies issued by one thread), each warp waits at its first use;
+                              // 2 = cp.async.bulk in chunks issued by the lanes of warp 0, every warp waits before its first item
 #endif
 constexpr int QCAP = 256;                // queued pairs per warp
 constexpr int BRUTE_UNROLL = RT_SWEEP_BRUTE_UNROLL;
@@ -488,7 +490,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         for (int g = 0; g < MAX_SEGS; ++g) n_slot[warp][g] = 0;
     }
     __syncthreads();
-#if !RT_SWEEP_BULK_TABLE
+#if RT_SWEEP_BULK_TABLE == 0
     {
         const float4 *src = (ORIGIN ? ot.bound : sc.bound) + slot_begin;
         for (int k = tid; k < n_tab; k += SWEEP_THREADS) tab[k] = src[k];
@@ -498,6 +500,22 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         for (int k = tid; k < n_qtab; k += SWEEP_THREADS) qtab[k] = qsrc[k];
     }
     __syncthreads();
+    bool table_ready = true;
+#elif RT_SWEEP_BULK_TABLE == 2
+    if (warp == 0) { // the table (slots, groups, quads: three contiguous runs of float4) in chunks, one bulk copy per lane and run
+        const unsigned int b_tab = (unsigned int)n_tab * sizeof(float4), b_g = (unsigned int)n_gtab * sizeof(float4),
+                           b_q = (unsigned int)n_qtab * sizeof(float4);
+        if (lane == 0) mbar_expect_tx(&tab_bar, b_tab + b_g + b_q);
+        __syncwarp();
+        auto chunked = [&](void *dst, const void *src, unsigned int bytes) {
+            const unsigned int per = ((bytes + 31) / 32 + 15) & ~15u, off = (unsigned int)lane * per; // 16-byte multiples
+            if (off < bytes) bulk_load((char *)dst + off, (const char *)src + off, min(per, bytes - off), &tab_bar);
+        };
+        chunked(tab, (ORIGIN ? ot.bound : sc.bound) + slot_begin, b_tab);
+        chunked(gtab, (ORIGIN ? ot.group : sc.group) + slot_begin / GROUP_SLOTS, b_g);
+        chunked(qtab, (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS, b_q);
+    }
+    mbar_wait(&tab_bar, 0); // (the copies of a 171 KB table take ~2 us; waiting here keeps the item loop free of the flag)
     bool table_ready = true;
 #else
     if (tid == 0) { // the table: slots, groups, quads -- three contiguous runs of float4
@@ -543,7 +561,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         }
         const long long ray0_ll = (long long)batch * (R * 32);
         if (ray0_ll >= total) break;
-        RT_CHECK(slice >= 0 && slot_begin + slice * ss < slot_end && ss % SEG_PAD == 0);
+        RT_CHECK(slice >= 0 && (slot_begin + slice * ss < slot_end || slot_end == slot_begin) && ss % SEG_PAD == 0); // (an empty table has one empty slice)
         const int ray0 = (int)ray0_ll;
         const int sb = slot_begin + slice * ss, se = min(slot_end, sb + ss);
 
