@@ -74,7 +74,7 @@ struct HostScene {
     // what a bound slot of segment g holds (rt_shape_kind; the sweeps count filter evaluations per segment)
     int seg_kind[MAX_SEGS] = {0, 0, 0, 0};
     int seg_real[MAX_SEGS] = {0, 0, 0, 0}; // bound slots of the segment that hold a shape (the rest are pads)
-    std::vector<float4> bound, group, quad;
+    std::vector<float4> bound, group, quad, super;
     std::vector<int> bound_shape;
     std::vector<int2> slot_meta;
     std::vector<float4> slot_geom;
@@ -86,8 +86,8 @@ struct HostScene {
     std::vector<DevLight> lights;
     // origin tables (kernels.h: OriginTable); empty when the table is too small to pay
     bool origin = false;
-    std::vector<HostSlot> slots, groups, quads;
-    std::vector<std::vector<float4>> light_host; // by DevLight::point_index: slots, groups, quads re-centred on the light
+    std::vector<HostSlot> slots, groups, quads, supers;
+    std::vector<std::vector<float4>> light_host; // by DevLight::point_index: slots, groups, quads, supers re-centred on the light
     std::vector<OriginTable> light_tabs;         // their scalar fields (table pointers null)
     // the table of the camera origin of the last render, shared by the devices of a multi-GPU scene
     mutable std::mutex cam_mu;
@@ -127,7 +127,7 @@ struct rt_scene {
 namespace rt {
 // Upload a built scene to `device`: one allocation, one batch of copies.
 int upload_scene(const std::shared_ptr<const HostScene> &hs, int device, rt_scene **out);
-// Re-centre the bound, group and quad tables on `o` (out = slots, groups, quads, each in
+// Re-centre the bound, group and quad tables on `o` (out = slots, groups, quads, supers, each in
 // the paired layout of DevScene::bound) and fill every field of *tab but the table pointers; toward: the table serves shadow rays travelling towards `o`.
 void build_origin_table(const HostScene &hs, const float o[3], std::vector<float4> &out, OriginTable *tab, bool toward);
 // Make scene->cam the table of this camera origin (no-op when origin tables are off).

@@ -181,7 +181,8 @@ static Bound bound_from(const double c[3], double rf) {
 // then dist(G, line) <= a + sqrt(R^2 + mu), and (a + sqrt(R^2 + mu))^2 <= (a + R)^2 + (1 + a / R) mu.
 // The group radius therefore counts every member as at least a / 16 wide, and the sweep gives
 // group spheres 17 times the margin mu of a bound (sweep.cu: GROUP_MARGIN).  Quads are built from
-// their 4 group spheres in the same way with a / 2: 3 times the margin of a group (QUAD_MARGIN).
+// their 4 group spheres in the same way with a / 2: 3 times the margin of a group (QUAD_MARGIN), and
+// supers from their 4 quad spheres likewise: 3 times the margin of a quad (SUPER_MARGIN).
 static Bound make_group(const Bound *slots, const int *shape, int n, double floor_div) {
     double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
     int m = 0;
@@ -244,9 +245,9 @@ void build_origin_table(const HostScene &hs, const float o[3], std::vector<float
         clip = false; // a bound every ray must pass: no far clip in this table
         return S{0.f, 0.f, 0.f, -3.402823466e+38f};
     };
-    // slots, then groups, then quads (each paired); rmax (the far clip of slot tests) is the slots' alone
-    const size_t ns = hs.slots.size(), ng = hs.groups.size(), nq = hs.quads.size();
-    out.resize(ns + ng + nq);
+    // slots, then groups, quads, supers (each paired); rmax (the far clip of slot tests) is the slots' alone
+    const size_t ns = hs.slots.size(), ng = hs.groups.size(), nq = hs.quads.size(), nsu = hs.supers.size();
+    out.resize(ns + ng + nq + nsu);
     bool clip = toward;
     auto fill = [&](const std::vector<HostSlot> &v, float4 *dst) { // returns the largest radius
         double rm[MAX_HOST_CHUNKS] = {0.0};
@@ -271,6 +272,7 @@ void build_origin_table(const HostScene &hs, const float o[3], std::vector<float
     const double rmax_slots = fill(hs.slots, out.data());
     fill(hs.groups, out.data() + ns);
     fill(hs.quads, out.data() + ns + ng);
+    fill(hs.supers, out.data() + ns + ng + nq);
     double on = std::sqrt((double)o[0] * o[0] + (double)o[1] * o[1] + (double)o[2] * o[2]);
     double r = (on + (double)hs.dev.cmax) * (1.0 + 1e-6);
     tab->reach = std::isfinite(r) && r < 3e38 ? round_up_f32(r) : 3.0e38f;
@@ -300,6 +302,7 @@ int prepare_camera_table(rt_scene *scene, const float origin[3]) {
     t.bound = scene->cam_tab;
     t.group = scene->cam_tab + hs.slots.size();
     t.quad = t.group + hs.groups.size();
+    t.super = t.quad + hs.quads.size();
     scene->cam = t;
     std::memcpy(scene->cam_origin, origin, 3 * sizeof(float));
     return RT_OK;
@@ -609,7 +612,17 @@ int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
             cmax = std::max(cmax, quads[q].reach);
         }
     }
-    lap("groups, quads");
+    const int per_super = SUPER_SLOTS / QUAD_SLOTS, n_supers = n_quads / per_super; // even: SEG_PAD is two supers
+    std::vector<Bound> supers(n_supers);
+    {
+        std::vector<int> live(n_quads);
+        for (int q = 0; q < n_quads; ++q) live[q] = quads[q].w == 3.402823466e+38f ? -1 : 0; // a quad of pads
+        for (int q = 0; q < n_supers; ++q) {
+            supers[q] = make_group(&quads[(size_t)q * per_super], &live[(size_t)q * per_super], per_super, 2.0);
+            cmax = std::max(cmax, supers[q].reach);
+        }
+    }
+    lap("groups, quads, supers");
     auto paired = [](const std::vector<Bound> &v) {
         std::vector<float4> out(v.size());
         for (size_t j = 0; j + 1 < v.size(); j += 2) {
@@ -619,7 +632,7 @@ int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
         }
         return out;
     };
-    hs.bound = paired(slots); hs.group = paired(groups); hs.quad = paired(quads);
+    hs.bound = paired(slots); hs.group = paired(groups); hs.quad = paired(quads); hs.super = paired(supers);
     hs.slot_meta.resize(n_slots);
     hs.slot_geom.assign(3 * (size_t)n_slots, make_float4(0.f, 0.f, 0.f, 0.f));
     for (int j = 0; j < n_slots; ++j) {
@@ -685,6 +698,7 @@ int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
         for (const Bound &b : slots) hs.slots.push_back(host_slot(b));
         for (const Bound &b : groups) hs.groups.push_back(host_slot(b));
         for (const Bound &b : quads) hs.quads.push_back(host_slot(b));
+        for (const Bound &b : supers) hs.supers.push_back(host_slot(b));
         hs.light_tabs.resize(n_point);
         hs.light_host.resize(n_point);
         for (int l = 0; l < desc->n_lights; ++l) {
@@ -806,17 +820,17 @@ int upload_scene(const std::shared_ptr<const HostScene> &host, int device, rt_sc
     s->own_stream = s->stream;
     const DevMaterial *dm = nullptr;
     Arena arena;
-    arena.add(hs.bound, &d.bound); arena.add(hs.group, &d.group); arena.add(hs.quad, &d.quad);
+    arena.add(hs.bound, &d.bound); arena.add(hs.group, &d.group); arena.add(hs.quad, &d.quad); arena.add(hs.super, &d.super);
     arena.add(hs.bound_shape, &d.bound_shape); arena.add(hs.slot_meta, &d.slot_meta); arena.add(hs.slot_geom, &d.slot_geom);
     arena.add(hs.meta, &d.shape_meta); arena.add(hs.geom, &d.geom);
     arena.add(hs.plane_shape, &d.plane_shape); arena.add(hs.plane_data, &d.plane_data);
     arena.add(hs.cube_tris, &d.cube_tris); arena.add(hs.materials, &dm); arena.add(hs.lights, &d.lights);
     const float4 *cam_tab = nullptr;
-    const int n_groups = d.n_slots / GROUP_SLOTS, n_quads = d.n_slots / QUAD_SLOTS;
+    const int n_groups = d.n_slots / GROUP_SLOTS, n_quads = d.n_slots / QUAD_SLOTS, n_supers = d.n_slots / SUPER_SLOTS;
     if (hs.origin) {
         s->light_tabs = hs.light_tabs;
         for (size_t l = 0; l < s->light_tabs.size(); ++l) arena.add(hs.light_host[l], &s->light_tabs[l].bound);
-        arena.add_raw(nullptr, (size_t)(d.n_slots + n_groups + n_quads) * sizeof(float4), (const void **)&cam_tab);
+        arena.add_raw(nullptr, (size_t)(d.n_slots + n_groups + n_quads + n_supers) * sizeof(float4), (const void **)&cam_tab);
     }
     s->ws = workspace_take_cached(device);
     int rc = arena.commit(s, s->stream);
@@ -829,6 +843,7 @@ int upload_scene(const std::shared_ptr<const HostScene> &host, int device, rt_sc
     for (OriginTable &t : s->light_tabs) {
         t.group = t.bound + d.n_slots;
         t.quad = t.group + n_groups;
+        t.super = t.quad + n_quads;
     }
     s->cam_tab = const_cast<float4 *>(cam_tab);
     *out = s;

@@ -30,6 +30,7 @@ struct OriginTable {
     const float4 *bound = nullptr; // null: no table, use the general filter
     const float4 *group = nullptr; // the group spheres (DevScene::group) re-centred likewise
     const float4 *quad = nullptr;  // and the quad spheres (DevScene::quad)
+    const float4 *super = nullptr; // and the super spheres (DevScene::super)
     float reach = 0.f;             // |O'| + cmax, rounded up
     float ox = 0.f, oy = 0.f, oz = 0.f; // O'
     // > 0: the rays are shadow rays travelling TOWARDS O' (a light); a bound whose centre lies

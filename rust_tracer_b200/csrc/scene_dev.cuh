@@ -16,7 +16,9 @@
 //                                             neighbours in space (Morton order within a segment).
 //                                             A warp skips a group none of its rays can touch.
 //   quad[2q], quad[2q+1]    float4 x 2        the same one level up: spheres around QUAD_SLOTS slots
-//                                             (4 consecutive groups), tested first.
+//                                             (4 consecutive groups).
+//   super[2q], super[2q+1]  float4 x 2        and one more: spheres around SUPER_SLOTS slots (4 consecutive
+//                                             quads), tested first.
 //   bound_shape[j] int32                      shape id of bound slot j, -1 for a pad
 //   slot_meta[j]   int2  (kind, shape id)     and
 //   slot_geom[3*j..] 3 x float4               copies of shape_meta / geom in SLOT order: the exact
@@ -78,7 +80,8 @@ struct DevLight { // 32 bytes
 
 constexpr int GROUP_SLOTS = 16; // bound slots per group
 constexpr int QUAD_SLOTS = 64;  // bound slots per quad = 4 consecutive groups
-constexpr int SEG_PAD = 128;    // every segment of the bound table is a multiple of this many slots (a pair of quads)
+constexpr int SUPER_SLOTS = 256; // bound slots per super = 4 consecutive quads
+constexpr int SEG_PAD = 512;    // every segment of the bound table is a multiple of this many slots (a pair of supers)
 constexpr int MAX_SEGS = 4;
 
 // Bound slots [begin, end) share one margin factor k: a ray passes slot j iff
@@ -111,6 +114,7 @@ struct DevScene {
     const float4 *bound;
     const float4 *group;    // n_slots / GROUP_SLOTS group spheres, paired like bound
     const float4 *quad;     // n_slots / QUAD_SLOTS spheres around 4 consecutive groups each, paired like bound
+    const float4 *super;    // n_slots / SUPER_SLOTS spheres around 4 consecutive quads each, paired like bound
     const int *bound_shape;
     const int2 *slot_meta;
     const float4 *slot_geom;

@@ -55,8 +55,8 @@ namespace rt {
 #ifndef RT_SWEEP_FLUSH_PIPE
 #define RT_SWEEP_FLUSH_PIPE 0 // 1: the exact stage fetches the next 32 pairs' operands while it tests the current 32 (A/B builds)
 #endif
-#ifndef RT_SWEEP_QUAD2
-#define RT_SWEEP_QUAD2 0 // 1: quad spheres are evaluated two pairs at a time (A/B builds)
+#ifndef RT_SWEEP_SUPERS
+#define RT_SWEEP_SUPERS 1 // 0: the sweep starts at the quad spheres (A/B builds); 1: at the super spheres above them
 #endif
 #ifndef RT_SWEEP_BRUTE_UNROLL
 #define RT_SWEEP_BRUTE_UNROLL 1 // measured: 1 beats 2 by 0.3 ms per c4 frame, 4 loses 5.6 ms (instruction cache)
@@ -68,18 +68,23 @@ namespace rt {
 #define RT_SWEEP_FLUSH_AT_SHADOW 32 // the same for shadow rays (sooner = rays leave the sweep sooner)
 #endif
 #ifndef RT_SWEEP_BULK_TABLE
-#define RT_SWEEP_BULK_TABLE 2 // how the table reaches shared memory: 0 = copied by the CTA's 512 threads behind a block barrier;
-                              // 1 = cp.async.bulk (three copies issued by one thread), each warp waits at its first use;
-                              // 2 = cp.async.bulk in chunks issued by the lanes of warp 0, every warp waits before its first item
+#define RT_SWEEP_BULK_TABLE 0 // how the table reaches shared memory, measured on c4 (profiles/r02_ab_table_staging_heavy_c4.log):
+                              // 0 = copied by the CTA's 512 threads behind a block barrier                       38.08 ms
+                              // 1 = cp.async.bulk + mbarrier, one copy per table issued by one thread, each
+                              //     warp waits at its first use                                                   38.55 ms
+                              // 2 = cp.async.bulk in 96 chunks issued by the lanes of warp 0, wait before the
+                              //     first item                                                                    53.35 ms
 #endif
 constexpr int QCAP = 256;                // queued pairs per warp
 constexpr int BRUTE_UNROLL = RT_SWEEP_BRUTE_UNROLL;
 constexpr float U24 = 5.9604645e-08f;    // 2^-24, unit round-off of f32
 constexpr float GROUP_MARGIN = 17.f;     // margin of a group sphere / margin of a bound (make_group: a / rho <= 16)
 constexpr float QUAD_MARGIN = 3.f;       // margin of a quad sphere / margin of a group sphere (a / rho <= 2)
+constexpr float SUPER_MARGIN = 3.f;      // margin of a super sphere / margin of a quad sphere (a / rho <= 2)
 // seed_q = seed_g + QUAD_SEED (seed_g - seed): (QUAD_MARGIN GROUP_MARGIN - GROUP_MARGIN) / (GROUP_MARGIN - 1)
 constexpr float QUAD_SEED = (QUAD_MARGIN * GROUP_MARGIN - GROUP_MARGIN) / (GROUP_MARGIN - 1.f) * 1.0001f;
-constexpr int MIN_SLICE_SLOTS = 256;     // smallest table slice of a work item
+constexpr float SUPER_SEED = (SUPER_MARGIN * QUAD_MARGIN * GROUP_MARGIN - GROUP_MARGIN) / (GROUP_MARGIN - 1.f) * 1.0001f; // likewise for a super
+constexpr int MIN_SLICE_SLOTS = SEG_PAD; // smallest table slice of a work item
 constexpr int SMEM_LIMIT = 232448;       // 227 KB opt-in dynamic shared memory per CTA on sm_100
 
 struct RayRegs {
@@ -458,11 +463,12 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
     unsigned int *const batch_counter = JOBS ? job.batch_counter : batch_counter_;
     __shared__ ExactCount n_exact[SWEEP_WARPS];
     __shared__ unsigned long long n_hier[SWEEP_WARPS], n_slot[SWEEP_WARPS][MAX_SEGS];
-    const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS, n_qtab = n_tab / QUAD_SLOTS;
+    const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS, n_qtab = n_tab / QUAD_SLOTS, n_stab = n_tab / SUPER_SLOTS;
     float4 *tab = smem;                                                         // n_tab slots + one slack pair
     float4 *gtab = tab + n_tab + 2;                                             // n_gtab groups
     float4 *qtab = gtab + n_gtab;                                               // n_qtab quads
-    unsigned long long *best = (unsigned long long *)(qtab + n_qtab);           // SWEEP_THREADS * R
+    float4 *stab = qtab + n_qtab;                                               // n_stab supers
+    unsigned long long *best = (unsigned long long *)(stab + n_stab);           // SWEEP_THREADS * R
     unsigned int *queue = (unsigned int *)(best + SWEEP_THREADS * R);           // SWEEP_WARPS * QCAP
     float *light_d2 = (float *)(queue + SWEEP_WARPS * QCAP);                    // SHADOW: SWEEP_THREADS * R
     unsigned int *occluded = (unsigned int *)(light_d2 + SWEEP_THREADS * R);    // SHADOW: SWEEP_WARPS * R bit masks
@@ -498,14 +504,16 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         for (int k = tid; k < n_gtab; k += SWEEP_THREADS) gtab[k] = gsrc[k];
         const float4 *qsrc = (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS;
         for (int k = tid; k < n_qtab; k += SWEEP_THREADS) qtab[k] = qsrc[k];
+        const float4 *ssrc = (ORIGIN ? ot.super : sc.super) + slot_begin / SUPER_SLOTS;
+        for (int k = tid; k < n_stab; k += SWEEP_THREADS) stab[k] = ssrc[k];
     }
     __syncthreads();
     bool table_ready = true;
 #elif RT_SWEEP_BULK_TABLE == 2
     if (warp == 0) { // the table (slots, groups, quads: three contiguous runs of float4) in chunks, one bulk copy per lane and run
         const unsigned int b_tab = (unsigned int)n_tab * sizeof(float4), b_g = (unsigned int)n_gtab * sizeof(float4),
-                           b_q = (unsigned int)n_qtab * sizeof(float4);
-        if (lane == 0) mbar_expect_tx(&tab_bar, b_tab + b_g + b_q);
+                           b_q = (unsigned int)n_qtab * sizeof(float4), b_s = (unsigned int)n_stab * sizeof(float4);
+        if (lane == 0) mbar_expect_tx(&tab_bar, b_tab + b_g + b_q + b_s);
         __syncwarp();
         auto chunked = [&](void *dst, const void *src, unsigned int bytes) {
             const unsigned int per = ((bytes + 31) / 32 + 15) & ~15u, off = (unsigned int)lane * per; // 16-byte multiples
@@ -514,23 +522,26 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         chunked(tab, (ORIGIN ? ot.bound : sc.bound) + slot_begin, b_tab);
         chunked(gtab, (ORIGIN ? ot.group : sc.group) + slot_begin / GROUP_SLOTS, b_g);
         chunked(qtab, (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS, b_q);
+        chunked(stab, (ORIGIN ? ot.super : sc.super) + slot_begin / SUPER_SLOTS, b_s);
     }
     mbar_wait(&tab_bar, 0); // (the copies of a 171 KB table take ~2 us; waiting here keeps the item loop free of the flag)
     bool table_ready = true;
 #else
     if (tid == 0) { // the table: slots, groups, quads -- three contiguous runs of float4
         const unsigned int b_tab = (unsigned int)n_tab * sizeof(float4), b_g = (unsigned int)n_gtab * sizeof(float4),
-                           b_q = (unsigned int)n_qtab * sizeof(float4);
-        mbar_expect_tx(&tab_bar, b_tab + b_g + b_q);
+                           b_q = (unsigned int)n_qtab * sizeof(float4), b_s = (unsigned int)n_stab * sizeof(float4);
+        mbar_expect_tx(&tab_bar, b_tab + b_g + b_q + b_s);
         bulk_load(tab, (ORIGIN ? ot.bound : sc.bound) + slot_begin, b_tab, &tab_bar);
         bulk_load(gtab, (ORIGIN ? ot.group : sc.group) + slot_begin / GROUP_SLOTS, b_g, &tab_bar);
         bulk_load(qtab, (ORIGIN ? ot.quad : sc.quad) + slot_begin / QUAD_SLOTS, b_q, &tab_bar);
+        bulk_load(stab, (ORIGIN ? ot.super : sc.super) + slot_begin / SUPER_SLOTS, b_s, &tab_bar);
     }
     bool table_ready = false; // this warp has seen the copies land
 #endif
     const float4 *tab0 = tab - slot_begin;                 // indexed by absolute slot
     const float4 *gtab0 = gtab - slot_begin / GROUP_SLOTS; // indexed by absolute group
     const float4 *qtab0 = qtab - slot_begin / QUAD_SLOTS;  // indexed by absolute quad
+    const float4 *stab0 = stab - slot_begin / SUPER_SLOTS; // indexed by absolute super
 
     for (;;) {
         unsigned int item = 0;
@@ -617,18 +628,18 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         // ---- phase 1 + 2 --------------------------------------------------------------
         typename std::conditional<ORIGIN, RayCoefO, RayCoef>::type c[R];
         // e[r] = (filter value of ray r against the two spheres packed in T0, T1)
-        // level: 0 bound slots, 1 group spheres, 2 quad spheres (wider margins, see GROUP_MARGIN)
+        // level: 0 bound slots, 1 group spheres, 2 quad spheres, 3 super spheres (wider margins, see GROUP_MARGIN)
         auto pair_e = [&](const float4 &T0, const float4 &T1, float2 (&e)[R], int level) {
             const float2 cx = make_float2(T0.x, T0.y), cy = make_float2(T0.z, T0.w), cz = make_float2(T1.x, T1.y);
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 if constexpr (ORIGIN) {
                     float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __fmul2_rn(cz, f2(c[r].dz))));
-                    e[r] = __ffma2_rn(b, b, f2(level == 0 ? c[r].mu : (level == 1 ? c[r].mu_g : QUAD_MARGIN * c[r].mu_g)));
+                    e[r] = __ffma2_rn(b, b, f2(level == 0 ? c[r].mu : (level == 1 ? c[r].mu_g : (level == 2 ? QUAD_MARGIN : SUPER_MARGIN * QUAD_MARGIN) * c[r].mu_g)));
                 } else {
                     float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
                     float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2),
-                                           f2(level == 0 ? c[r].seed : (level == 1 ? c[r].seed_g : fmaf(QUAD_SEED, c[r].seed_g - c[r].seed, c[r].seed_g))))));
+                                           f2(level == 0 ? c[r].seed : (level == 1 ? c[r].seed_g : fmaf(level == 2 ? QUAD_SEED : SUPER_SEED, c[r].seed_g - c[r].seed, c[r].seed_g))))));
                     // a centre behind the origin (b < 0): only s decides, i.e. whether the origin is inside the sphere
                     e[r] = __ffma2_rn(b, make_float2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f)), s);
                 }
@@ -672,31 +683,30 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                     else c[r] = ray_coef(rr, k_seg, sc.cmax, usable);
                 }
             }
-#if RT_SWEEP_QUAD2
-            unsigned int quads_next = 0; // the verdict on the quad pair after this one, evaluated with it
+#if RT_SWEEP_SUPERS
+            for (int js = gb; js < ge && alive; js += 2 * SUPER_SLOTS) { // runs and slices are whole pairs of supers (SEG_PAD)
+            // which of the two supers (4 quads each) can any ray of this warp touch?
+            unsigned int supers_hit;
+            {
+                const float4 T0 = stab0[js >> 8], T1 = stab0[(js >> 8) + 1];
+                float2 e[R];
+                pair_e(T0, T1, e, 3);
+                float m0 = e[0].x, m1 = e[0].y;
+#pragma unroll
+                for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); }
+                supers_hit = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
+                evals_hier += 2 * R;
+            }
+            if (!supers_hit) continue;
+            const int jq_begin = (supers_hit & 1u) ? js : js + SUPER_SLOTS, jq_end = (supers_hit & 2u) ? js + 2 * SUPER_SLOTS : js + SUPER_SLOTS;
+#else
+            {
+            const int jq_begin = gb, jq_end = ge;
 #endif
-            for (int jq = gb; jq < ge && alive; jq += 2 * QUAD_SLOTS) {
+            for (int jq = jq_begin; jq < jq_end && alive; jq += 2 * QUAD_SLOTS) {
             RT_CHECK(jq >= slot_begin && jq + 2 * QUAD_SLOTS <= slot_end && (jq & (2 * QUAD_SLOTS - 1)) == 0);
             // which of the two quads (4 groups each) can any ray of this warp touch?
             unsigned int quads_hit;
-#if RT_SWEEP_QUAD2
-            // two quad pairs per evaluation: twice the independent FFMA2 chains between one vote and the next
-            if ((jq - gb) & (2 * QUAD_SLOTS)) quads_hit = quads_next;
-            else {
-                const bool two = jq + 2 * QUAD_SLOTS < ge;
-                const float4 T0 = qtab0[jq >> 6], T1 = qtab0[(jq >> 6) + 1];
-                const float4 U0 = two ? qtab0[(jq >> 6) + 2] : T0, U1 = two ? qtab0[(jq >> 6) + 3] : T1;
-                float2 e[R], f[R];
-                pair_e(T0, T1, e, 2);
-                pair_e(U0, U1, f, 2);
-                float m0 = e[0].x, m1 = e[0].y, n0 = f[0].x, n1 = f[0].y;
-#pragma unroll
-                for (int r = 1; r < R; ++r) { m0 = fmaxf(m0, e[r].x); m1 = fmaxf(m1, e[r].y); n0 = fmaxf(n0, f[r].x); n1 = fmaxf(n1, f[r].y); }
-                quads_hit = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
-                quads_next = (__any_sync(FULL, n0 >= U1.z) ? 1u : 0u) | (__any_sync(FULL, n1 >= U1.w) ? 2u : 0u);
-                evals_hier += two ? 4 * R : 2 * R;
-            }
-#else
             {
                 const float4 T0 = qtab0[jq >> 6], T1 = qtab0[(jq >> 6) + 1];
                 float2 e[R];
@@ -707,7 +717,6 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 quads_hit = (__any_sync(FULL, m0 >= T1.z) ? 1u : 0u) | (__any_sync(FULL, m1 >= T1.w) ? 2u : 0u);
                 evals_hier += 2 * R;
             }
-#endif
             // most quad pairs are touched by no ray of the warp: leave before the group loop is set up
             // (its control flow for skipped quads was 12 % of the instructions executed)
             if (!quads_hit) continue;
@@ -845,6 +854,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 }
             }
             }
+            } // supers
         }
         if (lane == 0) n_hier[warp] += evals_hier;
         __syncwarp();
@@ -926,8 +936,9 @@ template <int R, int T, bool SHADOW> static size_t sweep_smem_fixed() {
 
 // Bound slots one launch can keep in shared memory.
 template <int R, int T, bool SHADOW> static int sweep_table_cap() {
-    // per slot: its float4, 1/GROUP_SLOTS of its group's and 1/QUAD_SLOTS of its quad's
-    int cap = (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T, SHADOW>()) * QUAD_SLOTS / (sizeof(float4) * (QUAD_SLOTS + QUAD_SLOTS / GROUP_SLOTS + 1))) /
+    // per slot: its float4, 1/GROUP_SLOTS of its group's, 1/QUAD_SLOTS of its quad's and 1/SUPER_SLOTS of its super's
+    int cap = (int)((SMEM_LIMIT - 1024 - sweep_smem_fixed<R, T, SHADOW>()) * SUPER_SLOTS /
+                    (sizeof(float4) * (SUPER_SLOTS + SUPER_SLOTS / GROUP_SLOTS + SUPER_SLOTS / QUAD_SLOTS + 1))) /
               SEG_PAD * SEG_PAD;
     const int forced = tuning().table_cap / SEG_PAD * SEG_PAD; // tests force several table chunks
     if (forced >= SEG_PAD && forced < cap) cap = forced;
@@ -992,7 +1003,7 @@ static ItemPlan plan_items(long long total, int heavy, int per, long long warps,
 }
 
 template <int R, int T, bool SHADOW> static size_t sweep_smem_bytes(int slots) {
-    return (size_t)(slots + slots / GROUP_SLOTS + slots / QUAD_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T, SHADOW>();
+    return (size_t)(slots + slots / GROUP_SLOTS + slots / QUAD_SLOTS + slots / SUPER_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T, SHADOW>();
 }
 
 template <int R, int T, bool ORIGIN, bool SHADOW>

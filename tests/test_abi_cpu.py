@@ -156,8 +156,8 @@ def test_library_does_not_read_the_environment():
     assert L.rt_debug_get(b"item_max") == 16 and L.rt_debug_get(b"no_such_knob") == -(1 << 63)
     assert L.rt_debug_set(b"tri_bound_scale", 1) == abi.RT_ERR_INVALID  # correctness margins are not knobs
     assert L.rt_debug_set(b"item_max", 99) == abi.RT_ERR_INVALID
-    with rt.tuned(item_max=3, table_cap=256):
-        assert L.rt_debug_get(b"item_max") == 3 and L.rt_debug_get(b"table_cap") == 256
+    with rt.tuned(item_max=3, table_cap=512):
+        assert L.rt_debug_get(b"item_max") == 3 and L.rt_debug_get(b"table_cap") == 512
     assert L.rt_debug_get(b"item_max") == 16 and L.rt_debug_get(b"table_cap") == 0
     L.rt_debug_set(b"want_light", 9)
     L.rt_debug_reset()

@@ -65,11 +65,11 @@ def test_chunked_bound_table_equals_resident_table():
     w, h = 192, 108
     sc = rt.Scene(desc)
     f0, u0, s0 = sc.render(w, h, 5)
-    with rt.tuned(table_cap=128):
+    with rt.tuned(table_cap=512):
         f1, u1, s1 = sc.render(w, h, 5)
     with rt.tuned(shadow_anyhit=0):  # every sweep finds the nearest hit: the exact tests are then the same set of pairs
         f2, u2, s2 = sc.render(w, h, 5)
-        with rt.tuned(table_cap=128):
+        with rt.tuned(table_cap=512):
             f3, u3, s3 = sc.render(w, h, 5)
     sc.close()
     assert np.array_equal(f0, f1, equal_nan=True) and (u0 == u1).all()
@@ -308,7 +308,7 @@ def test_merged_light_sweeps_and_tail_items_do_not_change_the_image():
     for knobs in ({}, {"merge_lights": 0}, {"tail_pct": 0}, {"tail_pct": 100, "tail_mult": 8},
                   {"tail_pct": 50, "tail_mult": 64}, {"rays_per_thread": 1},
                   {"rays_per_thread": 2, "want_light": 16}, {"shadow_anyhit": 0}, {"shadow_anyhit": 0, "merge_lights": 0},
-                  {"merge_lights": 0, "rays_per_thread": 2}, {"merge_lights": 0, "table_cap": 256}):
+                  {"merge_lights": 0, "rays_per_thread": 2}, {"merge_lights": 0, "table_cap": 512}):
         with rt.tuned(**knobs):
             sc = rt.Scene(desc)
             try:
