@@ -957,7 +957,7 @@ struct ItemPlan {
 };
 
 template <int R>
-static ItemPlan plan_items(long long total, int heavy, int per, long long warps, int n_chunks) {
+static ItemPlan plan_items(long long total, int heavy, int per, long long warps, int n_chunks, bool jobs = false) {
     const Tuning &tn = tuning();
     ItemPlan pl;
     const long long batches = (total + 32ll * R - 1) / (32ll * R);
@@ -973,7 +973,7 @@ static ItemPlan plan_items(long long total, int heavy, int per, long long warps,
         return std::max(1, (per + *slots - 1) / *slots);
     };
     pl.heavy_batches = std::min<long long>(batches, ((long long)std::max(heavy, 0) + 32ll * R - 1) / (32ll * R));
-    const long long want_light = (long long)tn.want_light * warps, want_heavy = (long long)tn.want_heavy * warps; // measured (tuning.h)
+    const long long want_light = (long long)tn.want_light * warps, want_heavy = (long long)(jobs ? tn.want_heavy_jobs : tn.want_heavy) * warps; // measured (tuning.h)
     pl.n_slices = slicing(want_light, batches - pl.heavy_batches, &pl.slice_slots);
     if (tn.slices > 0) {
         pl.n_slices = std::max(1, std::min(tn.slices, std::max(1, per / SEG_PAD)));
@@ -989,6 +989,7 @@ static ItemPlan plan_items(long long total, int heavy, int per, long long warps,
     const long long regular = batches - pl.heavy_batches;
     const int tail_pct = tn.tail_pct, tail_mult = tn.tail_mult;
     long long tail_batches = std::min<long long>(regular * tail_pct / 100, 2 * warps);
+    if (regular < (long long)tn.tail_min * warps) tail_batches = 0; // a short launch: finer items cost more (prologues, shadow rays stopping later) than its tail
     pl.tail_slices = pl.n_slices; pl.tail_slice_slots = pl.slice_slots;
     if (tail_batches > 0 && tail_mult > 1) {
         const int n = std::min(pl.n_slices * tail_mult, std::max(1, per / MIN_SLICE_SLOTS));
@@ -1064,7 +1065,7 @@ static cudaError_t launch_sweep_jobs_r(const DevScene &sc, const RaySeg *segs, c
     const unsigned int grid = (unsigned int)sm_count;
     for (int j = 0; j < n_jobs; ++j) {
         const long long ctas = (sm_count - j + n_jobs - 1) / n_jobs; // CTAs b with b % n_jobs == j
-        const ItemPlan pl = plan_items<R>(segs[j].n, segs[j].heavy, sc.n_slots, ctas * SWEEP_WARPS, 1);
+        const ItemPlan pl = plan_items<R>(segs[j].n, segs[j].heavy, sc.n_slots, ctas * SWEEP_WARPS, 1, true);
         SweepJob &J = jobs.j[j];
         J.s0 = segs[j]; J.ot = tabs[j]; J.batch_counter = batch_counters + j;
         J.n_slices = pl.n_slices; J.slice_slots = pl.slice_slots; J.merge = pl.merge;

@@ -13,7 +13,9 @@ namespace rt {
 struct Tuning {
     int rays_per_thread = 0;    // sweep: rays per thread (1, 2, 4); 0 = by the number of rays
     int want_light = 4;         // sweep: work items per warp aimed at for ordinary batches ...
-    int want_heavy = 2;         // ... and for the expensive first batches of a launch (measured on c4: 48 -> 8 saves 1.6 ms, 8 -> 2 another 0.8)
+    int want_heavy = 4;         // ... and for the expensive first batches of a launch (rays that start far outside the scene)
+    int want_heavy_jobs = 4;    // ... the same for the shadow rays of a level (one launch for all lights)
+    int tail_min = 0;           // sweep: the tail of a launch is cut finer only if it has >= tail_min batches per warp
     int slices = 0;             // sweep: force this many table slices per batch; 0 = plan
     int tail_pct = 15;          // sweep: the last tail_pct % of a launch's batches ...
     int tail_mult = 4;          // ... are cut tail_mult times finer
