@@ -27,10 +27,8 @@ struct Workspace {
     long long idx_cap = 0;
     unsigned int *h_counters = nullptr; // pinned mirror of pools.counters
     unsigned long long *exact_counter = nullptr;
-    unsigned int *batch_counters = nullptr; // one block of SWEEP_CTL_WORDS work counters per sweep launch of a band
+    unsigned int *batch_counters = nullptr; // one work counter per sweep launch of a band
     int batch_cap = 0, batch_next = 0;
-    uint4 *share_entries = nullptr;         // SHARE_ENTRIES shared work items per block (kernels.h: SweepShare)
-    unsigned int share_epoch = 0;
     void *out_f32 = nullptr, *out_u8 = nullptr; // device staging for host-buffer calls
     size_t out_f32_cap = 0, out_u8_cap = 0;
     void *tables = nullptr; // the device tables of the scene that holds this workspace (api_scene.cu: Arena)

@@ -30,8 +30,7 @@ struct HostLap {
 
 // ---- workspace --------------------------------------------------------------------------
 
-constexpr int BATCH_COUNTERS_MIN = 64; // one block of work counters per sweep launch of a band: (depth + 1) x (1 + lights) x table chunks
-constexpr int SHARE_ENTRIES = 8192;    // shared work items a launch can announce (sweep.cu stops announcing well before)
+constexpr int BATCH_COUNTERS_MIN = 1024; // one work counter per sweep launch of a band: (depth + 1) x (1 + lights) x table chunks
 
 template <typename T> static int dev_alloc(T **p, size_t n, const char *what) {
     *p = nullptr;
@@ -72,7 +71,6 @@ void Workspace::release() {
     h_counters = nullptr;
     cudaFree(exact_counter); exact_counter = nullptr;
     cudaFree(batch_counters); batch_counters = nullptr; batch_cap = 0;
-    cudaFree(share_entries); share_entries = nullptr;
     cudaFree(out_f32); cudaFree(out_u8);
     out_f32 = out_u8 = nullptr; out_f32_cap = out_u8_cap = 0;
     cudaFree(tables); tables = nullptr; tables_cap = 0;
@@ -179,12 +177,10 @@ int Workspace::ensure_idx(long long n) {
 
 int Workspace::ensure_batch_counters(int n) {
     n = std::max(n, BATCH_COUNTERS_MIN);
-    if (batch_counters && share_entries && batch_cap >= n) return RT_OK;
-    cudaFree(batch_counters); cudaFree(share_entries);
-    batch_counters = nullptr; share_entries = nullptr; batch_cap = 0;
-    int rc = dev_alloc(&batch_counters, (size_t)n * SWEEP_CTL_WORDS, "batch_counters");
-    if (rc == RT_OK) rc = dev_alloc(&share_entries, (size_t)n * SHARE_ENTRIES, "share_entries");
-    if (rc == RT_OK) rc = cudaMemset(share_entries, 0, sizeof(uint4) * (size_t)n * SHARE_ENTRIES) == cudaSuccess ? RT_OK : fail(RT_ERR_CUDA, "cudaMemset(share_entries)");
+    if (batch_counters && batch_cap >= n) return RT_OK;
+    cudaFree(batch_counters);
+    batch_counters = nullptr; batch_cap = 0;
+    int rc = dev_alloc(&batch_counters, (size_t)n, "batch_counters");
     if (rc == RT_OK) batch_cap = n;
     return rc;
 }
@@ -291,23 +287,12 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     CK(cudaMemcpyAsync(p.counters, init, sizeof(init), cudaMemcpyHostToDevice, st), "counters init");
     { // a counter per sweep launch: every level sweeps its tree rays and each light's shadow rays, chunk by chunk
         const long long need = (long long)(fp.depth + 2) * (1 + std::max(sc.n_point_lights, 0)) * sweep_table_chunks(sc);
-        if (need > 4096) return fail(RT_ERR_UNSUPPORTED, "depth %d x %d lights x %d table chunks: too many sweep launches per band", fp.depth, sc.n_point_lights, sweep_table_chunks(sc));
+        if (need > (1 << 24)) return fail(RT_ERR_UNSUPPORTED, "depth %d x %d lights x %d table chunks: too many sweep launches per band", fp.depth, sc.n_point_lights, sweep_table_chunks(sc));
         int rc = ws.ensure_batch_counters((int)need);
         if (rc != RT_OK) return rc;
     }
-    CK(cudaMemsetAsync(ws.batch_counters, 0, (size_t)ws.batch_cap * SWEEP_CTL_WORDS * sizeof(unsigned int), st), "batch counters");
+    CK(cudaMemsetAsync(ws.batch_counters, 0, (size_t)ws.batch_cap * sizeof(unsigned int), st), "batch counters");
     ws.batch_next = 0;
-    ws.share_epoch += 1; // (0 is what cleared entries hold)
-    if (ws.share_epoch == 0) ws.share_epoch = 1;
-    auto share_at = [&](int index) {
-        SweepShare sh;
-        if (tuning().share) {
-            sh.entries = ws.share_entries + (size_t)index * SHARE_ENTRIES;
-            sh.per_launch = SHARE_ENTRIES;
-            sh.epoch = ws.share_epoch;
-        }
-        return sh;
-    };
     cudaError_t sweep_err = cudaSuccess;
     launch_raygen(fp, p, sample0, n, st);
     scene->launches += 1;
@@ -323,8 +308,8 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         if (audit) launch_sweep_all_pairs(sc, a, b, ws.exact_counter, on);
         else {
             int used = 0;
-            cudaError_t e = launch_sweep(sc, a, b, ot, scene->sm_count, ws.batch_counters + (size_t)ws.batch_next * SWEEP_CTL_WORDS,
-                                         ws.batch_cap - ws.batch_next, &used, ws.exact_counter, share_at(ws.batch_next), on);
+            cudaError_t e = launch_sweep(sc, a, b, ot, scene->sm_count, ws.batch_counters + ws.batch_next,
+                                         ws.batch_cap - ws.batch_next, &used, ws.exact_counter, on);
             ws.batch_next += used;
             scene->launches += used > 0 ? used - 1 : 0;
             if (e != cudaSuccess && sweep_err == cudaSuccess) sweep_err = e;
@@ -401,8 +386,8 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
                 for (int l = 0; l < sc.n_point_lights; ++l) segs.push_back(light_seg(l));
                 int used = 0;
                 cudaError_t e = launch_sweep_jobs(sc, segs.data(), scene->light_tabs.data(), sc.n_point_lights, scene->sm_count,
-                                                  ws.batch_counters + (size_t)ws.batch_next * SWEEP_CTL_WORDS, ws.batch_cap - ws.batch_next, &used,
-                                                  ws.exact_counter, share_at(ws.batch_next), stream_for());
+                                                  ws.batch_counters + ws.batch_next, ws.batch_cap - ws.batch_next, &used,
+                                                  ws.exact_counter, stream_for());
                 if (e == cudaSuccess) {
                     merged = true;
                     ws.batch_next += used;

@@ -40,31 +40,16 @@ struct OriginTable {
     int shadow = 0; // the rays are the shadow rays of the light at O': any occluding hit ends a ray (sweep.cu: SHADOW)
 };
 
-// Work sharing inside a sweep launch.  Every launch (every job of a jobs launch) owns SWEEP_CTL_WORDS words:
-//   [0] next      static work items handed out so far (the plan of plan_items)
-//   [1] completed work items (static or shared) finished
-//   [2] head      tickets handed out for shared items
-//   [3] reserved  shared items announced
-// and SweepShare::per_launch entries {batch, slot_begin, slot_end, epoch}.  A warp that finds the static items
-// exhausted takes a ticket and waits for that shared item; a warp still busy then cuts the slots it has not
-// swept yet in two and announces the second half as a shared item (sweep.cu).  All words are zero at launch.
-constexpr int SWEEP_CTL_WORDS = 4;
-struct SweepShare {
-    uint4 *entries = nullptr;  // null: no sharing (items are what the plan says)
-    int per_launch = 0;        // entries per launch / job
-    unsigned int epoch = 0;    // tags the entries of this band (no clearing between bands)
-};
-
 // Nearest-hit query for every ray of s0 then s1 (Scene::intersect, scene/mod.rs:98-116).
-// batch_counters (device, n_counters zeroed blocks of SWEEP_CTL_WORDS words) hand work items to the persistent
-// warps, one block per launch; *used receives the number consumed (one per shared-memory chunk of the bound
-// table).  share.entries (if any) points at the entries of the first of these blocks.
+// batch_counters (device,
+// n_counters zeroed words) hand ray batches to the persistent warps, one word per launch;
+// *used receives the number consumed (one per shared-memory chunk of the bound table).
 // exact_counter (device, may be null; N_SWEEP_COUNTERS words) accumulates the number of exact pair
 // tests [0], [7], [8] and of filter evaluations [1..6] (sweep.cu: sweep_kernel).
 // origin.bound != null: every ray passes through origin's point; s1 must be empty.
 cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable origin, int sm_count,
                          unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
-                         SweepShare share, cudaStream_t stream);
+                         cudaStream_t stream);
 // Several sweeps against origin tables in ONE launch (the shadow rays of every light of a
 // wavefront level): job j = rays segs[j] (keys preset to KEY_MISS) against tabs[j]; CTA b serves job
 // b % n_jobs.  Consumes n_jobs batch counters.  cudaErrorNotSupported (nothing launched) when the
@@ -72,7 +57,7 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
 // and the caller falls back to one launch_sweep per job.
 cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs,
                               int sm_count, unsigned int *batch_counters, int n_counters, int *used,
-                              unsigned long long *exact_counter, SweepShare share, cudaStream_t stream);
+                              unsigned long long *exact_counter, cudaStream_t stream);
 // Launches one sweep of this scene's table takes (shared-memory chunks of the bound table; 1 when it is resident).
 int sweep_table_chunks(const DevScene &sc);
 // FMA per (ray, bound) pair of the two filters (for the executed-flop count)

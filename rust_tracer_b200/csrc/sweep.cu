@@ -86,7 +86,6 @@ constexpr float QUAD_SEED = (QUAD_MARGIN * GROUP_MARGIN - GROUP_MARGIN) / (GROUP
 constexpr float SUPER_SEED = (SUPER_MARGIN * QUAD_MARGIN * GROUP_MARGIN - GROUP_MARGIN) / (GROUP_MARGIN - 1.f) * 1.0001f; // likewise for a super
 constexpr int MIN_SLICE_SLOTS = SEG_PAD; // smallest table slice of a work item
 constexpr int SMEM_LIMIT = 232448;       // 227 KB opt-in dynamic shared memory per CTA on sm_100
-constexpr unsigned int SHARE_GUARD = 4096; // shared items are announced only while this many entries are free (>= the warps of a launch)
 
 struct RayRegs {
     float ox, oy, oz, dx, dy, dz;
@@ -181,9 +180,7 @@ struct SweepCtx {
 struct SweepJob {
     RaySeg s0;
     OriginTable ot;
-    unsigned int *batch_counter; // SWEEP_CTL_WORDS words
-    uint4 *share_entries;        // this job's shared items (null: no sharing)
-    unsigned int n_static;       // work items of the static plan
+    unsigned int *batch_counter;
     int n_slices, slice_slots, merge;
     int heavy_batches, heavy_slices, heavy_slice_slots;
     int reg_batches, tail_slices, tail_slice_slots;
@@ -404,28 +401,6 @@ RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, cons
 
 RT_DEV float2 f2(float x) { return make_float2(x, x); }
 
-RT_DEV unsigned int ld_volatile_u32(const unsigned int *p) {
-    unsigned int v;
-    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-// (no "memory" clobber: a hint read inside the filter loop; it need not order anything)
-RT_DEV uint2 ld_hint_u2(const unsigned int *p) {
-    uint2 v;
-    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
-    return v;
-}
-RT_DEV uint4 ld_volatile_u4(const uint4 *p) {
-    uint4 v;
-    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-    return v;
-}
-RT_DEV unsigned long long global_timer_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-
 // One persistent CTA per SM; slots [slot_begin, slot_end) of the bound table stay in shared
 // memory for the whole launch (staged by three bulk copies, cp.async.bulk + mbarrier, which run
 // while the warps fetch their first work item and load its rays).  A work item is (batch of
@@ -465,8 +440,7 @@ __global__ void __launch_bounds__(SWEEP_THREADS, 1)
 sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin, int slot_end, int n_slices_, int slice_slots_,
              int merge_, int planes, int item_max, int heavy_batches_, int heavy_slices_, int heavy_slice_slots_,
              int reg_batches_, int tail_slices_, int tail_slice_slots_,
-             unsigned int *batch_counter_, unsigned long long *exact_counter, const __grid_constant__ SweepJobs jobs,
-             uint4 *share_entries_, unsigned int n_static_, int share_cap, unsigned int share_epoch) {
+             unsigned int *batch_counter_, unsigned long long *exact_counter, const __grid_constant__ SweepJobs jobs) {
     static_assert(!SHADOW || ORIGIN, "shadow rays are swept against their light's origin table");
     constexpr int SWEEP_WARPS = SWEEP_THREADS / 32;
     constexpr unsigned int FULL = 0xffffffffu;
@@ -487,8 +461,6 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
     const int reg_batches = JOBS ? job.reg_batches : reg_batches_, tail_slices = JOBS ? job.tail_slices : tail_slices_;
     const int tail_slice_slots = JOBS ? job.tail_slice_slots : tail_slice_slots_;
     unsigned int *const batch_counter = JOBS ? job.batch_counter : batch_counter_;
-    uint4 *const share_entries = JOBS ? job.share_entries : share_entries_; // null: the items are what the plan says
-    const unsigned int n_static = JOBS ? job.n_static : n_static_;
     __shared__ ExactCount n_exact[SWEEP_WARPS];
     __shared__ unsigned long long n_hier[SWEEP_WARPS], n_slot[SWEEP_WARPS][MAX_SEGS];
     const int n_tab = slot_end - slot_begin, n_gtab = n_tab / GROUP_SLOTS, n_qtab = n_tab / QUAD_SLOTS, n_stab = n_tab / SUPER_SLOTS;
@@ -571,82 +543,38 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
     const float4 *qtab0 = qtab - slot_begin / QUAD_SLOTS;  // indexed by absolute quad
     const float4 *stab0 = stab - slot_begin / SUPER_SLOTS; // indexed by absolute super
 
-    // Work items: first the static plan (item numbers from ctl[0]), then -- with sharing -- whatever busy warps
-    // announce: a warp that finds the plan exhausted takes a ticket (ctl[2]) and waits for shared item number
-    // `ticket`, or for the end of the launch: every announced item (ctl[3]) and every item of the plan completed
-    // (ctl[1]).  An item is announced before its announcer completes, so that sum cannot be reached early.
-    bool plan_done = false;
     for (;;) {
-        unsigned int batch = 0;
-        int sb = 0, se = 0;
-        bool have = false;
-        if (!plan_done) {
-            unsigned int item = 0;
-            if (lane == 0) item = atomicAdd(batch_counter, 1u);
-            item = __shfl_sync(FULL, item, 0);
-            // items [0, heavy_batches * heavy_slices): the expensive first batches, cut finer
-            const unsigned int heavy_items = (unsigned int)heavy_batches * (unsigned int)heavy_slices;
-            int slice, ss;
-            if (item < heavy_items) {
-                batch = item / (unsigned int)heavy_slices;
-                slice = (int)(item - batch * (unsigned int)heavy_slices);
-                ss = heavy_slice_slots;
-            } else {
-                const unsigned int li = item - heavy_items, reg_items = (unsigned int)reg_batches * (unsigned int)n_slices;
-                if (li < reg_items) {
-                    batch = li / (unsigned int)n_slices;
-                    slice = (int)(li - batch * (unsigned int)n_slices);
-                    batch += (unsigned int)heavy_batches;
-                    ss = slice_slots;
-                } else { // the last batches of the launch, cut finer: the launch ends on short items
-                    const unsigned int lt = li - reg_items;
-                    batch = lt / (unsigned int)tail_slices;
-                    slice = (int)(lt - batch * (unsigned int)tail_slices);
-                    batch += (unsigned int)heavy_batches + (unsigned int)reg_batches;
-                    ss = tail_slice_slots;
-                }
-            }
-            if ((long long)batch * (R * 32) >= total) plan_done = true;
-            else {
-                RT_CHECK(item < n_static || !share_entries);
-                RT_CHECK(slice >= 0 && (slot_begin + slice * ss < slot_end || slot_end == slot_begin) && ss % SEG_PAD == 0); // (an empty table has one empty slice)
-                sb = slot_begin + slice * ss;
-                se = min(slot_end, sb + ss);
-                have = true;
+        unsigned int item = 0;
+        if (lane == 0) item = atomicAdd(batch_counter, 1u);
+        item = __shfl_sync(FULL, item, 0);
+        // items [0, heavy_batches * heavy_slices): the expensive first batches, cut finer
+        const unsigned int heavy_items = (unsigned int)heavy_batches * (unsigned int)heavy_slices;
+        unsigned int batch;
+        int slice, ss;
+        if (item < heavy_items) {
+            batch = item / (unsigned int)heavy_slices;
+            slice = (int)(item - batch * (unsigned int)heavy_slices);
+            ss = heavy_slice_slots;
+        } else {
+            const unsigned int li = item - heavy_items, reg_items = (unsigned int)reg_batches * (unsigned int)n_slices;
+            if (li < reg_items) {
+                batch = li / (unsigned int)n_slices;
+                slice = (int)(li - batch * (unsigned int)n_slices);
+                batch += (unsigned int)heavy_batches;
+                ss = slice_slots;
+            } else { // the last batches of the launch, cut finer: the launch ends on short items
+                const unsigned int lt = li - reg_items;
+                batch = lt / (unsigned int)tail_slices;
+                slice = (int)(lt - batch * (unsigned int)tail_slices);
+                batch += (unsigned int)heavy_batches + (unsigned int)reg_batches;
+                ss = tail_slice_slots;
             }
         }
-        if (!have) {
-            if (!share_entries) break;
-            uint4 ent = make_uint4(0u, 0u, 0u, 0u);
-            if (lane == 0) {
-                const unsigned int ticket = atomicAdd(batch_counter + 2, 1u);
-                const unsigned long long t0 = global_timer_ns();
-                for (;;) {
-                    if (ticket < (unsigned int)share_cap) {
-                        const uint4 e = ld_volatile_u4(share_entries + ticket);
-                        if (e.w == share_epoch) { // announced: the tag is written last, behind a fence; read the rest after it
-                            __threadfence();
-                            ent = ld_volatile_u4(share_entries + ticket);
-                            break;
-                        }
-                    }
-                    const unsigned int r1 = ld_volatile_u32(batch_counter + 3), done = ld_volatile_u32(batch_counter + 1),
-                                       r2 = ld_volatile_u32(batch_counter + 3);
-                    if (r1 == r2 && done == n_static + r1) break; // nothing left, nobody left who could announce
-                    if (global_timer_ns() - t0 > 2000000000ull) { // never spin for ever: a lost item shows as a wrong image, not a hang
-                        printf("rt_b200 sweep: shared work did not end (ticket %u, announced %u, completed %u of %u)\n", ticket, r1, done, n_static + r1);
-                        break;
-                    }
-                    __nanosleep(1000);
-                }
-            }
-            ent.x = __shfl_sync(FULL, ent.x, 0); ent.y = __shfl_sync(FULL, ent.y, 0);
-            ent.z = __shfl_sync(FULL, ent.z, 0); ent.w = __shfl_sync(FULL, ent.w, 0);
-            if (ent.w != share_epoch) break;
-            batch = ent.x; sb = (int)ent.y; se = (int)ent.z;
-            RT_CHECK((long long)batch * (R * 32) < total && sb >= slot_begin && se <= slot_end && sb < se && (sb - slot_begin) % SEG_PAD == 0);
-        }
-        const int ray0 = (int)((long long)batch * (R * 32));
+        const long long ray0_ll = (long long)batch * (R * 32);
+        if (ray0_ll >= total) break;
+        RT_CHECK(slice >= 0 && (slot_begin + slice * ss < slot_end || slot_end == slot_begin) && ss % SEG_PAD == 0); // (an empty table has one empty slice)
+        const int ray0 = (int)ray0_ll;
+        const int sb = slot_begin + slice * ss, se = min(slot_end, sb + ss);
 
         // vmask bits 2r, 2r+1: ray r of this lane exists, has no NaN component and is still
         // undecided (it can be queued); nanmask bit r: it exists and has a NaN component
@@ -683,10 +611,6 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                         const float d2 = vlen2(vsub(v3(ctx.lx, ctx.ly, ctx.lz), o));
                         wd2[r * 32 + lane] = d2;
                         first = plane_keys(sc.n_planes, sc.plane_shape, sc.plane_data, sc.geom, o, d, KEY_MISS);
-                        if (merge) { // what other items of this batch (table slices, shared halves) have found so far
-                            const unsigned long long seen = __ldcg(gi < s0.n ? s0.key + (long long)gi * s0.stride : s1.key + (gi - s0.n));
-                            first = seen < first ? seen : first;
-                        }
                         if (first != KEY_MISS) {
                             const float tp = key_t(first);
                             if (tp < 0.f || occludes(o, d, tp, d2)) vmask &= ~(3u << (2 * r));
@@ -741,8 +665,6 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         // filter evaluations of this item, in units of 32 (one per lane): against group / quad spheres,
         // and (per segment of the table = per kind of shape) against bound slots
         unsigned int evals_hier = 0;
-        uint2 seen = make_uint2(0u, 0u); // (tickets handed out, shared items announced) as of one super pair ago: more tickets
-                                         // than items = warps are waiting with nothing to do
         // the segment of slot j (segments hold one kind of shape each; ends of unused segments are INT_MAX)
         auto seg_of = [&](int j) { return (j >= sc.segs.end[0] ? 1 : 0) + (j >= sc.segs.end[1] ? 1 : 0) + (j >= sc.segs.end[2] ? 1 : 0); };
         for (int g = 0; g < sc.runs.n && alive; ++g) { // runs of segments that share their margin factors
@@ -762,28 +684,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 }
             }
 #if RT_SWEEP_SUPERS
-            for (int js = gb; js < min(ge, se) && alive; js += 2 * SUPER_SLOTS) { // runs and slices are whole pairs of supers (SEG_PAD)
-            if (share_entries) {
-                // Idle warps?  Then announce the second half of what this item has not swept yet as a shared item
-                // and keep the first (halving again at the next pair if there is still someone idle).
-                const int rest = se - (js + SEG_PAD);
-                if (seen.x > seen.y && rest >= 2 * SEG_PAD) {
-                    const int mid = js + SEG_PAD + (rest / 2) / SEG_PAD * SEG_PAD;
-                    int ok = 0;
-                    if (lane == 0 && ld_volatile_u32(batch_counter + 3) + SHARE_GUARD < (unsigned int)share_cap) {
-                        const unsigned int k = atomicAdd(batch_counter + 3, 1u);
-                        if (k < (unsigned int)share_cap) {
-                            share_entries[k] = make_uint4(batch, (unsigned int)mid, (unsigned int)se, 0u);
-                            __threadfence();
-                            asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(&share_entries[k].w), "r"(share_epoch) : "memory");
-                            ok = 1;
-                        }
-                    }
-                    ok = __shfl_sync(FULL, ok, 0);
-                    if (ok) se = mid;
-                }
-                seen = ld_hint_u2(batch_counter + 2);
-            }
+            for (int js = gb; js < ge && alive; js += 2 * SUPER_SLOTS) { // runs and slices are whole pairs of supers (SEG_PAD)
             // which of the two supers (4 quads each) can any ray of this warp touch?
             unsigned int supers_hit;
             {
@@ -971,7 +872,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                         : KEY_MISS;
             } else {
                 k = wbest[r * 32 + lane];
-                if (!SHADOW && planes && sb == slot_begin) { // (SHADOW: the planes went first, into wbest)
+                if (!SHADOW && planes && slice == 0) { // (SHADOW: the planes went first, into wbest)
                     RayRegs rr = load_ray(s0, s1, gi);
                     k = plane_keys(sc.n_planes, sc.plane_shape, sc.plane_data, sc.geom, v3(rr.ox, rr.oy, rr.oz),
                                    v3(rr.dx, rr.dy, rr.dz), k);
@@ -983,10 +884,6 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
             else if (k != KEY_MISS) atomicMin(kp, k);
         }
         __syncwarp();
-        if (share_entries && lane == 0) { // this item is done (whatever it announced, it announced before)
-            __threadfence();
-            atomicAdd(batch_counter + 1, 1u);
-        }
     }
     if (!table_ready) mbar_wait(&tab_bar, 0); // never leave a CTA with its bulk copies in flight
     if (exact_counter && lane == 0) {
@@ -1113,15 +1010,14 @@ template <int R, int T, bool SHADOW> static size_t sweep_smem_bytes(int slots) {
 template <int R, int T, bool ORIGIN, bool SHADOW>
 static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, long long total, int sm_count,
                                   unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
-                                  SweepShare share, cudaStream_t stream) {
+                                  cudaStream_t stream) {
     constexpr int SWEEP_WARPS = T / 32;
     const int cap = sweep_table_cap<R, T, SHADOW>();
     const int n_chunks = std::max(1, (sc.n_slots + cap - 1) / cap);
     if (n_chunks > n_counters) return cudaErrorInvalidValue;
     // chunks of equal size (rounded to SEG_PAD) rather than cap, cap, ..., rest
     const int per = ((sc.n_slots + n_chunks - 1) / n_chunks + SEG_PAD - 1) / SEG_PAD * SEG_PAD;
-    ItemPlan pl = plan_items<R>(total, s0.heavy, per, (long long)sm_count * SWEEP_WARPS, n_chunks);
-    if (share.entries) pl.merge = 1; // an item may hand part of its slots to another warp: keys are folded in
+    const ItemPlan pl = plan_items<R>(total, s0.heavy, per, (long long)sm_count * SWEEP_WARPS, n_chunks);
     if (pl.merge) { // every item folds its keys in with atomicMin: start from "no hit"
         cudaError_t err = cudaSuccess;
         if (s0.n > 0 && !s0.preset) {
@@ -1141,10 +1037,8 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
         sweep_kernel<R, T, ORIGIN, false, SHADOW><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, pl.n_slices, pl.slice_slots, pl.merge,
                                                                              c == n_chunks - 1 ? 1 : 0, tuning().item_max, (int)pl.heavy_batches,
                                                                              pl.heavy_slices, pl.heavy_slice_slots, (int)pl.reg_batches,
-                                                                             pl.tail_slices, pl.tail_slice_slots, batch_counters + (size_t)c * SWEEP_CTL_WORDS,
-                                                                             exact_counter, no_jobs,
-                                                                             share.entries ? share.entries + (size_t)c * share.per_launch : nullptr,
-                                                                             (unsigned int)pl.items, share.per_launch, share.epoch);
+                                                                             pl.tail_slices, pl.tail_slice_slots, batch_counters + c,
+                                                                             exact_counter, no_jobs);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
     }
     *used = n_chunks;
@@ -1163,8 +1057,7 @@ static int pick_rays_per_thread(long long total, int n_slots, int sm_count) {
 
 template <int R, int T, bool SHADOW>
 static cudaError_t launch_sweep_jobs_r(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int sm_count,
-                                       unsigned int *batch_counters, unsigned long long *exact_counter, SweepShare share,
-                                       cudaStream_t stream) {
+                                       unsigned int *batch_counters, unsigned long long *exact_counter, cudaStream_t stream) {
     constexpr int SWEEP_WARPS = T / 32;
     if (sc.n_slots > sweep_table_cap<R, T, SHADOW>()) return cudaErrorNotSupported; // one resident table only
     SweepJobs jobs{};
@@ -1174,10 +1067,8 @@ static cudaError_t launch_sweep_jobs_r(const DevScene &sc, const RaySeg *segs, c
         const long long ctas = (sm_count - j + n_jobs - 1) / n_jobs; // CTAs b with b % n_jobs == j
         const ItemPlan pl = plan_items<R>(segs[j].n, segs[j].heavy, sc.n_slots, ctas * SWEEP_WARPS, 1, true);
         SweepJob &J = jobs.j[j];
-        J.s0 = segs[j]; J.ot = tabs[j]; J.batch_counter = batch_counters + (size_t)j * SWEEP_CTL_WORDS;
-        J.share_entries = share.entries ? share.entries + (size_t)j * share.per_launch : nullptr;
-        J.n_static = (unsigned int)pl.items;
-        J.n_slices = pl.n_slices; J.slice_slots = pl.slice_slots; J.merge = (pl.merge || share.entries) ? 1 : 0;
+        J.s0 = segs[j]; J.ot = tabs[j]; J.batch_counter = batch_counters + j;
+        J.n_slices = pl.n_slices; J.slice_slots = pl.slice_slots; J.merge = pl.merge;
         J.heavy_batches = (int)pl.heavy_batches; J.heavy_slices = pl.heavy_slices; J.heavy_slice_slots = pl.heavy_slice_slots;
         J.reg_batches = (int)pl.reg_batches; J.tail_slices = pl.tail_slices; J.tail_slice_slots = pl.tail_slice_slots;
     }
@@ -1186,14 +1077,13 @@ static cudaError_t launch_sweep_jobs_r(const DevScene &sc, const RaySeg *segs, c
     if (err != cudaSuccess) return err;
     const RaySeg none{nullptr, nullptr, nullptr, 0};
     sweep_kernel<R, T, true, true, SHADOW><<<grid, T, smem, stream>>>(sc, none, none, OriginTable{}, 0, sc.n_slots, 1, SEG_PAD, 0, 1, tuning().item_max,
-                                                                      0, 1, SEG_PAD, 0, 1, SEG_PAD, nullptr, exact_counter, jobs, nullptr, 0u,
-                                                                      share.per_launch, share.epoch);
+                                                                      0, 1, SEG_PAD, 0, 1, SEG_PAD, nullptr, exact_counter, jobs);
     return cudaGetLastError();
 }
 
 cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const OriginTable *tabs, int n_jobs, int sm_count,
                               unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
-                              SweepShare share, cudaStream_t stream) {
+                              cudaStream_t stream) {
     *used = 0;
     if (n_jobs < 2 || n_jobs > MAX_SWEEP_JOBS || n_jobs > n_counters || sm_count < n_jobs) return cudaErrorNotSupported;
     long long most = 0;
@@ -1206,8 +1096,8 @@ cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const Orig
     const bool anyhit = tuning().shadow_anyhit != 0;
     cudaError_t err;
 #define RT_JOBS(R_) \
-    (anyhit ? launch_sweep_jobs_r<R_, 512, true>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, share, stream) \
-            : launch_sweep_jobs_r<R_, 512, false>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, share, stream))
+    (anyhit ? launch_sweep_jobs_r<R_, 512, true>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream) \
+            : launch_sweep_jobs_r<R_, 512, false>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream))
     if (r >= 4) err = RT_JOBS(4);
     else if (r >= 2) err = RT_JOBS(2);
     else err = RT_JOBS(1);
@@ -1218,7 +1108,7 @@ cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const Orig
 
 cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, int sm_count,
                          unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
-                         SweepShare share, cudaStream_t stream) {
+                         cudaStream_t stream) {
     long long total = (long long)s0.n + s1.n;
     *used = 0;
     if (total <= 0) return cudaSuccess;
@@ -1226,7 +1116,7 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
     if (sm_count < 1) sm_count = 1;
     const int r = pick_rays_per_thread(total, sc.n_slots, sm_count);
 #define RT_SWEEP(R_, T_, O_, S_) \
-    launch_sweep_r<R_, T_, O_, S_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, share, stream)
+    launch_sweep_r<R_, T_, O_, S_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
     if (ot.bound && ot.shadow && tuning().shadow_anyhit) { // the shadow rays of one light
         if (r >= 4) return RT_SWEEP(4, 512, true, true);
         if (r >= 2) return RT_SWEEP(2, 512, true, true);

@@ -17,9 +17,8 @@ struct Tuning {
     int want_heavy_jobs = 4;    // ... the same for the shadow rays of a level (one launch for all lights)
     int tail_min = 0;           // sweep: the tail of a launch is cut finer only if it has >= tail_min batches per warp
     int slices = 0;             // sweep: force this many table slices per batch; 0 = plan
-    int tail_pct = 8;           // sweep: the last tail_pct % of a launch's batches ...
-    int tail_mult = 2;          // ... are cut tail_mult times finer
-    int share = 1;              // sweep: busy warps hand half of their unswept slots to idle ones once the static items are out
+    int tail_pct = 15;          // sweep: the last tail_pct % of a launch's batches ...
+    int tail_mult = 4;          // ... are cut tail_mult times finer
     int item_max = 16;          // sweep: lanes with a touching ray up to which a group is swept pair by pair
     int table_cap = 0;          // sweep: bound slots per shared-memory chunk; 0 = what fits (tests force chunks)
     int merge_lights = 1;       // wavefront: all lights' shadow rays of a level in one launch
