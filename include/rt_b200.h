@@ -341,6 +341,15 @@ int rt_forest_get_stats(rt_forest *forest, rt_forest_stats *out);
 /* RayForest::size (src/render_tree.rs:62-64) and trees_with (:68-70). */
 int rt_forest_size(rt_forest *forest, uint64_t *out);
 int rt_forest_trees_with(rt_forest *forest, int32_t shape_id, uint64_t *out);
+/* rt_forest_trees_with without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same inputs, same result; the per-tree marks
+ * and the count live in a static device array of RT_STATIC_TREES_MAX + 256 bytes that every GPU
+ * loading the library holds until exit.  RT_ERR_INVALID for a forest of more than
+ * RT_STATIC_TREES_MAX trees.  Calls no cudaMalloc / cudaFree.  All calls on one GPU share the
+ * array: calls that overlap on the GPU race, serialise them per device.                 */
+#define RT_STATIC_TREES_MAX (4 * 1024 * 1024)
+int rt_forest_trees_with_static(rt_forest *forest, int32_t shape_id, uint64_t *out);
 void rt_forest_destroy(rt_forest *forest);
 
 /* ---- measurement --------------------------------------------------------------------- */

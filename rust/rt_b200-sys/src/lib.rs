@@ -287,6 +287,9 @@ extern "C" {
     pub fn rt_forest_get_stats(forest: *mut rt_forest, out: *mut rt_forest_stats) -> c_int;
     pub fn rt_forest_size(forest: *mut rt_forest, out: *mut u64) -> c_int;
     pub fn rt_forest_trees_with(forest: *mut rt_forest, shape_id: i32, out: *mut u64) -> c_int;
+    /// Not in the reference: `rt_forest_trees_with` on static device scratch, no allocation
+    /// (at most `RT_STATIC_TREES_MAX` = 4 Mi trees).
+    pub fn rt_forest_trees_with_static(forest: *mut rt_forest, shape_id: i32, out: *mut u64) -> c_int;
     pub fn rt_forest_destroy(forest: *mut rt_forest);
 
     // ---- measurement

@@ -61,6 +61,7 @@ def _declare(lib):
     lib.rt_forest_get_stats.argtypes = [vp, P(abi.rt_forest_stats)]
     lib.rt_forest_size.argtypes = [vp, P(C.c_uint64)]
     lib.rt_forest_trees_with.argtypes = [vp, C.c_int32, P(C.c_uint64)]
+    lib.rt_forest_trees_with_static.argtypes = [vp, C.c_int32, P(C.c_uint64)]
     lib.rt_forest_destroy.argtypes = [vp]
     lib.rt_forest_destroy.restype = None
     lib.rt_measure_fp32_peak.argtypes = [C.c_int32, P(C.c_double), P(C.c_int32), P(C.c_int32)]
@@ -94,7 +95,7 @@ EXPORTS = [
     "rt_multi_destroy", "rt_render_multi",
     "rt_frame_alloc", "rt_frame_export", "rt_frame_import", "rt_frame_release", "rt_frame_signal", "rt_frame_wait",
     "rt_forest_build", "rt_forest_eval", "rt_forest_eval_filtered", "rt_forest_get_stats", "rt_forest_size",
-    "rt_forest_trees_with", "rt_forest_destroy", "rt_measure_fp32_peak",
+    "rt_forest_trees_with", "rt_forest_trees_with_static", "rt_forest_destroy", "rt_measure_fp32_peak",
     "rt_builtin_scene", "rt_synthetic_scene", "rt_scene_desc_free", "rt_scene_desc_save", "rt_scene_desc_load",
     "rt_matrix_inverse", "rt_matrix_compose",
     "rt_plane_axes", "rt_triangle_normal",

@@ -286,6 +286,13 @@ class Forest:
         check(lib().rt_forest_trees_with(self._h, shape_id, C.byref(n)))
         return n.value
 
+    def trees_with_static(self, shape_id):
+        """trees_with through the entry point that allocates nothing (static device scratch, at most
+        RT_STATIC_TREES_MAX trees; not in the reference)."""
+        n = C.c_uint64()
+        check(lib().rt_forest_trees_with_static(self._h, shape_id, C.byref(n)))
+        return n.value
+
     def close(self):
         if self._h:
             lib().rt_forest_destroy(self._h)
