@@ -356,7 +356,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         // each other: launched on separate streams, the next one's CTAs take over the SMs the
         // previous one's have left, instead of waiting for its last work item.  One timed span
         // per level then; tracing keeps them serial and timed one by one.
-        const bool fork = !trace && scene_aux_streams(scene, 1 + sc.n_point_lights);
+        const bool fork = tuning().trace != 1 && scene_aux_streams(scene, 1 + sc.n_point_lights);
         const int n_aux = (int)scene->aux.size();
         cudaEvent_t e0 = nullptr, e1 = nullptr, forked = nullptr;
         long long rays = 0;
@@ -412,6 +412,12 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
             if (rays > 0) {
                 acc.sweep_spans.push_back({e0, e1});
                 acc.sweep_rays.push_back(rays);
+                if (trace) { // trace 2: the level's counters
+                    unsigned long long c[N_SWEEP_COUNTERS] = {};
+                    cudaMemcpyAsync(c, ws.exact_counter, sizeof(c), cudaMemcpyDeviceToHost, st);
+                    cudaStreamSynchronize(st);
+                    acc.sweep_counts.insert(acc.sweep_counts.end(), c, c + 3);
+                }
             }
         }
     };

@@ -959,8 +959,8 @@ const Knob KNOBS[] = {
     {"node_bits", &Tuning::node_bits, 0, NODE_BIN_BITS_MAX},
     {"band_samples", &Tuning::band_samples, 1 << 10, 1 << 28}, {"origin_tables", &Tuning::origin_tables, 0, 1},
     {"origin_min_slots", &Tuning::origin_min_slots, 0, 1 << 24}, {"host_threads", &Tuning::host_threads, 1, 64},
-    {"shadow_anyhit", &Tuning::shadow_anyhit, 0, 1},       {"trace", &Tuning::trace, 0, 1},
-    {"scene_cache", &Tuning::scene_cache, 0, 1},
+    {"shadow_anyhit", &Tuning::shadow_anyhit, 0, 1},       {"trace", &Tuning::trace, 0, 2},
+    {"scene_cache", &Tuning::scene_cache, 0, 1},         {"job_rotate", &Tuning::job_rotate, 0, 1},
 };
 } // namespace
 

@@ -22,6 +22,7 @@ struct Tuning {
     int item_max = 16;          // sweep: lanes with a touching ray up to which a group is swept pair by pair
     int table_cap = 0;          // sweep: bound slots per shared-memory chunk; 0 = what fits (tests force chunks)
     int merge_lights = 1;       // wavefront: all lights' shadow rays of a level in one launch
+    int job_rotate = 1;         // sweep: in that launch, a CTA whose light has run out of work items goes on with another light's
     int heavy_allow = 65536;    // wavefront: slack on the count of expensive child rays
     int node_bits = 0;          // wavefront: bits per axis of the node order's cells (3..7); 0 = by the size of the level
     int band_samples = 1 << 23; // render: samples per band
@@ -30,7 +31,8 @@ struct Tuning {
     int host_threads = 4;       // scene: host threads of the table build
     int scene_cache = 1;        // scene: keep the tables of the last description built (api_scene.cu: host_scene_for)
     int shadow_anyhit = 1;      // sweep: a shadow ray stops at the first hit that occludes its light
-    int trace = 0;              // print per-phase host laps and per-sweep counters to stderr
+    int trace = 0;              // 1: print per-phase host laps and per-sweep counters to stderr (sweeps one by one);
+                                // 2: the same per level, the level's sweeps overlapped as in a normal call
 };
 
 Tuning &tuning();
