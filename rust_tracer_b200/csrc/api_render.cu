@@ -74,6 +74,12 @@ void Workspace::release() {
     cudaFree(out_f32); cudaFree(out_u8);
     out_f32 = out_u8 = nullptr; out_f32_cap = out_u8_cap = 0;
     cudaFree(tables); tables = nullptr; tables_cap = 0;
+    for (int i = 0; i < n_aux; ++i) cudaStreamDestroy(aux[i]);
+    n_aux = 0;
+    if (stream) cudaStreamDestroy(stream);
+    stream = nullptr;
+    for (int i = 0; i < n_events; ++i) cudaEventDestroy(events[i]);
+    n_events = 0;
 }
 
 // ---- per-device cache of one released workspace --------------------------------------------
@@ -202,32 +208,42 @@ int Workspace::ensure_misc() {
 // ---- the wavefront ------------------------------------------------------------------------
 
 // Make sure the scene has min(want, 8) auxiliary streams; false if they cannot be had.
-static bool scene_aux_streams(rt_scene *scene, int want) {
-    want = std::min(std::max(want, 1), 8);
-    while ((int)scene->aux.size() < want) {
+static bool ws_aux_streams(Workspace &ws, int want) {
+    want = std::min(std::max(want, 1), (int)Workspace::MAX_AUX);
+    while (ws.n_aux < want) {
         cudaStream_t s = nullptr;
         if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) {
             cudaGetLastError();
-            return !scene->aux.empty();
+            return ws.n_aux > 0;
         }
-        scene->aux.push_back(s);
+        ws.aux[ws.n_aux++] = s;
     }
     return true;
 }
 
+// Events of one call, out of the workspace's store (created on first use, kept for the next call: every
+// call ends with a synchronisation of its stream, so none is in flight when it is handed out again).
 struct EventPool {
-    std::vector<cudaEvent_t> ev;
-    size_t used = 0;
+    Workspace &ws;
+    int used = 0;
+    std::vector<cudaEvent_t> extra; // beyond the store: created and destroyed by this call
+    explicit EventPool(Workspace &w) : ws(w) {}
     cudaEvent_t get() {
-        if (used == ev.size()) {
-            cudaEvent_t e;
-            cudaEventCreate(&e);
-            ev.push_back(e);
+        if (used < Workspace::MAX_EVENTS) {
+            if (used == ws.n_events) {
+                cudaEvent_t e = nullptr;
+                cudaEventCreate(&e);
+                ws.events[ws.n_events++] = e;
+            }
+            return ws.events[used++];
         }
-        return ev[used++];
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        extra.push_back(e);
+        return e;
     }
     ~EventPool() {
-        for (cudaEvent_t e : ev) cudaEventDestroy(e);
+        for (cudaEvent_t e : extra) cudaEventDestroy(e);
     }
 };
 
@@ -356,18 +372,18 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         // each other: launched on separate streams, the next one's CTAs take over the SMs the
         // previous one's have left, instead of waiting for its last work item.  One timed span
         // per level then; tracing keeps them serial and timed one by one.
-        const bool fork = tuning().trace != 1 && scene_aux_streams(scene, 1 + sc.n_point_lights);
-        const int n_aux = (int)scene->aux.size();
+        const bool fork = tuning().trace != 1 && ws_aux_streams(ws, 1 + sc.n_point_lights);
+        const int n_aux = ws.n_aux;
         cudaEvent_t e0 = nullptr, e1 = nullptr, forked = nullptr;
         long long rays = 0;
         if (fork) {
             e0 = events.get(); e1 = events.get(); forked = events.get();
             cudaEventRecord(e0, st);
             cudaEventRecord(forked, st);
-            for (int i = 0; i < n_aux; ++i) cudaStreamWaitEvent(scene->aux[i], forked, 0);
+            for (int i = 0; i < n_aux; ++i) cudaStreamWaitEvent(ws.aux[i], forked, 0);
         }
         int next_aux = 0;
-        auto stream_for = [&]() { return fork ? scene->aux[next_aux++ % n_aux] : st; };
+        auto stream_for = [&]() { return fork ? ws.aux[next_aux++ % n_aux] : st; };
         // tree rays first: measured against shadows first (c4: 51.4 vs 52.0 ms)
         sweep_on(tree, none, level == 0 ? scene->cam : general, stream_for(), !fork);
         rays += tree.n;
@@ -405,7 +421,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         if (fork) {
             for (int i = 0; i < std::min(next_aux, n_aux); ++i) {
                 cudaEvent_t done = events.get();
-                cudaEventRecord(done, scene->aux[i]);
+                cudaEventRecord(done, ws.aux[i]);
                 cudaStreamWaitEvent(st, done, 0);
             }
             cudaEventRecord(e1, st);
@@ -614,7 +630,7 @@ int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_params *p
     const long long n_samples = n_pixels * pr->spp;
     FrameParams fp = frame_params(cam, pr, ws.rows, (int)rows.size());
 
-    EventPool events;
+    EventPool events(ws);
     cudaEvent_t ev0 = events.get(), ev1 = events.get();
     scene->launches = 0;
     CK(cudaMemsetAsync(ws.exact_counter, 0, N_SWEEP_COUNTERS * sizeof(unsigned long long), st), "exact counter");
@@ -751,7 +767,7 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
     f->n_samples = (int)n;
     f->width = camera->x_res;
     f->n_rows = (int)rows.size();
-    EventPool events;
+    EventPool events(ws);
     cudaEvent_t ev0 = events.get(), ev1 = events.get();
     cudaStream_t st = scene->stream;
     cudaMemsetAsync(ws.exact_counter, 0, N_SWEEP_COUNTERS * sizeof(unsigned long long), st);
@@ -838,7 +854,7 @@ static int forest_eval_impl(rt_forest *f, const float *ambient, const int32_t *i
     if ((rc = ws.ensure_samples(std::max(n, 1))) != RT_OK) return rc;
     DevScene sc = scene->dev; // current materials; ambient as passed by the caller
     if (ambient) { sc.amb_r = ambient[0]; sc.amb_g = ambient[1]; sc.amb_b = ambient[2]; }
-    EventPool events;
+    EventPool events(ws);
     cudaEvent_t ev0 = events.get(), ev1 = events.get();
     cudaEventRecord(ev0, st);
     const unsigned char *mask = nullptr;

@@ -790,9 +790,7 @@ int host_scene_for(const rt_scene_desc *desc, std::shared_ptr<const HostScene> *
 void scene_free(rt_scene *scene) {
     if (!scene) return;
     cudaSetDevice(scene->device);
-    workspace_give_cached(scene->device, scene->ws);
-    for (cudaStream_t a : scene->aux) cudaStreamDestroy(a);
-    if (scene->own_stream) cudaStreamDestroy(scene->own_stream);
+    workspace_give_cached(scene->device, scene->ws); // the scene's stream goes with it
     delete scene;
 }
 
@@ -813,11 +811,6 @@ int upload_scene(const std::shared_ptr<const HostScene> &host, int device, rt_sc
     s->dev = hs.dev;
     DevScene &d = s->dev;
     cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
-    if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) {
-        scene_free(s);
-        return cuda_fail(e, "cudaStreamCreate");
-    }
-    s->own_stream = s->stream;
     const DevMaterial *dm = nullptr;
     Arena arena;
     arena.add(hs.bound, &d.bound); arena.add(hs.group, &d.group); arena.add(hs.quad, &d.quad); arena.add(hs.super, &d.super);
@@ -833,6 +826,11 @@ int upload_scene(const std::shared_ptr<const HostScene> &host, int device, rt_sc
         arena.add_raw(nullptr, (size_t)(d.n_slots + n_groups + n_quads + n_supers) * sizeof(float4), (const void **)&cam_tab);
     }
     s->ws = workspace_take_cached(device);
+    if (!s->ws.stream && (e = cudaStreamCreateWithFlags(&s->ws.stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        scene_free(s);
+        return cuda_fail(e, "cudaStreamCreate");
+    }
+    s->stream = s->own_stream = s->ws.stream;
     int rc = arena.commit(s, s->stream);
     if (rc != RT_OK) {
         scene_free(s);

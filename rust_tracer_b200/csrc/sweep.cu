@@ -41,6 +41,7 @@
 // shadow rays of all lights of a wavefront level go into ONE launch whose CTAs each serve one
 // light's rays and origin table (JOBS).
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
 #include <cstdio>
 #include <type_traits>
@@ -1037,6 +1038,20 @@ template <int R, int T, bool SHADOW> static size_t sweep_smem_bytes(int slots) {
     return (size_t)(slots + slots / GROUP_SLOTS + slots / QUAD_SLOTS + slots / SUPER_SLOTS) * sizeof(float4) + sweep_smem_fixed<R, T, SHADOW>();
 }
 
+// Opt in to SMEM_LIMIT bytes of dynamic shared memory, once per kernel and device rather than per launch
+// (a driver call that takes a process-wide lock: it showed when 8 threads drive 8 devices).
+template <typename K> static cudaError_t allow_big_smem(K kernel, std::atomic<unsigned long long> &done) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64 && ((done.load(std::memory_order_acquire) >> dev) & 1ull)) return cudaSuccess;
+    cudaFuncAttributes fa{};
+    if ((e = cudaFuncGetAttributes(&fa, kernel)) != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - (int)fa.sharedSizeBytes); // static + dynamic <= 227 KB
+    if (e == cudaSuccess && dev >= 0 && dev < 64) done.fetch_or(1ull << dev, std::memory_order_release);
+    return e;
+}
+
 template <int R, int T, bool ORIGIN, bool SHADOW>
 static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable ot, long long total, int sm_count,
                                   unsigned int *batch_counters, int n_counters, int *used, unsigned long long *exact_counter,
@@ -1066,7 +1081,8 @@ static cudaError_t launch_sweep_r(const DevScene &sc, RaySeg s0, RaySeg s1, Orig
     for (int c = 0; c < n_chunks; ++c) {
         int b = c * per, e = std::min(sc.n_slots, b + per);
         const size_t smem = sweep_smem_bytes<R, T, SHADOW>(e - b);
-        cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, ORIGIN, false, SHADOW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        static std::atomic<unsigned long long> smem_allowed{0}; // per instantiation: bit d = done on device d
+        cudaError_t err = allow_big_smem(sweep_kernel<R, T, ORIGIN, false, SHADOW>, smem_allowed);
         if (err != cudaSuccess) return err;
         sweep_kernel<R, T, ORIGIN, false, SHADOW><<<grid, T, smem, stream>>>(sc, s0, s1, ot, b, e, pl.n_slices, pl.slice_slots, pl.merge,
                                                                              c == n_chunks - 1 ? 1 : 0, tuning().item_max, (int)pl.heavy_batches,
@@ -1112,7 +1128,8 @@ static cudaError_t launch_sweep_jobs_r(const DevScene &sc, const RaySeg *segs, c
                          segs[j].n, R, pl.items, pl.heavy_batches, pl.heavy_slices, pl.reg_batches, pl.n_slices, pl.tail_slices, ctas);
     }
     const size_t smem = sweep_smem_bytes<R, T, SHADOW>(sc.n_slots);
-    cudaError_t err = cudaFuncSetAttribute(sweep_kernel<R, T, true, true, SHADOW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static std::atomic<unsigned long long> smem_allowed{0};
+    cudaError_t err = allow_big_smem(sweep_kernel<R, T, true, true, SHADOW>, smem_allowed);
     if (err != cudaSuccess) return err;
     const RaySeg none{nullptr, nullptr, nullptr, 0};
     sweep_kernel<R, T, true, true, SHADOW><<<grid, T, smem, stream>>>(sc, none, none, OriginTable{}, 0, sc.n_slots, 1, SEG_PAD, 0, 1, tuning().item_max,
