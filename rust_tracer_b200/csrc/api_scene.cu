@@ -948,7 +948,7 @@ struct Knob {
     long long lo, hi;
 };
 const Knob KNOBS[] = {
-    {"rays_per_thread", &Tuning::rays_per_thread, 0, 4},   {"want_light", &Tuning::want_light, 1, 4096},
+    {"rays_per_thread", &Tuning::rays_per_thread, 0, 8},   {"want_light", &Tuning::want_light, 1, 4096},
     {"want_heavy", &Tuning::want_heavy, 1, 4096},          {"want_heavy_jobs", &Tuning::want_heavy_jobs, 1, 4096},
     {"tail_min", &Tuning::tail_min, 0, 1 << 20},          {"slices", &Tuning::slices, 0, 1 << 20},
     {"tail_pct", &Tuning::tail_pct, 0, 100},               {"tail_mult", &Tuning::tail_mult, 1, 64},

@@ -69,6 +69,9 @@ namespace rt {
 #ifndef RT_SWEEP_FLUSH_AT_SHADOW
 #define RT_SWEEP_FLUSH_AT_SHADOW 32 // the same for shadow rays (sooner = rays leave the sweep sooner)
 #endif
+#ifndef RT_SWEEP_R8
+#define RT_SWEEP_R8 0 // 1: also build 8 rays per thread x 256 threads (rays_per_thread=8; A/B builds)
+#endif
 #ifndef RT_SWEEP_BULK_TABLE
 #define RT_SWEEP_BULK_TABLE 0 // how the table reaches shared memory, measured on c4 (profiles/r02_ab_table_staging_heavy_c4.log):
                               // 0 = copied by the CTA's 512 threads behind a block barrier                       38.08 ms
@@ -77,7 +80,13 @@ namespace rt {
                               // 2 = cp.async.bulk in 96 chunks issued by the lanes of warp 0, wait before the
                               //     first item                                                                    53.35 ms
 #endif
-constexpr int QCAP = 256;                // queued pairs per warp
+#ifndef RT_SWEEP_QCAP
+#define RT_SWEEP_QCAP 256
+#endif
+#ifndef RT_SWEEP_T2
+#define RT_SWEEP_T2 512 // threads per CTA of the 2-rays-per-thread kernels (A/B builds: 1024 with RT_SWEEP_QCAP=128)
+#endif
+constexpr int QCAP = RT_SWEEP_QCAP;      // queued pairs per warp
 constexpr int BRUTE_UNROLL = RT_SWEEP_BRUTE_UNROLL;
 constexpr float U24 = 5.9604645e-08f;    // 2^-24, unit round-off of f32
 constexpr float GROUP_MARGIN = 17.f;     // margin of a group sphere / margin of a bound (make_group: a / rho <= 16)
@@ -1151,13 +1160,19 @@ cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const Orig
     const int r = pick_rays_per_thread(most, sc.n_slots, std::max(1, sm_count / n_jobs));
     const bool anyhit = tuning().shadow_anyhit != 0;
     cudaError_t err;
-#define RT_JOBS(R_) \
-    (anyhit ? launch_sweep_jobs_r<R_, 512, true>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream) \
-            : launch_sweep_jobs_r<R_, 512, false>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream))
+#define RT_JOBS_T(R_, T_) \
+    (anyhit ? launch_sweep_jobs_r<R_, T_, true>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream) \
+            : launch_sweep_jobs_r<R_, T_, false>(sc, segs, tabs, n_jobs, sm_count, batch_counters, exact_counter, stream))
+#define RT_JOBS(R_) RT_JOBS_T(R_, 512)
+#if RT_SWEEP_R8
+    if (r >= 8) err = RT_JOBS_T(8, 256);
+    else
+#endif
     if (r >= 4) err = RT_JOBS(4);
-    else if (r >= 2) err = RT_JOBS(2);
+    else if (r >= 2) err = RT_JOBS_T(2, RT_SWEEP_T2);
     else err = RT_JOBS(1);
 #undef RT_JOBS
+#undef RT_JOBS_T
     if (err == cudaSuccess) *used = n_jobs;
     return err;
 }
@@ -1173,18 +1188,25 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
     const int r = pick_rays_per_thread(total, sc.n_slots, sm_count);
 #define RT_SWEEP(R_, T_, O_, S_) \
     launch_sweep_r<R_, T_, O_, S_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
+#if RT_SWEEP_R8
+    if (r >= 8) {
+        if (ot.bound && ot.shadow && tuning().shadow_anyhit) return RT_SWEEP(8, 256, true, true);
+        if (ot.bound) return RT_SWEEP(8, 256, true, false);
+        return RT_SWEEP(8, 256, false, false);
+    }
+#endif
     if (ot.bound && ot.shadow && tuning().shadow_anyhit) { // the shadow rays of one light
         if (r >= 4) return RT_SWEEP(4, 512, true, true);
-        if (r >= 2) return RT_SWEEP(2, 512, true, true);
+        if (r >= 2) return RT_SWEEP(2, RT_SWEEP_T2, true, true);
         return RT_SWEEP(1, 512, true, true);
     }
     if (ot.bound) {
         if (r >= 4) return RT_SWEEP(4, 512, true, false);
-        if (r >= 2) return RT_SWEEP(2, 512, true, false);
+        if (r >= 2) return RT_SWEEP(2, RT_SWEEP_T2, true, false);
         return RT_SWEEP(1, 512, true, false);
     }
     if (r >= 4) return RT_SWEEP(4, 512, false, false); // 16 warps x <= 128 registers; more warps spill the filter loop
-    if (r >= 2) return RT_SWEEP(2, 512, false, false);
+    if (r >= 2) return RT_SWEEP(2, RT_SWEEP_T2, false, false);
     return RT_SWEEP(1, 512, false, false);
 #undef RT_SWEEP
 }

@@ -301,14 +301,16 @@ def test_merged_light_sweeps_and_tail_items_do_not_change_the_image():
     one launch per light (merge_lights = 0), and the finer work items at the end of a launch
     (tail_pct, tail_mult): scheduling only -- the same image and counts,
     and the same as the all-pairs audit.  Also at fewer rays per thread, where the jobs kernel is
-    another instantiation."""
+    another instantiation; with and without CTAs moving on to another light's items when theirs run out
+    (job_rotate)."""
     desc = rt.SceneDesc.synthetic(500, 500, 77, 0.03, 0.1)
     w, h, depth = 224, 126, 4
     ref = None
     for knobs in ({}, {"merge_lights": 0}, {"tail_pct": 0}, {"tail_pct": 100, "tail_mult": 8},
                   {"tail_pct": 50, "tail_mult": 64}, {"rays_per_thread": 1},
                   {"rays_per_thread": 2, "want_light": 16}, {"shadow_anyhit": 0}, {"shadow_anyhit": 0, "merge_lights": 0},
-                  {"merge_lights": 0, "rays_per_thread": 2}, {"merge_lights": 0, "table_cap": 512}):
+                  {"merge_lights": 0, "rays_per_thread": 2}, {"merge_lights": 0, "table_cap": 512},
+                  {"job_rotate": 0}, {"job_rotate": 0, "rays_per_thread": 1}, {"job_rotate": 1, "want_heavy_jobs": 64}):
         with rt.tuned(**knobs):
             sc = rt.Scene(desc)
             try:
