@@ -662,6 +662,19 @@ int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
     std::memset(&d, 0, sizeof(d));
     d.n_shapes = n; d.n_bounded = nb; d.n_planes = (int)plane_shape.size();
     d.n_slots = n_slots; d.segs = segs; d.cmax = round_up_f32(cmax * (1.0 + 1e-6));
+    { // largest sphere of each level of the hierarchy, for the sweeps' distance clip (origin tables move a centre by its f32 rounding only)
+        const std::vector<Bound> *levels[3] = {&groups, &quads, &supers};
+        for (int l = 0; l < 3; ++l) {
+            double r = 0.0;
+            bool all_pass = false;
+            for (const Bound &b : *levels[l]) {
+                if (b.w == -3.402823466e+38f) all_pass = true;
+                else if (b.w != 3.402823466e+38f) r = std::max(r, b.rf);
+            }
+            r = r * (1.0 + 1e-5) + 1e-5 * cmax;
+            d.level_rmax[l] = (all_pass || !(r < 1e15)) ? 3.0e38f : round_up_f32(r);
+        }
+    }
     for (int g = 0; g < segs.n; ++g) { // runs of segments with the same margins
         SweepSegs &r = d.runs;
         if (r.n > 0 && r.k[r.n - 1] == segs.k[g] && r.kx[r.n - 1] == segs.kx[g] && r.end[r.n - 1] == segs.begin[g]) {

@@ -69,6 +69,13 @@ namespace rt {
 #ifndef RT_SWEEP_FLUSH_AT_SHADOW
 #define RT_SWEEP_FLUSH_AT_SHADOW 32 // the same for shadow rays (sooner = rays leave the sweep sooner)
 #endif
+#ifndef RT_SWEEP_CLIP
+#define RT_SWEEP_CLIP 1 // nearest-hit sweeps: group / quad / super spheres wholly beyond a ray's best hit so far are not descended into
+#endif
+#ifndef RT_SWEEP_NEAR_FIRST
+#define RT_SWEEP_NEAR_FIRST 0 // 1: a work item visits the super pairs of a run nearest first (as seen from its first ray's origin). Measured: no gain on c4
+                               // (35.99 vs 35.69 ms, profiles/r02_ab_near_first_c4.log) -- in a dense scene the first hit found already clips well
+#endif
 #ifndef RT_SWEEP_R8
 #define RT_SWEEP_R8 0 // 1: also build 8 rays per thread x 256 threads (rays_per_thread=8; A/B builds)
 #endif
@@ -184,6 +191,7 @@ struct SweepCtx {
     const float4 *slot_geom;
     const float4 *cube_tris;
     float lx, ly, lz; // SHADOW: the light the rays of this CTA travel towards
+    float cmax;       // DevScene::cmax
     int n_slots;      // (checked build)
 };
 
@@ -212,6 +220,20 @@ struct SweepJobs {
 // for bit.  For t >= 0 the left side is a non-decreasing function of t even in f32 (a chain of
 // monotone roundings), so once ANY hit with t >= 0 occludes, the nearest hit occludes too.
 RT_DEV bool occludes(V3 o, V3 d, float t, float light_d2) { return vlen2(vsub(ray_at(o, d, t), o)) < light_d2; }
+
+// sqrt.approx / rsqrt.approx (2 ulp): the filter's margins allow dh 4 u of error per component and every length
+// here is rounded UP by a factor far above 2 ulp, so the IEEE sqrt and the three IEEE divisions (some 90
+// instructions per ray, once per work item) are not needed
+RT_DEV float sqrt_approx(float x) {
+    float y;
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+RT_DEV float rsqrt_approx(float x) {
+    float y;
+    asm("rsqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 // per-warp counters of the exact stage
 struct ExactCount {
@@ -245,7 +267,7 @@ RT_DEV PairOperands fetch_pair(const SweepCtx *ctx, const unsigned int *wqueue, 
 
 template <bool SHADOW>
 __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueue, unsigned long long *wbest, int ray0,
-                                        int cnt, int all, ExactCount *n_exact, const float *wd2, unsigned int *wocc) {
+                                        int cnt, int all, ExactCount *n_exact, float *wd2, unsigned int *wocc) {
     const int lane = threadIdx.x & 31;
     int done = 0;
     unsigned int n_sphere = 0, n_triangle = 0;
@@ -280,6 +302,16 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
                 atomicMin(&wbest[local], k);
                 if constexpr (SHADOW) {
                     if (occludes(o, d, key_t(k), wd2[local])) atomicOr(&wocc[local >> 5], 1u << (local & 31));
+                } else {
+#if RT_SWEEP_CLIP
+                    // distance clip (wd2 = the rays' clip distances here): nothing further along the ray than this hit can win.
+                    // 1.001 and 1e-4 (|O| + cmax) are far above the rounding of t, of |d| and of the filters' b (<= 24 u lambda)
+                    const float n2 = vlen2(d);
+                    const float s_hit = key_t(k) * sqrt_approx(n2);
+                    const float clip = fmaf(s_hit, 1.001f, 1e-4f * (sqrt_approx(vlen2(o)) + ctx->cmax));
+                    if (n2 > 1e-30f && n2 < 1e30f && clip >= 0.f) // (|d|^2 a normal f32; false for NaN)
+                        atomicMin((unsigned int *)&wd2[local], __float_as_uint(clip));
+#endif
                 }
             }
         }
@@ -369,20 +401,6 @@ RT_DEV RayCoef ray_coef(const RayRegs &r, float k_seg, float cmax, bool usable) 
 struct RayCoefO {
     float dx, dy, dz, mu, mu_g, tf;
 };
-
-// sqrt.approx / rsqrt.approx (2 ulp): the filter's margins allow dh 4 u of error per component and every length
-// here is rounded UP by a factor far above 2 ulp, so the IEEE sqrt and the three IEEE divisions (some 90
-// instructions per ray, once per work item) are not needed
-RT_DEV float sqrt_approx(float x) {
-    float y;
-    asm("sqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-RT_DEV float rsqrt_approx(float x) {
-    float y;
-    asm("rsqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
 
 RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, const OriginTable &ot, bool usable) {
     const float reach = ot.reach;
@@ -516,7 +534,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
     const int total = s0.n + s1.n;
     unsigned long long *wbest = best + warp * (32 * R);
     unsigned int *wqueue = queue + warp * QCAP;
-    float *wd2 = SHADOW ? light_d2 + warp * (32 * R) : nullptr;
+    float *wd2 = light_d2 + warp * (32 * R); // SHADOW: squared distance to the light; else: the distance clip of each ray
     unsigned int *wocc = SHADOW ? occluded + warp * R : nullptr;
     const unsigned int lt_mask = (1u << lane) - 1u;
 
@@ -526,6 +544,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         ctx.slot_meta = sc.slot_meta; ctx.slot_geom = sc.slot_geom; ctx.cube_tris = sc.cube_tris;
         ctx.lx = ot.ox; ctx.ly = ot.oy; ctx.lz = ot.oz;
         ctx.n_slots = sc.n_slots;
+        ctx.cmax = sc.cmax;
     }
     if (tid < 2) tab[n_tab + tid] = make_float4(0.f, 0.f, 0.f, 0.f); // prefetched past the end, never used
     if (lane == 0 && round == 0) {
@@ -658,6 +677,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 }
             }
             wbest[r * 32 + lane] = first;
+            if constexpr (!SHADOW) wd2[r * 32 + lane] = 3.0e38f; // no hit yet: no clip
         }
         __syncwarp();
         int qn = 0; // queued pairs of this warp (warp-uniform)
@@ -675,12 +695,28 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 if constexpr (ORIGIN) {
                     float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __fmul2_rn(cz, f2(c[r].dz))));
                     e[r] = __ffma2_rn(b, b, f2(level == 0 ? c[r].mu : (level == 1 ? c[r].mu_g : (level == 2 ? QUAD_MARGIN : SUPER_MARGIN * QUAD_MARGIN) * c[r].mu_g)));
+#if RT_SWEEP_CLIP
+                    if constexpr (!SHADOW) { // (the rays start at O': b is the distance along the ray to the centre's foot)
+                        if (level >= 1) {
+                            const float lim = wd2[r * 32 + lane] + sc.level_rmax[level - 1];
+                            if (b.x > lim) e[r].x = -3.0e38f; // the whole sphere lies beyond this ray's best hit
+                            if (b.y > lim) e[r].y = -3.0e38f;
+                        }
+                    }
+#endif
                 } else {
                     float2 b = __ffma2_rn(cx, f2(c[r].dx), __ffma2_rn(cy, f2(c[r].dy), __ffma2_rn(cz, f2(c[r].dz), f2(c[r].kb))));
                     float2 s = __ffma2_rn(cx, f2(c[r].ox2), __ffma2_rn(cy, f2(c[r].oy2), __ffma2_rn(cz, f2(c[r].oz2),
                                            f2(level == 0 ? c[r].seed : (level == 1 ? c[r].seed_g : fmaf(level == 2 ? QUAD_SEED : SUPER_SEED, c[r].seed_g - c[r].seed, c[r].seed_g))))));
                     // a centre behind the origin (b < 0): only s decides, i.e. whether the origin is inside the sphere
                     e[r] = __ffma2_rn(b, make_float2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f)), s);
+#if RT_SWEEP_CLIP
+                    if (level >= 1) {
+                        const float lim = wd2[r * 32 + lane] + sc.level_rmax[level - 1];
+                        if (b.x > lim) e[r].x = -3.0e38f;
+                        if (b.y > lim) e[r].y = -3.0e38f;
+                    }
+#endif
                 }
             }
         };
@@ -711,6 +747,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
             if (gb >= ge) continue;
             // the coefficients depend on the run through its margin factor only
             const float k_seg = ORIGIN ? sc.runs.kx[g] : sc.runs.k[g];
+            float ref_x = 0.f, ref_y = 0.f, ref_z = 0.f; // origin of this lane's first ray
             {
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
@@ -718,12 +755,40 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                     RayRegs rr;
                     rr.ox = rr.oy = rr.oz = rr.dx = rr.dy = rr.dz = 0.f;
                     if (usable) rr = load_ray(s0, s1, ray0 + r * 32 + lane);
+                    if (r == 0) { ref_x = rr.ox; ref_y = rr.oy; ref_z = rr.oz; }
                     if constexpr (ORIGIN) c[r] = ray_coef_origin(rr, k_seg, sc.cmax, ot, usable);
                     else c[r] = ray_coef(rr, k_seg, sc.cmax, usable);
                 }
             }
 #if RT_SWEEP_SUPERS
+#if RT_SWEEP_NEAR_FIRST
+            // Visiting order of the run's super pairs (at most 21 in a resident table): by the power of the item's first ray
+            // origin with respect to the nearer sphere of the pair, |G - O|^2 - R^2 = W - 2 G.O + |O|^2 -- a heuristic for
+            // "nearest first" only, nothing depends on it but how soon hits are found (SHADOW: rays leave; else: the clip).
+            // Lane p holds the key of pair p with p in its low 5 bits; the minimum of the warp is visited and retired.
+            unsigned int order_key = 0xffffffffu;
+            const int n_pairs = (ge - gb) / (2 * SUPER_SLOTS);
+            {
+                float ox = __shfl_sync(FULL, ref_x, 0), oy = __shfl_sync(FULL, ref_y, 0), oz = __shfl_sync(FULL, ref_z, 0);
+                if constexpr (ORIGIN) { ox -= ot.ox; oy -= ot.oy; oz -= ot.oz; } // the table is centred on O'
+                if (lane < n_pairs) {
+                    const float4 T0 = stab0[(gb >> 8) + 2 * lane], T1 = stab0[(gb >> 8) + 2 * lane + 1];
+                    const float o2 = fmaf(ox, ox, fmaf(oy, oy, oz * oz));
+                    const float p0 = fmaf(-2.f, fmaf(T0.x, ox, fmaf(T0.z, oy, T1.x * oz)), T1.z) + o2;
+                    const float p1 = fmaf(-2.f, fmaf(T0.y, ox, fmaf(T0.w, oy, T1.y * oz)), T1.w) + o2;
+                    unsigned int u = __float_as_uint(fminf(p0, p1));
+                    u ^= (u >> 31) ? 0xffffffffu : 0x80000000u; // orderable
+                    order_key = (u & ~31u) | (unsigned int)lane;
+                }
+            }
+            RT_CHECK(n_pairs <= 31);
+            for (int it = 0; it < n_pairs && alive; ++it) {
+            const unsigned int nearest = __reduce_min_sync(FULL, order_key);
+            if (order_key == nearest) order_key = 0xffffffffu; // retired
+            const int js = gb + (int)(nearest & 31u) * 2 * SUPER_SLOTS;
+#else
             for (int js = gb; js < ge && alive; js += 2 * SUPER_SLOTS) { // runs and slices are whole pairs of supers (SEG_PAD)
+#endif
             // which of the two supers (4 quads each) can any ray of this warp touch?
             unsigned int supers_hit;
             {
@@ -971,7 +1036,7 @@ sweep_all_pairs_kernel(DevScene sc, RaySeg s0, RaySeg s1, unsigned long long *ex
 
 template <int R, int T, bool SHADOW> static size_t sweep_smem_fixed() {
     return 2 * sizeof(float4) + (size_t)T * R * sizeof(unsigned long long) + (size_t)(T / 32) * QCAP * sizeof(unsigned int) +
-           (SHADOW ? (size_t)T * R * sizeof(float) + (size_t)(T / 32) * R * sizeof(unsigned int) : 0);
+           (size_t)T * R * sizeof(float) + (SHADOW ? (size_t)(T / 32) * R * sizeof(unsigned int) : 0);
 }
 
 // Bound slots one launch can keep in shared memory.

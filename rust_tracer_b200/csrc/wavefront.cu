@@ -15,6 +15,23 @@
 
 namespace rt {
 
+#ifndef RT_SHADE_MIN_BLOCKS
+#define RT_SHADE_MIN_BLOCKS 8 // resident blocks per SM the shade kernel is compiled for: 8 = 64 registers, 40 B of spills, 50 % occupancy instead of 37.5 %
+                              // (c4: spawn + shade + node order 4.70 -> 4.37 ms, profiles/r02_ab_wavefront_occupancy_c4.log); 0 = the compiler's choice
+#endif
+#ifndef RT_SPAWN_MIN_BLOCKS
+#define RT_SPAWN_MIN_BLOCKS 0 // likewise for the spawn kernel (blocks of 512 threads); 3 = 40 registers measured no faster
+#endif
+#if RT_SHADE_MIN_BLOCKS > 0
+#define RT_SHADE_BOUNDS __launch_bounds__(WF_BLOCK, RT_SHADE_MIN_BLOCKS)
+#else
+#define RT_SHADE_BOUNDS __launch_bounds__(WF_BLOCK)
+#endif
+#if RT_SPAWN_MIN_BLOCKS > 0
+#define RT_SPAWN_BOUNDS __launch_bounds__(SPAWN_BLOCK, RT_SPAWN_MIN_BLOCKS)
+#else
+#define RT_SPAWN_BOUNDS __launch_bounds__(SPAWN_BLOCK)
+#endif
 constexpr int WF_BLOCK = 128;
 
 RT_DEV unsigned long long splitmix64(unsigned long long &state) {
@@ -224,7 +241,7 @@ __global__ void __launch_bounds__(256) node_scatter_kernel(Pools p, int begin, i
 // the surface or into it -- which is what the sweep's group culling feeds on.
 constexpr int SPAWN_BLOCK = 512;
 
-__global__ void __launch_bounds__(SPAWN_BLOCK)
+__global__ void RT_SPAWN_BOUNDS
 spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn_children, int ordered, int s_begin) {
     const int rank = blockIdx.x * blockDim.x + threadIdx.x; // node number within the level when ordered
     bool refl = false, refr = false, far_node = false;
@@ -342,7 +359,7 @@ spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn
     }
 }
 
-__global__ void __launch_bounds__(WF_BLOCK)
+__global__ void RT_SHADE_BOUNDS
 shade_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int level, int light_stride, float4 *sample_rgb,
              const unsigned char *sample_mask) {
     int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
