@@ -76,6 +76,11 @@ namespace rt {
 #define RT_SWEEP_NEAR_FIRST 0 // 1: a work item visits the super pairs of a run nearest first (as seen from its first ray's origin). Measured: no gain on c4
                                // (35.99 vs 35.69 ms, profiles/r02_ab_near_first_c4.log) -- in a dense scene the first hit found already clips well
 #endif
+#ifndef RT_SWEEP_SLICE_MAJOR
+#define RT_SWEEP_SLICE_MAJOR 1 // items of a sliced launch are handed out slice by slice (all batches against slice 0, then slice 1, ...) and an item
+                               // starts from what earlier slices have left in the rays' keys: a shadow ray found occluded does not enter, a tree
+                               // ray starts with its clip.  0: batch by batch, every slice from scratch
+#endif
 #ifndef RT_SWEEP_R8
 #define RT_SWEEP_R8 0 // 1: also build 8 rays per thread x 256 threads (rays_per_thread=8; A/B builds)
 #endif
@@ -609,6 +614,28 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         const unsigned int heavy_items = (unsigned int)heavy_batches * (unsigned int)heavy_slices;
         unsigned int batch;
         int slice, ss;
+#if RT_SWEEP_SLICE_MAJOR
+        // within each of the three runs of items: slice-major (item = slice * batches + batch)
+        if (item < heavy_items) {
+            slice = (int)(item / (unsigned int)heavy_batches);
+            batch = item - (unsigned int)slice * (unsigned int)heavy_batches;
+            ss = heavy_slice_slots;
+        } else {
+            const unsigned int li = item - heavy_items, reg_items = (unsigned int)reg_batches * (unsigned int)n_slices;
+            if (li < reg_items) {
+                slice = (int)(li / (unsigned int)reg_batches);
+                batch = li - (unsigned int)slice * (unsigned int)reg_batches + (unsigned int)heavy_batches;
+                ss = slice_slots;
+            } else { // the last batches of the launch, cut finer: the launch ends on short items
+                const unsigned int lt = li - reg_items;
+                const long long tail_batches = ((long long)total + R * 32 - 1) / (R * 32) - heavy_batches - reg_batches;
+                if (tail_batches <= 0 || lt >= (unsigned long long)tail_batches * (unsigned int)tail_slices) break; // past the plan
+                slice = (int)(lt / (unsigned int)tail_batches);
+                batch = lt - (unsigned int)slice * (unsigned int)tail_batches + (unsigned int)heavy_batches + (unsigned int)reg_batches;
+                ss = tail_slice_slots;
+            }
+        }
+#else
         if (item < heavy_items) {
             batch = item / (unsigned int)heavy_slices;
             slice = (int)(item - batch * (unsigned int)heavy_slices);
@@ -628,6 +655,7 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                 ss = tail_slice_slots;
             }
         }
+#endif
         const long long ray0_ll = (long long)batch * (R * 32);
         if (ray0_ll >= total) break;
         RT_CHECK(slice >= 0 && (slot_begin + slice * ss < slot_end || slot_end == slot_begin) && ss % SEG_PAD == 0); // (an empty table has one empty slice)
@@ -673,11 +701,32 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                             const float tp = key_t(first);
                             if (tp < 0.f || occludes(o, d, tp, d2)) vmask &= ~(3u << (2 * r));
                         }
+#if RT_SWEEP_SLICE_MAJOR
+                        if (merge && slice > 0) { // what the items of earlier slices have found for this ray
+                            const unsigned long long seen = __ldcg(s0.key + (long long)gi * s0.stride);
+                            if (seen != KEY_MISS && occludes(o, d, key_t(seen), d2)) vmask &= ~(3u << (2 * r));
+                        }
+#endif
                     }
                 }
             }
             wbest[r * 32 + lane] = first;
-            if constexpr (!SHADOW) wd2[r * 32 + lane] = 3.0e38f; // no hit yet: no clip
+            if constexpr (!SHADOW) {
+                float clip0 = 3.0e38f; // no hit yet: no clip
+#if RT_SWEEP_SLICE_MAJOR && RT_SWEEP_CLIP && RT_SWEEP_PRELOAD
+                if (merge && slice > 0 && gi < total && ((vmask >> (2 * r)) & 1u)) {
+                    const unsigned long long seen = __ldcg(gi < s0.n ? s0.key + (long long)gi * s0.stride : s1.key + (gi - s0.n));
+                    if (seen != KEY_MISS) { // the same clip sweep_flush derives from a hit
+                        const RayRegs rr = pre[r];
+                        const float n2 = fmaf(rr.dx, rr.dx, fmaf(rr.dy, rr.dy, rr.dz * rr.dz));
+                        const float c0 = fmaf(key_t(seen) * sqrt_approx(n2), 1.001f,
+                                              1e-4f * (sqrt_approx(fmaf(rr.ox, rr.ox, fmaf(rr.oy, rr.oy, rr.oz * rr.oz))) + sc.cmax));
+                        if (n2 > 1e-30f && n2 < 1e30f && c0 >= 0.f) clip0 = c0;
+                    }
+                }
+#endif
+                wd2[r * 32 + lane] = clip0;
+            }
         }
         __syncwarp();
         int qn = 0; // queued pairs of this warp (warp-uniform)

@@ -67,14 +67,17 @@ def test_chunked_bound_table_equals_resident_table():
     f0, u0, s0 = sc.render(w, h, 5)
     with rt.tuned(table_cap=512):
         f1, u1, s1 = sc.render(w, h, 5)
-    with rt.tuned(shadow_anyhit=0):  # every sweep finds the nearest hit: the exact tests are then the same set of pairs
+    # every sweep finds the nearest hit: the exact tests are then nearly the same set of pairs (not exactly: what the distance
+    # clip culls depends on which hits were found first, and chunks are separate launches that start without a clip)
+    with rt.tuned(shadow_anyhit=0):
         f2, u2, s2 = sc.render(w, h, 5)
         with rt.tuned(table_cap=512):
             f3, u3, s3 = sc.render(w, h, 5)
     sc.close()
     assert np.array_equal(f0, f1, equal_nan=True) and (u0 == u1).all()
     assert np.array_equal(f0, f2, equal_nan=True) and np.array_equal(f0, f3, equal_nan=True)
-    assert s0["rays"] == s1["rays"] and s2["exact_tests"] == s3["exact_tests"]
+    assert s0["rays"] == s1["rays"] and s2["rays"] == s3["rays"] and s2["nodes"] == s3["nodes"]
+    assert abs(s2["exact_tests"] - s3["exact_tests"]) <= 0.25 * s2["exact_tests"]
     assert s0["exact_tests"] <= s2["exact_tests"]  # shadow rays that stop at the first occluder test fewer pairs
     assert s1["kernel_launches"] > s0["kernel_launches"]  # the chunks really were separate launches
     of, ou, oc = orc.render(desc.desc, abi.default_camera(w, h), 5)
