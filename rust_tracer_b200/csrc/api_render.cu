@@ -266,6 +266,28 @@ struct Accum {
     bool audit = false;                // RT_FLAG_AUDIT_ALL_PAIRS: every pair went through the exact test
 };
 
+// Device time during which at least one sweep was running: the union of the spans (they overlap when a level's
+// shadow sweep runs beside the next level's tree sweep), each placed on the time line of `origin`.
+static float sweep_union_ms(const Accum &acc, cudaEvent_t origin, std::vector<float> *each = nullptr) {
+    std::vector<std::pair<float, float>> iv;
+    for (const auto &sp : acc.sweep_spans) {
+        float a = 0.f, b = 0.f;
+        if (cudaEventElapsedTime(&a, origin, sp.first) != cudaSuccess || cudaEventElapsedTime(&b, origin, sp.second) != cudaSuccess) {
+            cudaGetLastError();
+            continue;
+        }
+        if (each) each->push_back(b - a);
+        iv.push_back({a, std::max(a, b)});
+    }
+    std::sort(iv.begin(), iv.end());
+    float total = 0.f, end = -1e30f;
+    for (const auto &x : iv) {
+        if (x.first > end) { total += x.second - x.first; end = x.second; }
+        else if (x.second > end) { total += x.second - end; end = x.second; }
+    }
+    return total;
+}
+
 // exact-test count and filter counts of the sweeps, from the device counters read back into
 // ws.h_counters + N_COUNTERS: [0] exact tests, [1] spheres evaluated by the general filter, [2] by the
 // origin filter (bounds, group and quad spheres alike), [3 + g] of those, evaluations of bound slots of
@@ -357,6 +379,15 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
     const int heavy_allow = tuning().heavy_allow;
     // heavy_tree / heavy_nodes: how many of the level's first tree rays / of the previous level's
     // first nodes start far outside the scene (counters[4], [5]); their sweeps get finer work items
+    int aux_dirty = 0; // side streams that carry sweeps not yet joined into the main stream (pipelined levels)
+    auto join_aux = [&]() {
+        for (int i = 0; i < aux_dirty; ++i) {
+            cudaEvent_t done = events.get();
+            cudaEventRecord(done, ws.aux[i]);
+            cudaStreamWaitEvent(st, done, 0);
+        }
+        aux_dirty = 0;
+    };
     auto sweep_level = [&](int level, int tb, int te, int sb, int se, int heavy_tree, int heavy_nodes) {
         if (!by_origin) {
             sweep(tree_seg(tb, te), shadow_seg(sb, se), general);
@@ -373,19 +404,26 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         // previous one's have left, instead of waiting for its last work item.  One timed span
         // per level then; tracing keeps them serial and timed one by one.
         const bool fork = tuning().trace != 1 && ws_aux_streams(ws, 1 + sc.n_point_lights);
+        // Pipelined: nothing but the final shading waits for a level's shadow sweep, so it is not joined here -- it keeps
+        // running on its side stream beside the spawn kernels and the next level's tree sweep (which fill the SMs its last
+        // work items leave idle), and cast_band joins the side streams once, at its end.  The tree sweep stays on the main stream.
+        const bool pipe = fork && !trace && tuning().level_pipeline != 0;
         const int n_aux = ws.n_aux;
         cudaEvent_t e0 = nullptr, e1 = nullptr, forked = nullptr;
         long long rays = 0;
         if (fork) {
-            e0 = events.get(); e1 = events.get(); forked = events.get();
-            cudaEventRecord(e0, st);
+            forked = events.get();
+            if (!pipe) {
+                e0 = events.get(); e1 = events.get();
+                cudaEventRecord(e0, st);
+            }
             cudaEventRecord(forked, st);
             for (int i = 0; i < n_aux; ++i) cudaStreamWaitEvent(ws.aux[i], forked, 0);
         }
         int next_aux = 0;
         auto stream_for = [&]() { return fork ? ws.aux[next_aux++ % n_aux] : st; };
         // tree rays first: measured against shadows first (c4: 51.4 vs 52.0 ms)
-        sweep_on(tree, none, level == 0 ? scene->cam : general, stream_for(), !fork);
+        sweep_on(tree, none, level == 0 ? scene->cam : general, pipe ? st : stream_for(), !fork || pipe);
         rays += tree.n;
         if (se > sb) {
             auto light_seg = [&](int l) {
@@ -401,24 +439,39 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
                 std::vector<RaySeg> segs;
                 for (int l = 0; l < sc.n_point_lights; ++l) segs.push_back(light_seg(l));
                 int used = 0;
+                cudaStream_t on = stream_for();
+                cudaEvent_t j0 = nullptr, j1 = nullptr;
+                if (pipe) { // its own span, on its own stream
+                    j0 = events.get(); j1 = events.get();
+                    cudaEventRecord(j0, on);
+                }
                 cudaError_t e = launch_sweep_jobs(sc, segs.data(), scene->light_tabs.data(), sc.n_point_lights, scene->sm_count,
                                                   ws.batch_counters + ws.batch_next, ws.batch_cap - ws.batch_next, &used,
-                                                  ws.exact_counter, stream_for());
+                                                  ws.exact_counter, on);
                 if (e == cudaSuccess) {
                     merged = true;
                     ws.batch_next += used;
                     scene->launches += 1;
-                    for (const RaySeg &sh : segs) rays += sh.n;
+                    long long shadow_rays = 0;
+                    for (const RaySeg &sh : segs) shadow_rays += sh.n;
+                    rays += shadow_rays;
+                    if (pipe) {
+                        cudaEventRecord(j1, on);
+                        acc.sweep_spans.push_back({j0, j1});
+                        acc.sweep_rays.push_back(shadow_rays);
+                    }
                 } else if (e != cudaErrorNotSupported && sweep_err == cudaSuccess) sweep_err = e;
                 else --next_aux; // nothing was launched on that stream
             }
             for (int l = 0; !merged && l < sc.n_point_lights; ++l) {
                 RaySeg sh = light_seg(l);
-                sweep_on(sh, none, scene->light_tabs[l], stream_for(), !fork);
+                sweep_on(sh, none, scene->light_tabs[l], stream_for(), !fork || pipe);
                 rays += sh.n;
             }
         }
-        if (fork) {
+        if (pipe) {
+            aux_dirty = std::max(aux_dirty, std::min(next_aux, n_aux));
+        } else if (fork) {
             for (int i = 0; i < std::min(next_aux, n_aux); ++i) {
                 cudaEvent_t done = events.get();
                 cudaEventRecord(done, ws.aux[i]);
@@ -450,7 +503,11 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         if (te > tb) scene->launches += by_origin ? 5 : 1;
         CK(cudaMemcpyAsync(ws.h_counters, p.counters, N_COUNTERS * sizeof(unsigned int), cudaMemcpyDeviceToHost, st), "counters readback");
         CK(cudaStreamSynchronize(st), "wavefront level");
-        if (ws.h_counters[3]) return 1; // pool overflow
+        if (ws.h_counters[3]) { // pool overflow: the caller grows the pools and casts the band again
+            join_aux();
+            CK(cudaStreamSynchronize(st), "wavefront level");
+            return 1;
+        }
         lv.tb.push_back(tb); lv.te.push_back(te);
         int new_te = (int)ws.h_counters[0], new_se = (int)ws.h_counters[1];
         lv.sb.push_back(se); lv.se.push_back(new_se);
@@ -463,6 +520,7 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         if (tb == te && sb == se) break; // nothing left to cast
     }
     sweep_level(-1, 0, 0, sb, se, 0, heavy_nodes); // shadows of the last level
+    join_aux(); // shading reads every level's shadow keys
     lv.nodes = ws.h_counters[2];
     CK(sweep_err, "sweep launch");
     CK(cudaGetLastError(), "wavefront launch");
@@ -669,13 +727,13 @@ int render_impl(rt_scene *scene, const rt_camera *cam, const rt_render_params *p
     if (!acc.audit) read_sweep_counters(ws, acc);
     if (stats) {
         fill_stats(scene, acc, (unsigned long long)n_pixels, stats);
-        float ms = 0.f, sweep = 0.f;
+        float ms = 0.f;
         cudaEventElapsedTime(&ms, ev0, ev1);
         const bool trace = tuning().trace != 0;
-        for (size_t i = 0; i < acc.sweep_spans.size(); ++i) {
-            float t = 0.f;
-            cudaEventElapsedTime(&t, acc.sweep_spans[i].first, acc.sweep_spans[i].second);
-            sweep += t;
+        std::vector<float> each;
+        const float sweep = sweep_union_ms(acc, ev0, &each);
+        for (size_t i = 0; i < acc.sweep_spans.size() && i < each.size(); ++i) {
+            const float t = each[i];
             if (trace)
             {
                 double ex = 0, ev = 0;
@@ -798,13 +856,9 @@ int rt_forest_build(rt_scene *scene, const rt_camera *camera, const rt_render_pa
         acc.audit = (pr.flags & RT_FLAG_AUDIT_ALL_PAIRS) != 0;
         if (!acc.audit) read_sweep_counters(ws, acc);
         fill_stats(scene, acc, (unsigned long long)n, stats);
-        float ms = 0.f, sweep = 0.f;
+        float ms = 0.f;
         cudaEventElapsedTime(&ms, ev0, ev1);
-        for (auto &sp : acc.sweep_spans) {
-            float t = 0.f;
-            cudaEventElapsedTime(&t, sp.first, sp.second);
-            sweep += t;
-        }
+        const float sweep = sweep_union_ms(acc, ev0);
         stats->total_ms = ms; stats->sweep_ms = sweep; stats->shade_ms = ms - sweep;
     }
     *out = f;

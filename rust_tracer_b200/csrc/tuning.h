@@ -22,6 +22,7 @@ struct Tuning {
     int item_max = 16;          // sweep: lanes with a touching ray up to which a group is swept pair by pair
     int table_cap = 0;          // sweep: bound slots per shared-memory chunk; 0 = what fits (tests force chunks)
     int merge_lights = 1;       // wavefront: all lights' shadow rays of a level in one launch
+    int level_pipeline = 1;     // wavefront: a level's shadow sweep is not joined before the next level starts (only before shading)
     int job_rotate = 1;         // sweep: in that launch, a CTA whose light has run out of work items goes on with another light's
     int heavy_allow = 65536;    // wavefront: slack on the count of expensive child rays
     int node_bits = 0;          // wavefront: bits per axis of the node order's cells (3..7); 0 = by the size of the level
