@@ -617,6 +617,7 @@ static FrameParams frame_params(const rt_camera *cam, const rt_render_params *pr
     fp.depth = pr->depth; fp.spp = pr->spp; fp.seed = pr->seed;
     fp.rows = d_rows; fp.n_rows = n_rows;
     fp.forest_shading = (pr->flags & RT_FLAG_FOREST_SHADING) ? 1 : 0;
+    fp.primary_tiles = tuning().primary_tiles;
     return fp;
 }
 

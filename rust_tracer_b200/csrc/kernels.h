@@ -104,6 +104,7 @@ struct FrameParams {
     const int *rows; // device: image rows rendered by this call
     int n_rows;
     int forest_shading;
+    int primary_tiles; // primary rays are laid out in tiles of 16 x 8 pixels rather than row by row (wavefront.cu: raygen_kernel)
 };
 
 constexpr int N_COUNTERS = 6;

@@ -48,6 +48,24 @@ __global__ void __launch_bounds__(WF_BLOCK) raygen_kernel(FrameParams fp, Pools 
     long long sidx = sample0 + i;
     long long pix = sidx / fp.spp;
     int s = (int)(sidx - pix * fp.spp);
+    // Tree ray i carries the sample `sidx` of the call (t_parent = t_root = its index in the band).  Row by row, a warp's
+    // 128 consecutive rays are a fan one pixel high and 128 wide; laid out in tiles of 16 x 8 pixels they form a narrow
+    // pyramid that touches about a third as many bound groups.  Chunks of 8 rendered rows that lie wholly inside this band
+    // are walked tile by tile (the last tile of a chunk may be narrower, the last chunk lower); the rest stays row by row.
+    if (fp.primary_tiles) {
+        constexpr int TW = 16, TH = 8;
+        const long long W = fp.x_res, chunk = pix / (W * TH);
+        const long long c0 = chunk * W * TH, c1 = min(c0 + W * TH, (long long)fp.n_rows * W); // pixels of the chunk
+        if (c0 * fp.spp >= sample0 && c1 * fp.spp <= sample0 + n) {
+            const int h = (int)((c1 - c0) / W);             // rows of this chunk
+            const long long k = pix - c0;                   // position in the chunk's tile order
+            const int t = (int)(k / (TW * h));              // tile
+            const int m = (int)(k - (long long)t * TW * h); // position in the tile
+            const int tw = (int)min((long long)TW, W - (long long)t * TW);
+            pix = c0 + (long long)(m / tw) * W + (long long)t * TW + m % tw;
+            sidx = pix * fp.spp + s;
+        }
+    }
     int v = fp.rows[pix / fp.x_res];
     int u = (int)(pix % fp.x_res);
     float x_delta = xdiv(xsub(fp.x_max, fp.x_min), (float)fp.x_res);
@@ -68,8 +86,8 @@ __global__ void __launch_bounds__(WF_BLOCK) raygen_kernel(FrameParams fp, Pools 
     V3 dir = vnorm(vsub(v3(x, y, 0.f), origin));
     p.t_a[i] = make_float4(origin.x, origin.y, origin.z, dir.x);
     p.t_b[i] = make_float4(dir.y, dir.z, 0.f, 0.f);
-    p.t_parent[i] = i;
-    p.t_root[i] = i;
+    p.t_parent[i] = (int)(sidx - sample0);
+    p.t_root[i] = (int)(sidx - sample0);
 }
 
 RT_DEV void load_tree_ray(const Pools &p, int i, V3 &o, V3 &d) {
