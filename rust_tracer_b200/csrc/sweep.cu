@@ -95,6 +95,9 @@ namespace rt {
 #ifndef RT_SWEEP_QCAP
 #define RT_SWEEP_QCAP 256
 #endif
+#ifndef RT_SWEEP_T4
+#define RT_SWEEP_T4 512 // threads per CTA of the 4-rays-per-thread kernels (A/B builds: 576 = 18 warps under 112 registers)
+#endif
 #ifndef RT_SWEEP_T2
 #define RT_SWEEP_T2 512 // threads per CTA of the 2-rays-per-thread kernels (A/B builds: 1024 with RT_SWEEP_QCAP=128)
 #endif
@@ -1282,7 +1285,7 @@ cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const Orig
     if (r >= 8) err = RT_JOBS_T(8, 256);
     else
 #endif
-    if (r >= 4) err = RT_JOBS(4);
+    if (r >= 4) err = RT_JOBS_T(4, RT_SWEEP_T4);
     else if (r >= 2) err = RT_JOBS_T(2, RT_SWEEP_T2);
     else err = RT_JOBS(1);
 #undef RT_JOBS
@@ -1310,23 +1313,23 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
     }
 #endif
     if (ot.bound && ot.shadow && tuning().shadow_anyhit) { // the shadow rays of one light
-        if (r >= 4) return RT_SWEEP(4, 512, true, true);
+        if (r >= 4) return RT_SWEEP(4, RT_SWEEP_T4, true, true);
         if (r >= 2) return RT_SWEEP(2, RT_SWEEP_T2, true, true);
         return RT_SWEEP(1, 512, true, true);
     }
     if (ot.bound) {
-        if (r >= 4) return RT_SWEEP(4, 512, true, false);
+        if (r >= 4) return RT_SWEEP(4, RT_SWEEP_T4, true, false);
         if (r >= 2) return RT_SWEEP(2, RT_SWEEP_T2, true, false);
         return RT_SWEEP(1, 512, true, false);
     }
-    if (r >= 4) return RT_SWEEP(4, 512, false, false); // 16 warps x <= 128 registers; more warps spill the filter loop
+    if (r >= 4) return RT_SWEEP(4, RT_SWEEP_T4, false, false); // 16 warps x <= 128 registers; more warps spill the filter loop
     if (r >= 2) return RT_SWEEP(2, RT_SWEEP_T2, false, false);
     return RT_SWEEP(1, 512, false, false);
 #undef RT_SWEEP
 }
 
 int sweep_table_chunks(const DevScene &sc) {
-    const int cap = sweep_table_cap<4, 512, true>(); // the smallest of the kernels' capacities
+    const int cap = sweep_table_cap<4, RT_SWEEP_T4, true>(); // the smallest of the kernels' capacities
     return std::max(1, (sc.n_slots + cap - 1) / cap);
 }
 
