@@ -106,6 +106,35 @@ RT_DEV unsigned int spread3_dev(unsigned int x) { // <= 10 bits -> every third b
     return x;
 }
 
+#ifndef RT_NODE_HILBERT
+#define RT_NODE_HILBERT 1 // cells inside the box are numbered along a Hilbert curve (no jumps between consecutive cells) rather than in Morton order
+#endif
+// Index of cell (x, y, z), `bits` bits per axis, along the 3-D Hilbert curve (Skilling, "Programming the Hilbert curve", 2004:
+// axes -> transpose, then the bits of the three words interleaved).
+RT_DEV unsigned int hilbert3_dev(unsigned int x, unsigned int y, unsigned int z, int bits) {
+    unsigned int X[3] = {x, y, z};
+    const unsigned int M = 1u << (bits - 1);
+    for (unsigned int Q = M; Q > 1u; Q >>= 1) { // inverse undo
+        const unsigned int P = Q - 1u;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            if (X[i] & Q) X[0] ^= P;
+            else {
+                const unsigned int t = (X[0] ^ X[i]) & P;
+                X[0] ^= t;
+                X[i] ^= t;
+            }
+        }
+    }
+    X[1] ^= X[0]; // Gray encode
+    X[2] ^= X[1];
+    unsigned int t = 0;
+    for (unsigned int Q = M; Q > 1u; Q >>= 1)
+        if (X[2] & Q) t ^= Q - 1u;
+    X[0] ^= t; X[1] ^= t; X[2] ^= t;
+    return (spread3_dev(X[0]) << 2) | (spread3_dev(X[1]) << 1) | spread3_dev(X[2]);
+}
+
 __global__ void __launch_bounds__(256) node_bin_kernel(DevScene sc, Pools p, int begin, int end) {
     int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = i < end;
@@ -130,7 +159,11 @@ __global__ void __launch_bounds__(256) node_bin_kernel(DevScene sc, Pools p, int
         if (inside) {
             const float half = (float)(1 << (bits - 1)), top = 2.f * half - 1.f;
             auto cell = [=](float u) { return (unsigned int)fminf(fmaxf((u + 1.f) * half, 0.f), top); };
+#if RT_NODE_HILBERT
+            bin = NODE_FAR_BINS + hilbert3_dev(cell(ux), cell(uy), cell(uz), bits);
+#else
             bin = NODE_FAR_BINS + (spread3_dev(cell(ux)) | (spread3_dev(cell(uy)) << 1) | (spread3_dev(cell(uz)) << 2));
+#endif
         } else {
             auto cell = [](float u) {
                 float c = u / (1.f + fabsf(u)); // (-1, 1); NaN -> cell 0 below
