@@ -168,7 +168,10 @@ typedef struct rt_stats {
     uint64_t plane_tests;
     uint64_t triangle_tests;
     uint64_t cube_tests;    /* each = 12 triangle tests + one ray transform               */
-    uint64_t exact_tests;   /* pairs that went through the exact (reference-order) test   */
+    uint64_t exact_tests;   /* pairs that went through the exact (reference-order) test.  This and the
+                               evaluation counters below depend on which hits a sweep found first (distance clip,
+                               any-hit shadows) and vary by a fraction of a percent between runs; pixels, rays,
+                               shadow_rays and nodes do not                                  */
     double   algorithmic_flops; /* per SURVEY 8d: 54/sphere, 30/triangle, 47|14/plane, 33+12*30/cube, 60+70L/node */
     float    sweep_ms;      /* device time in the nearest-hit sweeps (CUDA events)        */
     float    shade_ms;      /* device time in ray generation, spawn and shading           */
@@ -228,8 +231,9 @@ int rt_scene_set_stream(rt_scene *scene, void *stream);
  * last of them is destroyed (either order of the two destroy calls is fine).                  */
 void rt_scene_destroy(rt_scene *scene);
 /* Destroyed scenes and forests leave their ray pools (device memory) cached, one set per
- * device, for the next scene; rt_trim frees the cache of `device` (-1: every device, and the
- * host-side tables kept for the last scene description built).                            */
+ * device, for the next scene; rt_trim frees the cache of `device` (-1: every device, the
+ * host-side tables kept for the last scene description built, and the idle worker threads
+ * kept between rt_multi objects).                                                        */
 int rt_trim(int32_t device);
 
 /* ---- Basic renderer ------------------------------------------------------------------ */

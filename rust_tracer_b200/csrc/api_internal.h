@@ -64,6 +64,7 @@ struct HostSlot {
     int kind;   // 0 bound, 1 pad (passes no ray), 2 beyond the filter's range (passes every ray)
 };
 
+void drop_worker_pool(); // api_multi.cu: joins the idle worker threads kept between rt_multi objects
 Workspace workspace_take_cached(int device);
 void workspace_give_cached(int device, Workspace &ws);
 
@@ -104,6 +105,15 @@ struct HostScene {
     mutable float cam_origin[3] = {0.f, 0.f, 0.f};
     mutable std::vector<float4> cam_host;
     mutable OriginTable cam_tab;
+    // Everything upload_scene sends to a device, packed in upload order (api_scene.cu: Arena, 256-byte aligned) so that ONE
+    // copy does it; page-locked on first upload (cudaHostRegister): one DMA per device instead of ~19 staged copies.
+    std::vector<char> blob;
+    mutable std::mutex blob_mu;
+    mutable bool blob_pin_tried = false, blob_pinned = false;
+    HostScene() = default;
+    HostScene(const HostScene &) = delete;
+    HostScene &operator=(const HostScene &) = delete;
+    ~HostScene();
 };
 
 int build_host_scene(const rt_scene_desc *desc, HostScene &hs);

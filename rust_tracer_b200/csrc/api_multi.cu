@@ -94,6 +94,37 @@ class Worker {
     std::thread th_; // last: starts when everything above exists
 };
 
+// Idle workers are kept for the next rt_multi_create: starting and joining 8 threads was ~0.4 ms of the 1.3 ms that the
+// one-shot call on 8 devices spent outside its devices' render (profiles/r02_e2e_laps_multi_device.log).  A worker is
+// not tied to a device (every job selects its own).  rt_trim(-1) joins them.
+namespace {
+std::mutex g_pool_mu;
+std::vector<std::unique_ptr<Worker>> g_pool;
+} // namespace
+
+static std::unique_ptr<Worker> worker_take() {
+    {
+        std::lock_guard<std::mutex> lock(g_pool_mu);
+        if (!g_pool.empty()) {
+            std::unique_ptr<Worker> w = std::move(g_pool.back());
+            g_pool.pop_back();
+            return w;
+        }
+    }
+    return std::unique_ptr<Worker>(new Worker());
+}
+static void worker_give(std::unique_ptr<Worker> w) {
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    if (g_pool.size() < 64) g_pool.push_back(std::move(w)); // (else: joined here, by its destructor)
+}
+void drop_worker_pool() {
+    std::vector<std::unique_ptr<Worker>> drop;
+    {
+        std::lock_guard<std::mutex> lock(g_pool_mu);
+        drop.swap(g_pool);
+    }
+}
+
 } // namespace rt
 
 using namespace rt;
@@ -187,7 +218,7 @@ int rt_multi_create(const rt_scene_desc *desc, const int32_t *devices, int32_t n
         m->devices.assign(devices, devices + n_devices);
         m->scenes.assign(n_devices, nullptr);
         m->peer_ok.assign(n_devices, 0);
-        for (int i = 0; i < n_devices; ++i) m->workers.emplace_back(new Worker());
+        for (int i = 0; i < n_devices; ++i) m->workers.push_back(worker_take());
     } catch (...) {
         delete m;
         return fail(RT_ERR_NOMEM, "out of host memory or threads");
@@ -231,6 +262,8 @@ void rt_multi_destroy(rt_multi *m) {
                 return (int)RT_OK;
             });
         for (auto &w : m->workers) w->wait(nullptr);
+        for (auto &w : m->workers) worker_give(std::move(w)); // idle now: kept for the next rt_multi_create
+        m->workers.clear();
     }
     delete m;
 }

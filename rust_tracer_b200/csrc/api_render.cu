@@ -881,7 +881,10 @@ void rt_forest_destroy(rt_forest *forest) {
 }
 
 int rt_trim(int32_t device) {
-    if (device < 0) drop_scene_cache();
+    if (device < 0) {
+        drop_scene_cache();
+        drop_worker_pool();
+    }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");

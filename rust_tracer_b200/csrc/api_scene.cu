@@ -344,15 +344,36 @@ struct Arena {
         }
         void *d = ws.tables;
         cudaError_t e;
-        for (const Item &it : items) {
-            *it.dev = (const char *)d + it.off;
-            if (!it.src) continue;
-            e = cudaMemcpyAsync((char *)d + it.off, it.src, it.bytes, cudaMemcpyHostToDevice, st);
-            if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(scene table)");
+        const size_t packed = blob ? packed_bytes() : 0;
+        if (blob && packed > 0 && blob->size() == packed) { // the items' bytes lie in `blob` at the same offsets: one copy
+            for (const Item &it : items) *it.dev = (const char *)d + it.off;
+            e = cudaMemcpyAsync(d, blob->data(), packed, cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(scene tables)");
+        } else {
+            for (const Item &it : items) {
+                *it.dev = (const char *)d + it.off;
+                if (!it.src) continue;
+                e = cudaMemcpyAsync((char *)d + it.off, it.src, it.bytes, cudaMemcpyHostToDevice, st);
+                if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(scene table)");
+            }
         }
         if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return cuda_fail(e, "scene table upload");
         return RT_OK;
     }
+    // bytes up to the end of the last item that has a source (space-only items come last)
+    size_t packed_bytes() const {
+        size_t end = 0;
+        for (const Item &it : items)
+            if (it.src) end = std::max(end, it.off + it.bytes);
+        return end;
+    }
+    // the items' bytes at their offsets, for HostScene::blob
+    void pack(std::vector<char> &out) const {
+        out.assign(packed_bytes(), 0);
+        for (const Item &it : items)
+            if (it.src) std::memcpy(out.data() + it.off, it.src, it.bytes);
+    }
+    const std::vector<char> *blob = nullptr;
 };
 
 static int convert_colorfn(const rt_colorfn &in, DevColorFn &out) {
@@ -413,6 +434,9 @@ static void cube_tris(std::vector<float4> &out) {
 }
 
 // ---- scene build (host only) -----------------------------------------------------------------
+
+static void add_tables(const HostScene &hs, Arena &arena, DevScene &d, const DevMaterial **dm, std::vector<OriginTable> &light_tabs,
+                       const float4 **cam_tab);
 
 int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
     const bool trace = tuning().trace != 0; // phase times of the host-side build
@@ -721,6 +745,20 @@ int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
         }
     }
     lap("light tables");
+    { // the same tables once more, packed the way upload_scene lays them out on a device (HostScene::blob)
+        Arena arena;
+        DevScene dd = hs.dev;
+        const DevMaterial *dm = nullptr;
+        const float4 *cam = nullptr;
+        std::vector<OriginTable> lt = hs.light_tabs;
+        add_tables(hs, arena, dd, &dm, lt, &cam);
+        try {
+            arena.pack(hs.blob);
+        } catch (...) {
+            hs.blob.clear(); // no memory for the copy: upload_scene sends the tables one by one
+        }
+    }
+    lap("upload blob");
     return RT_OK;
 }
 
@@ -800,6 +838,28 @@ int host_scene_for(const rt_scene_desc *desc, std::shared_ptr<const HostScene> *
 
 // ---- scene upload (one device) ------------------------------------------------------------------
 
+// The tables of a scene in upload order; `light_tabs` (a copy of hs.light_tabs) and *cam_tab receive their device addresses.
+static void add_tables(const HostScene &hs, Arena &arena, DevScene &d, const DevMaterial **dm, std::vector<OriginTable> &light_tabs,
+                       const float4 **cam_tab) {
+    arena.add(hs.bound, &d.bound); arena.add(hs.group, &d.group); arena.add(hs.quad, &d.quad); arena.add(hs.super, &d.super);
+    arena.add(hs.bound_shape, &d.bound_shape); arena.add(hs.slot_meta, &d.slot_meta); arena.add(hs.slot_geom, &d.slot_geom);
+    arena.add(hs.meta, &d.shape_meta); arena.add(hs.geom, &d.geom);
+    arena.add(hs.plane_shape, &d.plane_shape); arena.add(hs.plane_data, &d.plane_data);
+    arena.add(hs.cube_tris, &d.cube_tris); arena.add(hs.materials, dm); arena.add(hs.lights, &d.lights);
+    if (hs.origin) {
+        const int n = hs.dev.n_slots;
+        for (size_t l = 0; l < light_tabs.size(); ++l) arena.add(hs.light_host[l], &light_tabs[l].bound);
+        arena.add_raw(nullptr, (size_t)(n + n / GROUP_SLOTS + n / QUAD_SLOTS + n / SUPER_SLOTS) * sizeof(float4), (const void **)cam_tab); // space only, last
+    }
+}
+
+HostScene::~HostScene() {
+    if (blob_pinned) {
+        cudaHostUnregister((void *)blob.data());
+        cudaGetLastError(); // (at process exit the runtime may be gone already)
+    }
+}
+
 void scene_free(rt_scene *scene) {
     if (!scene) return;
     cudaSetDevice(scene->device);
@@ -826,17 +886,18 @@ int upload_scene(const std::shared_ptr<const HostScene> &host, int device, rt_sc
     cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
     const DevMaterial *dm = nullptr;
     Arena arena;
-    arena.add(hs.bound, &d.bound); arena.add(hs.group, &d.group); arena.add(hs.quad, &d.quad); arena.add(hs.super, &d.super);
-    arena.add(hs.bound_shape, &d.bound_shape); arena.add(hs.slot_meta, &d.slot_meta); arena.add(hs.slot_geom, &d.slot_geom);
-    arena.add(hs.meta, &d.shape_meta); arena.add(hs.geom, &d.geom);
-    arena.add(hs.plane_shape, &d.plane_shape); arena.add(hs.plane_data, &d.plane_data);
-    arena.add(hs.cube_tris, &d.cube_tris); arena.add(hs.materials, &dm); arena.add(hs.lights, &d.lights);
     const float4 *cam_tab = nullptr;
     const int n_groups = d.n_slots / GROUP_SLOTS, n_quads = d.n_slots / QUAD_SLOTS, n_supers = d.n_slots / SUPER_SLOTS;
-    if (hs.origin) {
-        s->light_tabs = hs.light_tabs;
-        for (size_t l = 0; l < s->light_tabs.size(); ++l) arena.add(hs.light_host[l], &s->light_tabs[l].bound);
-        arena.add_raw(nullptr, (size_t)(d.n_slots + n_groups + n_quads + n_supers) * sizeof(float4), (const void **)&cam_tab);
+    s->light_tabs = hs.light_tabs;
+    add_tables(hs, arena, d, &dm, s->light_tabs, &cam_tab);
+    if (!hs.blob.empty()) { // page-lock the packed tables once; without it the copy is staged like any pageable one
+        std::lock_guard<std::mutex> lock(hs.blob_mu);
+        if (!hs.blob_pin_tried) {
+            hs.blob_pin_tried = true;
+            if (cudaHostRegister((void *)hs.blob.data(), hs.blob.size(), cudaHostRegisterPortable) == cudaSuccess) hs.blob_pinned = true;
+            else cudaGetLastError();
+        }
+        arena.blob = &hs.blob;
     }
     s->ws = workspace_take_cached(device);
     if (!s->ws.stream && (e = cudaStreamCreateWithFlags(&s->ws.stream, cudaStreamNonBlocking)) != cudaSuccess) {
