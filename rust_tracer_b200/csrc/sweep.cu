@@ -278,7 +278,7 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
                                         int cnt, int all, ExactCount *n_exact, float *wd2, unsigned int *wocc) {
     const int lane = threadIdx.x & 31;
     int done = 0;
-    unsigned int n_sphere = 0, n_triangle = 0;
+    unsigned int n_sphere = 0, n_triangle = 0, n_run = 0;
 #if RT_SWEEP_FLUSH_PIPE
     PairOperands next;
     bool have_next = (cnt >= 32 || (all && cnt > 0)) && lane < cnt;
@@ -298,7 +298,14 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
         }
         if (have) {
 #else
-        if (idx < cnt) {
+        bool run = idx < cnt;
+        if constexpr (SHADOW) { // a ray an earlier round of this flush (or an earlier flush) found occluded needs no more tests
+            if (run) {
+                const unsigned int local = wqueue[idx] >> 24;
+                run = ((wocc[local >> 5] >> (local & 31)) & 1u) == 0u;
+            }
+        }
+        if (run) {
             const PairOperands cur = fetch_pair(ctx, wqueue, idx, ray0);
 #endif
             const float4 g[3] = {cur.g0, cur.g1, cur.g2};
@@ -326,10 +333,11 @@ __device__ __noinline__ int sweep_flush(const SweepCtx *ctx, unsigned int *wqueu
         (void)idx;
         n_sphere += __popc(__ballot_sync(0xffffffffu, kind == KIND_SPHERE));
         n_triangle += __popc(__ballot_sync(0xffffffffu, kind == KIND_TRIANGLE));
+        n_run += __popc(__ballot_sync(0xffffffffu, kind >= 0)); // pairs tested (queued pairs of occluded rays are dropped untested)
         done += 32;
     }
     if (lane == 0) {
-        n_exact->all += (unsigned int)min(done, cnt);
+        n_exact->all += n_run;
         n_exact->sphere += n_sphere;
         n_exact->triangle += n_triangle;
     }
