@@ -1310,7 +1310,10 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
     if (total <= 0) return cudaSuccess;
     if (ot.bound && s1.n > 0) return cudaErrorInvalidValue;
     if (sm_count < 1) sm_count = 1;
-    const int r = pick_rays_per_thread(total, sc.n_slots, sm_count);
+    int r = pick_rays_per_thread(total, sc.n_slots, sm_count);
+    // sweeps with the general filter (reflected / refracted rays, far less coherent than primary or shadow rays): batches of
+    // 64 rays make narrower beams (and a small sweep needs half the table slices to occupy the warps)
+    if (!ot.bound && tuning().rays_per_thread == 0 && total < (long long)tuning().small_tree_rays) r = std::min(r, std::max(1, tuning().tree_rays_per_thread));
 #define RT_SWEEP(R_, T_, O_, S_) \
     launch_sweep_r<R_, T_, O_, S_>(sc, s0, s1, ot, total, sm_count, batch_counters, n_counters, used, exact_counter, stream)
 #if RT_SWEEP_R8
