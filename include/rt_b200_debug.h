@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-/* name: a field of rt::Tuning ("rays_per_thread", "small_tree_rays", "tree_rays_per_thread", "want_light", "want_heavy", "want_heavy_jobs", "tail_min", "slices",
+/* name: a field of rt::Tuning ("rays_per_thread", "small_tree_rays", "tree_rays_per_thread", "small_shadow_rays", "want_light", "want_heavy", "want_heavy_jobs", "tail_min", "slices",
  * "tail_pct", "tail_mult", "item_max", "table_cap", "merge_lights", "job_rotate", "level_pipeline", "primary_tiles", "heavy_allow", "node_bits",
  * "band_samples", "origin_tables", "origin_min_slots", "host_threads", "scene_cache", "shadow_anyhit",
  * "trace").  Process-wide; takes effect at the next call (scene knobs: at the next

@@ -1034,6 +1034,7 @@ const Knob KNOBS[] = {
     {"shadow_anyhit", &Tuning::shadow_anyhit, 0, 1},       {"trace", &Tuning::trace, 0, 2},
     {"scene_cache", &Tuning::scene_cache, 0, 1},         {"job_rotate", &Tuning::job_rotate, 0, 1},
     {"small_tree_rays", &Tuning::small_tree_rays, 0, 1 << 30}, {"tree_rays_per_thread", &Tuning::tree_rays_per_thread, 1, 4},
+    {"small_shadow_rays", &Tuning::small_shadow_rays, 0, 1 << 30},
     {"level_pipeline", &Tuning::level_pipeline, 0, 1},     {"primary_tiles", &Tuning::primary_tiles, 0, 1},
 };
 } // namespace

@@ -1282,7 +1282,8 @@ cudaError_t launch_sweep_jobs(const DevScene &sc, const RaySeg *segs, const Orig
         if (!tabs[j].bound || segs[j].n <= 0 || !segs[j].preset) return cudaErrorNotSupported;
         most = std::max<long long>(most, segs[j].n);
     }
-    const int r = pick_rays_per_thread(most, sc.n_slots, std::max(1, sm_count / n_jobs));
+    int r = pick_rays_per_thread(most, sc.n_slots, std::max(1, sm_count / n_jobs));
+    if (tuning().rays_per_thread == 0 && most < (long long)tuning().small_shadow_rays) r = std::min(r, 2); // (A/B knob; measured: no gain)
     const bool anyhit = tuning().shadow_anyhit != 0;
     cudaError_t err;
 #define RT_JOBS_T(R_, T_) \

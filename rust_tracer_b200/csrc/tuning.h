@@ -13,6 +13,7 @@ namespace rt {
 struct Tuning {
     int rays_per_thread = 0;    // sweep: rays per thread (1, 2, 4); 0 = by the number of rays
     int small_tree_rays = 1 << 30; // sweep: general-filter sweeps of fewer rays than this run ...
+    int small_shadow_rays = 0;     // sweep: a level's shadow launch with fewer rays per light than this runs 2 rays per thread (0: never)
     int tree_rays_per_thread = 2;  // ... this many rays per thread instead of 4
     int want_light = 4;         // sweep: work items per warp aimed at for ordinary batches ...
     int want_heavy = 4;         // ... and for the expensive first batches of a launch (rays that start far outside the scene)
