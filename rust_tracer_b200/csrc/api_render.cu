@@ -388,6 +388,12 @@ static int cast_band(rt_scene *scene, Workspace &ws, const FrameParams &fp, long
         }
         aux_dirty = 0;
     };
+    // whatever way this function is left (a CK() of a failed call included), no sweep stays behind on a side stream:
+    // the caller may grow or release the pools next
+    struct JoinOnExit {
+        decltype(join_aux) &join;
+        ~JoinOnExit() { join(); }
+    } join_on_exit{join_aux};
     auto sweep_level = [&](int level, int tb, int te, int sb, int se, int heavy_tree, int heavy_nodes) {
         if (!by_origin) {
             sweep(tree_seg(tb, te), shadow_seg(sb, se), general);
