@@ -225,7 +225,9 @@ int rt_scene_create(const rt_scene_desc *desc, int32_t device, rt_scene **out);
 int rt_scene_update_materials(rt_scene *scene, const rt_material *materials, int32_t n);
 /* Launch this scene's kernels and copies on `stream` (a cudaStream_t created by the caller
  * on the scene's device, e.g. a torch stream's handle) so that the caller's own events
- * bracket the work; NULL restores the scene's private stream.  Calls stay synchronous.   */
+ * bracket the work (a level's shadow sweeps run on side streams of the library, forked from
+ * and joined back into `stream` by events inside the call); NULL restores the scene's private
+ * stream.  Calls stay synchronous.                                                       */
 int rt_scene_set_stream(rt_scene *scene, void *stream);
 /* Forests built from the scene keep using its tables: if any is alive, the scene is freed when the
  * last of them is destroyed (either order of the two destroy calls is fine).                  */

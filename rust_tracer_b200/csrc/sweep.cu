@@ -4,18 +4,21 @@
 // src/render.rs:47 and, once per light, src/scene/mod.rs:193).  Every (ray, shape) pair is
 // resolved, most of them wholesale:
 //   phase 1  FILTER   one persistent CTA per SM keeps the bounding-sphere table of the shapes
-//                     (slots), of every 16 slots (groups) and of every 64 (quads) in shared
-//                     memory; each warp fetches batches of 32 R rays, each thread keeps the
-//                     filter coefficients of R rays in registers and tests them against two
-//                     spheres at a time with packed FFMA2 (fma.rn.f32x2): quads first, then the
-//                     groups of a quad some ray of the warp may touch, then the slots of such a
-//                     group -- all 32 R rays against each slot pair (brute loop), or, when few
-//                     lanes hold a touching ray, one (ray, group) pair per half warp with
-//                     lane = slot (pair path).  7 FMA per (ray, sphere) decide "this ray
+//                     (slots), of every 16 slots (groups), every 64 (quads) and every 256 (supers) in
+//                     shared memory; each warp fetches batches of 32 R rays (R = 4; 2 for reflected /
+//                     refracted rays), each thread keeps the filter coefficients of R rays in registers
+//                     and tests them against two spheres at a time with packed FFMA2 (fma.rn.f32x2):
+//                     supers first, then the quads of a super some ray of the warp may touch, its
+//                     groups, then the slots of such a group -- all 32 R rays against each slot pair
+//                     (brute loop), or, when few lanes hold a touching ray, one (ray, group) pair per
+//                     half warp with lane = slot (pair path).  7 FMA per (ray, sphere) decide "this ray
 //                     certainly misses everything in this sphere"; 4 FMA for rays that share a
 //                     point (origin tables, below).  The tests are conservative: their margins
 //                     cover both their own rounding and the reference's ("filter
 //                     margins"), so they only ever reject pairs the exact test would reject too.
+//                     Shadow rays leave the sweep at their first occluding hit (any-hit); nearest-hit
+//                     rays skip the spheres of the hierarchy that lie wholly beyond their best hit so
+//                     far (distance clip).
 //   phase 2  EXACT    surviving (ray, slot) pairs go to a per-warp queue in shared memory;
 //                     whenever 32 are waiting the warp runs 32 exact tests, one per lane,
 //                     with the reference's own operand order (exact.cuh), and folds the
@@ -37,9 +40,9 @@
 //
 // Scheduling (host side, plan_items / launch_sweep / launch_sweep_jobs): a launch's rays are cut
 // into work items = (batch of 32 R rays) x (slice of the resident table) handed out by an atomic
-// counter -- finer for the first, expensive batches and for the last 15 % of the launch -- and the
-// shadow rays of all lights of a wavefront level go into ONE launch whose CTAs each serve one
-// light's rays and origin table (JOBS).
+// counter, slice by slice -- finer for the first, expensive batches and for the last 8 % of the launch -- and the
+// shadow rays of all lights of a wavefront level go into ONE launch whose CTAs start on one light's rays and
+// origin table each and move on to another light's when theirs run out (JOBS).
 #include <algorithm>
 #include <atomic>
 #include <cfloat>
@@ -454,8 +457,8 @@ RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, cons
 RT_DEV float2 f2(float x) { return make_float2(x, x); }
 
 // One persistent CTA per SM; slots [slot_begin, slot_end) of the bound table stay in shared
-// memory for the whole launch (staged by three bulk copies, cp.async.bulk + mbarrier, which run
-// while the warps fetch their first work item and load its rays).  A work item is (batch of
+// memory for the whole launch (copied by the CTA's threads behind one block barrier; RT_SWEEP_BULK_TABLE
+// selects cp.async.bulk + mbarrier instead, measured slower).  A work item is (batch of
 // 32 R rays) x (slice of the resident slots); each WARP fetches its own items from
 // batch_counter, so no block barrier follows the table load, and small launches still spread
 // over every warp of the GPU (n_slices > 1).
@@ -1154,7 +1157,7 @@ static ItemPlan plan_items(long long total, int heavy, int per, long long warps,
         if (pl.heavy_slices < pl.n_slices) { pl.heavy_slices = pl.n_slices; pl.heavy_slice_slots = pl.slice_slots; }
     }
     // A warp's last item ends, on average, half an item before the launch does.  The last
-    // tail_pct % of the batches (at most 2 per warp) are therefore cut tail_mult times finer (measured: 15 %, 4 x).
+    // tail_pct % of the batches (at most 2 per warp) are therefore cut tail_mult times finer (measured: tuning.h).
     const long long regular = batches - pl.heavy_batches;
     const int tail_pct = tn.tail_pct, tail_mult = tn.tail_mult;
     long long tail_batches = std::min<long long>(regular * tail_pct / 100, 2 * warps);
