@@ -305,7 +305,8 @@ def test_merged_light_sweeps_and_tail_items_do_not_change_the_image():
     (tail_pct, tail_mult): scheduling only -- the same image and counts,
     and the same as the all-pairs audit.  Also at fewer rays per thread, where the jobs kernel is
     another instantiation; with and without CTAs moving on to another light's items when theirs run out
-    (job_rotate)."""
+    (job_rotate); levels pipelined or joined one by one (level_pipeline); primary rays in tiles or row by row
+    (primary_tiles); reflected / refracted rays at 1, 2 or 4 per thread."""
     desc = rt.SceneDesc.synthetic(500, 500, 77, 0.03, 0.1)
     w, h, depth = 224, 126, 4
     ref = None
@@ -313,7 +314,10 @@ def test_merged_light_sweeps_and_tail_items_do_not_change_the_image():
                   {"tail_pct": 50, "tail_mult": 64}, {"rays_per_thread": 1},
                   {"rays_per_thread": 2, "want_light": 16}, {"shadow_anyhit": 0}, {"shadow_anyhit": 0, "merge_lights": 0},
                   {"merge_lights": 0, "rays_per_thread": 2}, {"merge_lights": 0, "table_cap": 512},
-                  {"job_rotate": 0}, {"job_rotate": 0, "rays_per_thread": 1}, {"job_rotate": 1, "want_heavy_jobs": 64}):
+                  {"job_rotate": 0}, {"job_rotate": 0, "rays_per_thread": 1}, {"job_rotate": 1, "want_heavy_jobs": 64},
+                  {"level_pipeline": 0}, {"level_pipeline": 0, "merge_lights": 0}, {"level_pipeline": 1, "merge_lights": 0},
+                  {"primary_tiles": 0}, {"tree_rays_per_thread": 4}, {"tree_rays_per_thread": 1, "want_light": 16},
+                  {"small_shadow_rays": 1 << 30}, {"small_tree_rays": 0}):
         with rt.tuned(**knobs):
             sc = rt.Scene(desc)
             try:
