@@ -687,6 +687,16 @@ int build_host_scene(const rt_scene_desc *desc, HostScene &hs) {
     d.n_shapes = n; d.n_bounded = nb; d.n_planes = (int)plane_shape.size();
     d.n_slots = n_slots; d.segs = segs; d.cmax = round_up_f32(cmax * (1.0 + 1e-6));
     { // largest sphere of each level of the hierarchy, for the sweeps' distance clip (origin tables move a centre by its f32 rounding only)
+        {
+            double r = 0.0;
+            bool all_pass = false;
+            for (const Bound &b : slots) {
+                if (b.w == -3.402823466e+38f) all_pass = true;
+                else if (b.w != 3.402823466e+38f) r = std::max(r, b.rf);
+            }
+            r = r * (1.0 + 1e-5) + 1e-5 * cmax;
+            d.slot_rmax = (all_pass || !(r < 1e15)) ? 3.0e38f : round_up_f32(r);
+        }
         const std::vector<Bound> *levels[3] = {&groups, &quads, &supers};
         for (int l = 0; l < 3; ++l) {
             double r = 0.0;
@@ -1035,7 +1045,7 @@ const Knob KNOBS[] = {
     {"scene_cache", &Tuning::scene_cache, 0, 1},         {"job_rotate", &Tuning::job_rotate, 0, 1},
     {"small_tree_rays", &Tuning::small_tree_rays, 0, 1 << 30}, {"tree_rays_per_thread", &Tuning::tree_rays_per_thread, 1, 4},
     {"small_shadow_rays", &Tuning::small_shadow_rays, 0, 1 << 30},
-    {"level_pipeline", &Tuning::level_pipeline, 0, 1},     {"primary_tiles", &Tuning::primary_tiles, 0, 1},
+    {"level_pipeline", &Tuning::level_pipeline, 0, 1},     {"primary_tiles", &Tuning::primary_tiles, 0, 2},
 };
 } // namespace
 

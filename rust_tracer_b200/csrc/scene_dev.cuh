@@ -103,6 +103,7 @@ struct DevScene {
     int n_bounded;  // bounded shapes (without pads)
     int n_slots;    // bound slots including pads (multiple of SEG_PAD)
     float cmax;     // max over bounds of |C| + R, rounded up
+    float slot_rmax;     // largest radius of a bound slot, rounded up (3e38: one passes every ray)
     float level_rmax[3]; // largest radius of a group / quad / super sphere, rounded up (3e38: one of them passes every ray): sweep.cu, distance clip
     SweepSegs segs;
     SweepSegs runs; // segs merged where k and kx agree

@@ -88,6 +88,9 @@ namespace rt {
 #define RT_SWEEP_SKIP_OCCLUDED 0 // 1: the exact stage drops queued pairs of shadow rays already found occluded.  Measured: 3 % fewer exact tests,
                                   // 0.1 ms slower per c4 frame (the check sits on the flush's critical path): profiles/r02_ab_skip_occluded_pairs_c4.log
 #endif
+#ifndef RT_SWEEP_PRIMARY_TF
+#define RT_SWEEP_PRIMARY_TF 0 // 1: primary rays also clip bound slots (not only the hierarchy) beyond their best hit (A/B builds)
+#endif
 #ifndef RT_SWEEP_R8
 #define RT_SWEEP_R8 0 // 1: also build 8 rays per thread x 256 threads (rays_per_thread=8; A/B builds)
 #endif
@@ -799,6 +802,16 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
                     }
                 alive = __any_sync(FULL, vmask != 0u);
             }
+#if RT_SWEEP_PRIMARY_TF
+            if constexpr (!SHADOW && ORIGIN) { // primary rays: the far clip of the slot tests follows the best hit (e = b^2 + mu, b from the camera)
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const float lim = wd2[r * 32 + lane] + sc.slot_rmax;
+                    const float t = fmaf(lim, lim, c[r].mu) * 1.0001f;
+                    if (t < c[r].tf) c[r].tf = t; // (false for NaN; no hit yet: lim = 3e38, t = inf)
+                }
+            }
+#endif
         };
         if (!table_ready) { // first use of the table by this warp: the copies ran while it fetched and loaded its rays
             mbar_wait(&tab_bar, 0);

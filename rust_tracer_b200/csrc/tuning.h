@@ -25,7 +25,8 @@ struct Tuning {
     int item_max = 16;          // sweep: lanes with a touching ray up to which a group is swept pair by pair
     int table_cap = 0;          // sweep: bound slots per shared-memory chunk; 0 = what fits (tests force chunks)
     int merge_lights = 1;       // wavefront: all lights' shadow rays of a level in one launch
-    int primary_tiles = 1;      // wavefront: primary rays in tiles of 16 x 8 pixels (a warp's 128 rays form a narrow pyramid, not a one-pixel-high fan)
+    int primary_tiles = 2;      // wavefront: primary rays in tiles of 16 x 8 pixels (a warp's 128 rays form a narrow pyramid, not a one-pixel-high
+                                // fan); 2: at 4 samples per pixel the tiles are 8 x 4 pixels (again one batch); 1: 16 x 8 always; 0: row by row
     int level_pipeline = 1;     // wavefront: a level's shadow sweep is not joined before the next level starts (only before shading)
     int job_rotate = 1;         // sweep: in that launch, a CTA whose light has run out of work items goes on with another light's
     int heavy_allow = 65536;    // wavefront: slack on the count of expensive child rays

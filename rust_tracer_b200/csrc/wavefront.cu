@@ -53,7 +53,8 @@ __global__ void __launch_bounds__(WF_BLOCK) raygen_kernel(FrameParams fp, Pools 
     // pyramid that touches about a third as many bound groups.  Chunks of 8 rendered rows that lie wholly inside this band
     // are walked tile by tile (the last tile of a chunk may be narrower, the last chunk lower); the rest stays row by row.
     if (fp.primary_tiles) {
-        constexpr int TW = 16, TH = 8;
+        // 16 x 8 pixels = one batch of 128 rays; at 4 samples per pixel (primary_tiles = 2) 8 x 4 pixels are one batch
+        const int TW = (fp.primary_tiles == 2 && fp.spp == 4) ? 8 : 16, TH = (fp.primary_tiles == 2 && fp.spp == 4) ? 4 : 8;
         const long long W = fp.x_res, chunk = pix / (W * TH);
         const long long c0 = chunk * W * TH, c1 = min(c0 + W * TH, (long long)fp.n_rows * W); // pixels of the chunk
         if (c0 * fp.spp >= sample0 && c1 * fp.spp <= sample0 + n) {
@@ -290,7 +291,10 @@ __global__ void __launch_bounds__(256) node_scatter_kernel(Pools p, int begin, i
 // rays.  With the nodes in cell order (node_*_kernel) a run of up to SPAWN_BLOCK consecutive tree
 // rays of the next level then starts at neighbouring points AND leaves the same way -- away from
 // the surface or into it -- which is what the sweep's group culling feeds on.
-constexpr int SPAWN_BLOCK = 512;
+#ifndef RT_SPAWN_BLOCK
+#define RT_SPAWN_BLOCK 512 // threads per block of the spawn kernel (A/B builds)
+#endif
+constexpr int SPAWN_BLOCK = RT_SPAWN_BLOCK;
 
 __global__ void RT_SPAWN_BOUNDS
 spawn_kernel(DevScene sc, FrameParams fp, Pools p, int begin, int end, int spawn_children, int ordered, int s_begin) {

@@ -316,7 +316,7 @@ def test_merged_light_sweeps_and_tail_items_do_not_change_the_image():
                   {"merge_lights": 0, "rays_per_thread": 2}, {"merge_lights": 0, "table_cap": 512},
                   {"job_rotate": 0}, {"job_rotate": 0, "rays_per_thread": 1}, {"job_rotate": 1, "want_heavy_jobs": 64},
                   {"level_pipeline": 0}, {"level_pipeline": 0, "merge_lights": 0}, {"level_pipeline": 1, "merge_lights": 0},
-                  {"primary_tiles": 0}, {"tree_rays_per_thread": 4}, {"tree_rays_per_thread": 1, "want_light": 16},
+                  {"primary_tiles": 0}, {"primary_tiles": 1}, {"tree_rays_per_thread": 4}, {"tree_rays_per_thread": 1, "want_light": 16},
                   {"small_shadow_rays": 1 << 30}, {"small_tree_rays": 0}):
         with rt.tuned(**knobs):
             sc = rt.Scene(desc)
