@@ -306,6 +306,14 @@ impl Forest {
         Ok(n)
     }
 
+    /// `trees_with` through the entry point that allocates nothing (static device scratch; forests of
+    /// at most `RT_STATIC_TREES_MAX` = 4 Mi trees; calls on one GPU must not overlap).  Not in the reference.
+    pub fn trees_with_static(&self, shape_id: i32) -> Result<u64> {
+        let mut n = 0u64;
+        check(unsafe { sys::rt_forest_trees_with_static(self.handle, shape_id, &mut n) })?;
+        Ok(n)
+    }
+
     /// `RayForest::stats` (src/render_tree.rs:73-105).
     pub fn stats(&self) -> Result<rt_forest_stats> {
         let mut st = rt_forest_stats::default();
