@@ -164,6 +164,22 @@ def test_library_does_not_read_the_environment():
     assert L.rt_debug_get(b"want_light") == 4
 
 
+def test_debug_knobs_named_in_the_header_are_the_fields_of_tuning_h():
+    """include/rt_b200_debug.h lists the knobs by name; each is a field of rt::Tuning (csrc/tuning.h) with the
+    default the library reports, and the library knows no field the header does not name."""
+    import os, re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "rt_b200_debug.h")).read()
+    listed = re.findall(r'"([a-z_0-9]+)"', header[header.index("name: a field of rt::Tuning"):header.index("Process-wide")])
+    tuning = open(os.path.join(root, "rust_tracer_b200", "csrc", "tuning.h")).read()
+    fields = dict(re.findall(r"^\s+int (\w+) = ([^;]+);", tuning, flags=re.M))
+    assert sorted(listed) == sorted(fields), (sorted(set(listed) ^ set(fields)))
+    L = rt.lib()
+    L.rt_debug_reset()
+    for name, default in fields.items():
+        assert L.rt_debug_get(name.encode()) == eval(default), name  # ("1 << 23" and the like)
+
+
 def test_package_does_not_import_the_oracle():
     import subprocess, sys
     code = ("import sys; sys.path.insert(0, %r); import rust_tracer_b200 as rt; rt.lib(); "
