@@ -30,6 +30,15 @@ int64_t rt_debug_get(const char *name);
 /* Back to the compile-time defaults. */
 void rt_debug_reset(void);
 
+/* Host-side logic of the sweep's scheduling, callable without a GPU (tests/test_sweep_plan_cpu.py): the plan of work items for
+ * `total` rays (`heavy` of them expensive) against a resident table of `per` slots on `warps` persistent warps --
+ * out = {items, heavy_batches, heavy_slices, heavy_slice_slots, reg_batches, n_slices, slice_slots, tail_slices,
+ * tail_slice_slots, merge} -- and the (batch, slice, slots per slice) an item number decodes to in the kernel
+ * (returns 1, or 0 past the plan).  -1: bad argument.                                                              */
+int rt_debug_plan_items(int32_t rays_per_thread, int64_t total, int32_t heavy, int32_t per, int64_t warps, int32_t n_chunks,
+                        int32_t jobs, int64_t out[10]);
+int rt_debug_decode_item(uint32_t item, int64_t total, int32_t batch_rays, const int64_t plan[10], int64_t out[3]);
+
 #ifdef __cplusplus
 }
 #endif

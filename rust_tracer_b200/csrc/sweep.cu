@@ -459,6 +459,60 @@ RT_DEV RayCoefO ray_coef_origin(const RayRegs &r, float kx_seg, float cmax, cons
 
 RT_DEV float2 f2(float x) { return make_float2(x, x); }
 
+// Work item number -> (ray batch, table slice, slots per slice).  Items come in three runs -- the batches of the first `heavy`
+// rays (heavy_slices slices each), the bulk (reg_batches batches, n_slices each) and the last batches of the launch
+// (tail_slices each) -- and within a run slice-major (item = slice * batches + batch; RT_SWEEP_SLICE_MAJOR) or batch-major.
+// False past the last item of the plan.  Host and device: tests/test_sweep_plan_cpu.py walks every item of a plan through it.
+__host__ __device__ inline bool decode_item(unsigned int item, long long total, int batch_rays, int heavy_batches, int heavy_slices,
+                                            int heavy_slice_slots, int reg_batches, int n_slices, int slice_slots, int tail_slices,
+                                            int tail_slice_slots, unsigned int &batch, int &slice, int &ss) {
+    // items [0, heavy_batches * heavy_slices): the expensive first batches, cut finer
+    const unsigned int heavy_items = (unsigned int)heavy_batches * (unsigned int)heavy_slices;
+#if RT_SWEEP_SLICE_MAJOR
+    // within each of the three runs of items: slice-major (item = slice * batches + batch)
+    if (item < heavy_items) {
+        slice = (int)(item / (unsigned int)heavy_batches);
+        batch = item - (unsigned int)slice * (unsigned int)heavy_batches;
+        ss = heavy_slice_slots;
+    } else {
+        const unsigned int li = item - heavy_items, reg_items = (unsigned int)reg_batches * (unsigned int)n_slices;
+        if (li < reg_items) {
+            slice = (int)(li / (unsigned int)reg_batches);
+            batch = li - (unsigned int)slice * (unsigned int)reg_batches + (unsigned int)heavy_batches;
+            ss = slice_slots;
+        } else { // the last batches of the launch, cut finer: the launch ends on short items
+            const unsigned int lt = li - reg_items;
+            const long long tail_batches = (total + batch_rays - 1) / batch_rays - heavy_batches - reg_batches;
+            if (tail_batches <= 0 || lt >= (unsigned long long)tail_batches * (unsigned int)tail_slices) return false; // past the plan
+            slice = (int)(lt / (unsigned int)tail_batches);
+            batch = lt - (unsigned int)slice * (unsigned int)tail_batches + (unsigned int)heavy_batches + (unsigned int)reg_batches;
+            ss = tail_slice_slots;
+        }
+    }
+#else
+    if (item < heavy_items) {
+        batch = item / (unsigned int)heavy_slices;
+        slice = (int)(item - batch * (unsigned int)heavy_slices);
+        ss = heavy_slice_slots;
+    } else {
+        const unsigned int li = item - heavy_items, reg_items = (unsigned int)reg_batches * (unsigned int)n_slices;
+        if (li < reg_items) {
+            batch = li / (unsigned int)n_slices;
+            slice = (int)(li - batch * (unsigned int)n_slices);
+            batch += (unsigned int)heavy_batches;
+            ss = slice_slots;
+        } else { // the last batches of the launch, cut finer: the launch ends on short items
+            const unsigned int lt = li - reg_items;
+            batch = lt / (unsigned int)tail_slices;
+            slice = (int)(lt - batch * (unsigned int)tail_slices);
+            batch += (unsigned int)heavy_batches + (unsigned int)reg_batches;
+            ss = tail_slice_slots;
+        }
+    }
+#endif
+    return (long long)batch * batch_rays < total;
+}
+
 // One persistent CTA per SM; slots [slot_begin, slot_end) of the bound table stay in shared
 // memory for the whole launch (copied by the CTA's threads behind one block barrier; RT_SWEEP_BULK_TABLE
 // selects cp.async.bulk + mbarrier instead, measured slower).  A work item is (batch of
@@ -631,52 +685,11 @@ sweep_kernel(DevScene sc, RaySeg s0_, RaySeg s1, OriginTable ot_, int slot_begin
         unsigned int item = 0;
         if (lane == 0) item = atomicAdd(batch_counter, 1u);
         item = __shfl_sync(FULL, item, 0);
-        // items [0, heavy_batches * heavy_slices): the expensive first batches, cut finer
-        const unsigned int heavy_items = (unsigned int)heavy_batches * (unsigned int)heavy_slices;
         unsigned int batch;
         int slice, ss;
-#if RT_SWEEP_SLICE_MAJOR
-        // within each of the three runs of items: slice-major (item = slice * batches + batch)
-        if (item < heavy_items) {
-            slice = (int)(item / (unsigned int)heavy_batches);
-            batch = item - (unsigned int)slice * (unsigned int)heavy_batches;
-            ss = heavy_slice_slots;
-        } else {
-            const unsigned int li = item - heavy_items, reg_items = (unsigned int)reg_batches * (unsigned int)n_slices;
-            if (li < reg_items) {
-                slice = (int)(li / (unsigned int)reg_batches);
-                batch = li - (unsigned int)slice * (unsigned int)reg_batches + (unsigned int)heavy_batches;
-                ss = slice_slots;
-            } else { // the last batches of the launch, cut finer: the launch ends on short items
-                const unsigned int lt = li - reg_items;
-                const long long tail_batches = ((long long)total + R * 32 - 1) / (R * 32) - heavy_batches - reg_batches;
-                if (tail_batches <= 0 || lt >= (unsigned long long)tail_batches * (unsigned int)tail_slices) break; // past the plan
-                slice = (int)(lt / (unsigned int)tail_batches);
-                batch = lt - (unsigned int)slice * (unsigned int)tail_batches + (unsigned int)heavy_batches + (unsigned int)reg_batches;
-                ss = tail_slice_slots;
-            }
-        }
-#else
-        if (item < heavy_items) {
-            batch = item / (unsigned int)heavy_slices;
-            slice = (int)(item - batch * (unsigned int)heavy_slices);
-            ss = heavy_slice_slots;
-        } else {
-            const unsigned int li = item - heavy_items, reg_items = (unsigned int)reg_batches * (unsigned int)n_slices;
-            if (li < reg_items) {
-                batch = li / (unsigned int)n_slices;
-                slice = (int)(li - batch * (unsigned int)n_slices);
-                batch += (unsigned int)heavy_batches;
-                ss = slice_slots;
-            } else { // the last batches of the launch, cut finer: the launch ends on short items
-                const unsigned int lt = li - reg_items;
-                batch = lt / (unsigned int)tail_slices;
-                slice = (int)(lt - batch * (unsigned int)tail_slices);
-                batch += (unsigned int)heavy_batches + (unsigned int)reg_batches;
-                ss = tail_slice_slots;
-            }
-        }
-#endif
+        if (!decode_item(item, total, R * 32, heavy_batches, heavy_slices, heavy_slice_slots, reg_batches, n_slices, slice_slots, tail_slices,
+                         tail_slice_slots, batch, slice, ss))
+            break; // past the plan
         const long long ray0_ll = (long long)batch * (R * 32);
         if (ray0_ll >= total) break;
         RT_CHECK(slice >= 0 && (slot_begin + slice * ss < slot_end || slot_end == slot_begin) && ss % SEG_PAD == 0); // (an empty table has one empty slice)
@@ -1359,6 +1372,35 @@ cudaError_t launch_sweep(const DevScene &sc, RaySeg s0, RaySeg s1, OriginTable o
     return RT_SWEEP(1, 512, false, false);
 #undef RT_SWEEP
 }
+
+} // namespace rt
+
+// Test hook (include/rt_b200_debug.h): the item plan of a sweep of `total` rays (`heavy` of them expensive) against a resident
+// table of `per` slots on `warps` persistent warps, and the decoding of one of its items -- host code only, no GPU.
+extern "C" int rt_debug_plan_items(int32_t rays_per_thread, int64_t total, int32_t heavy, int32_t per, int64_t warps, int32_t n_chunks,
+                                   int32_t jobs, int64_t out[10]) {
+    using namespace rt;
+    if (!out || total < 0 || per < SEG_PAD || per % SEG_PAD != 0 || warps < 1 || n_chunks < 1) return -1;
+    ItemPlan pl;
+    if (rays_per_thread == 4) pl = plan_items<4>(total, heavy, per, warps, n_chunks, jobs != 0);
+    else if (rays_per_thread == 2) pl = plan_items<2>(total, heavy, per, warps, n_chunks, jobs != 0);
+    else if (rays_per_thread == 1) pl = plan_items<1>(total, heavy, per, warps, n_chunks, jobs != 0);
+    else return -1;
+    out[0] = pl.items; out[1] = pl.heavy_batches; out[2] = pl.heavy_slices; out[3] = pl.heavy_slice_slots; out[4] = pl.reg_batches;
+    out[5] = pl.n_slices; out[6] = pl.slice_slots; out[7] = pl.tail_slices; out[8] = pl.tail_slice_slots; out[9] = pl.merge;
+    return 0;
+}
+extern "C" int rt_debug_decode_item(uint32_t item, int64_t total, int32_t batch_rays, const int64_t plan[10], int64_t out[3]) {
+    if (!plan || !out || batch_rays < 1) return -1;
+    unsigned int batch = 0;
+    int slice = 0, ss = 0;
+    const bool ok = rt::decode_item(item, total, batch_rays, (int)plan[1], (int)plan[2], (int)plan[3], (int)plan[4], (int)plan[5], (int)plan[6],
+                                    (int)plan[7], (int)plan[8], batch, slice, ss);
+    out[0] = batch; out[1] = slice; out[2] = ss;
+    return ok ? 1 : 0;
+}
+
+namespace rt {
 
 int sweep_table_chunks(const DevScene &sc) {
     const int cap = sweep_table_cap<4, RT_SWEEP_T4, true>(); // the smallest of the kernels' capacities
