@@ -37,6 +37,14 @@ void rt_debug_reset(void);
  * (returns 1, or 0 past the plan).  -1: bad argument.                                                              */
 int rt_debug_plan_items(int32_t rays_per_thread, int64_t total, int32_t heavy, int32_t per, int64_t warps, int32_t n_chunks,
                         int32_t jobs, int64_t out[10]);
+/* The bound hierarchy the library derives from a scene description, as built on the host (no GPU): level 0 bound slots,
+ * 1 groups of 16, 2 quads of 64, 3 supers of 256; five doubles per sphere (cx, cy, cz, radius incl. slack, kind: 0 sphere,
+ * 1 pad, 2 passes every ray).  Returns the number of spheres of the level (at most `cap` are written) or a negative
+ * rt_status.  rt_debug_scene_scalars: out = {n_slots, cmax, slot_rmax, level_rmax of groups, quads, supers}.
+ * (rt_scene_desc: include/rt_b200.h, to be included first.)                                                        */
+struct rt_scene_desc;
+int rt_debug_scene_spheres(const struct rt_scene_desc *desc, int32_t level, double *out, int32_t cap);
+int rt_debug_scene_scalars(const struct rt_scene_desc *desc, double out[6]);
 int rt_debug_decode_item(uint32_t item, int64_t total, int32_t batch_rays, const int64_t plan[10], int64_t out[3]);
 
 #ifdef __cplusplus

@@ -1049,6 +1049,32 @@ const Knob KNOBS[] = {
 };
 } // namespace
 
+// Test hook: the bound hierarchy build_host_scene derives from a description, as the host sees it -- level 0 bound slots,
+// 1 groups, 2 quads, 3 supers, five doubles per sphere (cx, cy, cz, radius incl. slack, kind: 0 sphere, 1 pad, 2 passes every
+// ray).  Returns the number of spheres of the level (up to `cap` are written), or a negative rt_status.  No GPU.
+int rt_debug_scene_spheres(const rt_scene_desc *desc, int32_t level, double *out, int32_t cap) {
+    if (!desc || level < 0 || level > 3 || (cap > 0 && !out)) return fail(RT_ERR_INVALID, "bad argument");
+    std::shared_ptr<const HostScene> hs;
+    int rc = host_scene_for(desc, &hs);
+    if (rc != RT_OK) return rc;
+    if (!hs->origin) return fail(RT_ERR_UNSUPPORTED, "the scene keeps no host copy of its hierarchy (origin tables are off)");
+    const std::vector<HostSlot> &v = level == 0 ? hs->slots : (level == 1 ? hs->groups : (level == 2 ? hs->quads : hs->supers));
+    for (size_t i = 0; i < v.size() && (int32_t)i < cap; ++i) {
+        out[5 * i] = v[i].cx; out[5 * i + 1] = v[i].cy; out[5 * i + 2] = v[i].cz; out[5 * i + 3] = v[i].rf; out[5 * i + 4] = v[i].kind;
+    }
+    return (int)v.size();
+}
+// ... and the scalars the sweeps take from it: out = {n_slots, cmax, slot_rmax, level_rmax[0..2]}.
+int rt_debug_scene_scalars(const rt_scene_desc *desc, double out[6]) {
+    if (!desc || !out) return fail(RT_ERR_INVALID, "bad argument");
+    std::shared_ptr<const HostScene> hs;
+    int rc = host_scene_for(desc, &hs);
+    if (rc != RT_OK) return rc;
+    const DevScene &d = hs->dev;
+    out[0] = d.n_slots; out[1] = d.cmax; out[2] = d.slot_rmax; out[3] = d.level_rmax[0]; out[4] = d.level_rmax[1]; out[5] = d.level_rmax[2];
+    return RT_OK;
+}
+
 int rt_debug_set(const char *name, int64_t value) {
     if (!name) return fail(RT_ERR_INVALID, "null argument");
     for (const Knob &k : KNOBS)
