@@ -45,6 +45,10 @@ int rt_debug_plan_items(int32_t rays_per_thread, int64_t total, int32_t heavy, i
 struct rt_scene_desc;
 int rt_debug_scene_spheres(const struct rt_scene_desc *desc, int32_t level, double *out, int32_t cap);
 int rt_debug_scene_scalars(const struct rt_scene_desc *desc, double out[6]);
+/* The origin table of point light `light` (in the order of the point lights of the description), unpacked: four doubles per
+ * sphere (cx, cy, cz, W' = |C'|^2 - R'^2, all relative to the light) -- the slots, then groups, quads, supers --
+ * and out_origin = {light x, y, z, reach, rmax}.  Returns the number of spheres or a negative rt_status.             */
+int rt_debug_scene_light_table(const struct rt_scene_desc *desc, int32_t light, double *out, int32_t cap, double out_origin[5]);
 int rt_debug_decode_item(uint32_t item, int64_t total, int32_t batch_rays, const int64_t plan[10], int64_t out[3]);
 
 #ifdef __cplusplus

@@ -73,6 +73,7 @@ def _declare(lib):
     lib.rt_debug_plan_items.argtypes = [C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int32, P(C.c_int64)]
     lib.rt_debug_scene_spheres.argtypes = [P(abi.rt_scene_desc), C.c_int32, P(C.c_double), C.c_int32]
     lib.rt_debug_scene_scalars.argtypes = [P(abi.rt_scene_desc), P(C.c_double)]
+    lib.rt_debug_scene_light_table.argtypes = [P(abi.rt_scene_desc), C.c_int32, P(C.c_double), C.c_int32, P(C.c_double)]
     lib.rt_debug_decode_item.argtypes = [C.c_uint32, C.c_int64, C.c_int32, P(C.c_int64), P(C.c_int64)]
     # host helpers
     lib.rt_builtin_scene.argtypes = [C.c_char_p, C.c_uint64, P(P(abi.rt_scene_desc))]
@@ -108,7 +109,7 @@ EXPORTS = [
 
 # include/rt_b200_debug.h: test and measurement hooks, not part of the drop-in ABI
 DEBUG_EXPORTS = ["rt_debug_set", "rt_debug_get", "rt_debug_reset", "rt_debug_plan_items", "rt_debug_decode_item",
-                 "rt_debug_scene_spheres", "rt_debug_scene_scalars"]
+                 "rt_debug_scene_spheres", "rt_debug_scene_scalars", "rt_debug_scene_light_table"]
 
 
 def lib():

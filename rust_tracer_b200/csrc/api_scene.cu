@@ -1064,6 +1064,27 @@ int rt_debug_scene_spheres(const rt_scene_desc *desc, int32_t level, double *out
     }
     return (int)v.size();
 }
+// The table of point light `light` (by DevLight::point_index order) as the sweeps read it, unpacked: four doubles per sphere
+// (cx, cy, cz, W) relative to the light -- the slots, then the groups, quads and supers -- and out_origin = the light's
+// position, reach, rmax.  Returns the number of spheres (at most `cap` written) or a negative rt_status.
+int rt_debug_scene_light_table(const rt_scene_desc *desc, int32_t light, double *out, int32_t cap, double out_origin[5]) {
+    if (!desc || light < 0 || (cap > 0 && !out)) return fail(RT_ERR_INVALID, "bad argument");
+    std::shared_ptr<const HostScene> hs;
+    int rc = host_scene_for(desc, &hs);
+    if (rc != RT_OK) return rc;
+    if (!hs->origin || light >= (int)hs->light_host.size()) return fail(RT_ERR_INVALID, "no such light table");
+    const std::vector<float4> &t = hs->light_host[light];
+    for (size_t j = 0; j + 1 < t.size() && (int32_t)(j + 1) < cap; j += 2) { // pairs: (x0, x1, y0, y1), (z0, z1, W0, W1)
+        const float4 a = t[j], b = t[j + 1];
+        out[4 * j] = a.x; out[4 * j + 1] = a.z; out[4 * j + 2] = b.x; out[4 * j + 3] = b.z;
+        out[4 * j + 4] = a.y; out[4 * j + 5] = a.w; out[4 * j + 6] = b.y; out[4 * j + 7] = b.w;
+    }
+    if (out_origin) {
+        const OriginTable &ot = hs->light_tabs[light];
+        out_origin[0] = ot.ox; out_origin[1] = ot.oy; out_origin[2] = ot.oz; out_origin[3] = ot.reach; out_origin[4] = ot.rmax;
+    }
+    return (int)t.size();
+}
 // ... and the scalars the sweeps take from it: out = {n_slots, cmax, slot_rmax, level_rmax[0..2]}.
 int rt_debug_scene_scalars(const rt_scene_desc *desc, double out[6]) {
     if (!desc || !out) return fail(RT_ERR_INVALID, "bad argument");

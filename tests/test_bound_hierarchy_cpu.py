@@ -88,3 +88,47 @@ def test_hooks_refuse_bad_arguments():
     assert L.rt_debug_scene_spheres(C.byref(desc.desc), 4, None, 0) < 0
     assert L.rt_debug_scene_spheres(None, 0, None, 0) < 0
     assert L.rt_debug_scene_scalars(C.byref(desc.desc), None) < 0
+
+
+def _light_table(desc, light):
+    L = rt.lib()
+    origin = (C.c_double * 5)()
+    n = L.rt_debug_scene_light_table(C.byref(desc.desc), light, None, 0, origin)
+    assert n > 0
+    buf = np.zeros((n, 4), np.float64)
+    assert L.rt_debug_scene_light_table(C.byref(desc.desc), light, buf.ctypes.data_as(C.POINTER(C.c_double)), n, origin) == n
+    return buf, np.array(origin[:3]), origin[3], origin[4]
+
+
+@pytest.mark.parametrize("name", ["default", "m10k"])
+def test_origin_tables_hold_the_same_spheres_seen_from_the_light(name):
+    """A light's table is the hierarchy re-centred on the light: C' = C - L rounded to f32, W' = |C'|^2 - R'^2 with R' no
+    smaller than the radius plus the centre's rounding displacement (so the re-centred sphere contains the original), pads
+    stay pads, and rmax / reach bound the slots' radii / every sphere's reach."""
+    desc = rt.SceneDesc.builtin(name)
+    levels = [_level(desc, k) for k in range(4)]
+    allspheres = np.concatenate(levels)
+    n_slots = len(levels[0])
+    n_point = sum(1 for i in range(desc.desc.n_lights) if desc.desc.lights[i].kind == 0)
+    assert n_point >= 1
+    for light in range(n_point):
+        tab, pos, reach, rmax = _light_table(desc, light)
+        assert len(tab) == len(allspheres)
+        real = allspheres[:, 4] == 0
+        assert (tab[allspheres[:, 4] == 1, 3] >= 3e38).all()  # pads pass no ray
+        want = allspheres[real, :3] - pos
+        got = tab[real, :3]
+        disp = np.linalg.norm(got - want, axis=1)
+        assert (disp <= 1e-6 * (np.linalg.norm(want, axis=1) + 1.0)).all()  # one f32 rounding of the re-centred centre
+        r2 = (got ** 2).sum(1) - tab[real, 3]  # R'^2 as the filter sees it
+        assert (r2 > 0).all()
+        rprime = np.sqrt(r2)
+        need = allspheres[real, 3] + disp
+        # W' is rounded down in f32 (R' only grows); cancellation in |C'|^2 - W' costs a few ulp of |C'|^2 here
+        slack = 4e-7 * (got ** 2).sum(1) / np.maximum(rprime, 1e-30)
+        assert (rprime + slack >= need).all()
+        assert (rprime <= need * 1.001 + slack + 1e-6).all()  # ... and not much larger: the table still culls
+        slots_real = allspheres[:n_slots, 4] == 0
+        assert rmax >= allspheres[:n_slots][slots_real, 3].max()
+        # reach = |L| + cmax: no sphere of the table reaches further from the light (|C - L| + R <= |L| + |C| + R)
+        assert (np.linalg.norm(got, axis=1) + rprime).max() <= reach * (1 + 1e-5)
